@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py -- STFT -> iSTFT round-trip throughput of the hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4] [--impl reference]
+
+One "step" = one pass of the three kernels (K1 frame+window+rFFT, K2 irFFT+synthesis window,
+K3 gather overlap-add) over one batch of synthetic input already resident in HBM.  Workloads
+(BASELINE.json configs):
+  c2 (default)  per rank: 1 channel x 2^30 samples, frame 2048 hop 512 Hann      [configs[1]]
+                N>1: N independent channels, one per rank, no communication (weak scaling)
+  c3            256 channels x 2^24 samples, frame 1024 hop 256, channels sharded over the
+                ranks (strong scaling; one rank processes its share in batches of 32 channels)
+  c4            one signal of N x 2^30 samples, frame 4096 hop 1024, time-sharded with a
+                (frame-hop)-sample halo exchanged between neighbour ranks over NCCL (weak)
+Rank 0 prints ONE JSON line.  `--impl reference` times the reference's CPU path instead
+(oracle/_ref built from the reference sources when present, else the plain-C oracle port).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "c2": dict(nfft=2048, hop=512, channels=1, length=1 << 30,
+               name="c2: 1ch x 2^30 fp32 samples per GPU, frame 2048 hop 512 Hann (BASELINE configs[1])"),
+    "c3": dict(nfft=1024, hop=256, channels=256, length=1 << 24,
+               name="c3: 256ch x 2^24 samples, frame 1024 hop 256 Hann, channel-sharded (BASELINE configs[2])"),
+    "c4": dict(nfft=4096, hop=1024, channels=1, length=1 << 30,
+               name="c4: single signal of n_gpus x 2^30 samples, frame 4096 hop 1024 Hann, time-sharded, NCCL halo (BASELINE configs[3])"),
+}
+SEED = 0xC0FFEE
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arms (the only places bench.py touches oracle/)
+# ------------------------------------------------------------------------------------------------
+def cpu_roundtrip_throughput(nfft, hop, per_thread_len, threads):
+    """All-thread reference-CPU throughput in samples/s on a bounded sample.  Each thread runs an
+    independent mono round trip (the reference is single-threaded; independent channels are the
+    only parallelism it admits)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+    orc = po.Oracle()
+    if po.Ref.available():
+        ref = po.Ref()
+        w = orc.window(po.HANN, nfft)
+        xs = [orc.synth_uniform(SEED, t, 0, per_thread_len) for t in range(threads)]
+        bar = threading.Barrier(threads + 1)
+        t_end = [0.0] * threads
+
+        def work(i):
+            bar.wait()
+            ref.roundtrip(xs[i], nfft, hop, w, po.DROP, taps=False)      # ctypes drops the GIL
+            t_end[i] = time.perf_counter()
+        th = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+        for t in th:
+            t.start()
+        bar.wait()
+        t0 = time.perf_counter()
+        for t in th:
+            t.join()
+        dt = max(t_end) - t0
+        kind = "reference"
+    else:
+        dt, _ = orc.bench_roundtrip_mt(threads, per_thread_len, nfft, hop, po.HANN, SEED)
+        kind = "port"
+    return threads * per_thread_len / dt, kind, dt
+
+
+def run_reference_arm(args, wl, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    per = 1 << 22
+    vals = []
+    kind = "port"
+    for i in range(args.warmup + args.steps):
+        v, kind, dt = cpu_roundtrip_throughput(wl["nfft"], wl["hop"], per, threads)
+        if i >= args.warmup:
+            vals.append((v, dt))
+    v = float(np.mean([a for a, _ in vals]))
+    sample = f"{threads} threads x 2^22 samples (independent mono round trips) per step, frame {wl['nfft']} hop {wl['hop']}"
+    line = {
+        "impl": "reference", "metric": "stft_istft_roundtrip_throughput", "value": v / 1e6, "unit": "Msamples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": float(np.mean([b for _, b in vals])) * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "note": "reference CPU path on host cores; Highway kernels replaced by the "
+                   "reference's scalar kernels auto-vectorised by GCC (Highway not vendored)"},
+        "cpu_baseline": {"value": v / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": v / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ------------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.p = index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except Exception:
+            out = ""
+        sm, mx, reasons, pw = [], [], set(), []
+        for ln in out.splitlines():
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--length-log2", type=int, default=None, help="override samples per channel (debug)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    wl = dict(WORKLOADS[args.workload])
+    if args.length_log2:
+        wl["length"] = 1 << args.length_log2
+        wl["name"] += f" [length overridden to 2^{args.length_log2}]"
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, wl, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import crlot_dsp_b200 as dsp
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (the product has no CPU path)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
+
+    N, H = wl["nfft"], wl["hop"]
+    w = dsp.window_make(dsp.HANN, N)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP, device=local)
+    halo = N - H
+
+    # ---- lay the workload out on this rank ------------------------------------------------------
+    if args.workload == "c2":
+        chans, L, batch = 1, wl["length"], 1
+        x = dsp.synth_uniform(1, L, seed=SEED, channel0=rank, device=local)
+        local_samples = L
+        scaling = "weak"
+    elif args.workload == "c3":
+        assert wl["channels"] % world == 0
+        chans, L = wl["channels"] // world, wl["length"]
+        batch = min(32, chans)                      # workspace batch: 32 ch = 21.5 GB of spectra+frames
+        x = dsp.synth_uniform(chans, L, seed=SEED, channel0=rank * chans, device=local)
+        local_samples = chans * L
+        scaling = "strong"
+    else:  # c4: rank r owns output/time range [r*S, (r+1)*S); receives N-H input samples from BOTH neighbours
+        chans, batch = 1, 1
+        S = wl["length"]
+        left = halo if rank > 0 else 0
+        right = halo if rank < world - 1 else 0
+        xbuf = torch.zeros(left + S + right, dtype=torch.float32, device=dev)
+        dsp.synth_uniform(1, S, seed=SEED, channel0=0, i0=rank * S, device=local, out=xbuf[left:left + S].unsqueeze(0))
+        local_samples = S
+        scaling = "weak"
+
+    def halo_exchange():
+        """NCCL send/recv of the (frame-hop)-sample halos between neighbouring ranks."""
+        ops = []
+        if rank > 0:
+            ops.append(dist.P2POp(dist.isend, xbuf[left:left + halo], rank - 1))
+            ops.append(dist.P2POp(dist.irecv, xbuf[:left], rank - 1))
+        if rank < world - 1:
+            ops.append(dist.P2POp(dist.isend, xbuf[left + S - halo:left + S], rank + 1))
+            ops.append(dist.P2POp(dist.irecv, xbuf[left + S:], rank + 1))
+        if ops:
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+
+    # workspaces
+    if args.workload == "c4":
+        Ltot = left + S + right
+        # local frames: global frame k with k*H in [r*S - halo, (r+1)*S) (left-halo frames are recomputed so
+        # every rank sums the same terms in the same order as one GPU would); last rank follows DROP
+        F = dsp.frame_count(Ltot, N, H, dsp.DROP) if rank == world - 1 else (Ltot - halo) // H if right else dsp.frame_count(Ltot, N, H, dsp.DROP)
+        F = min(F, dsp.frame_count(Ltot, N, H, dsp.DROP))
+        n_out = S if rank < world - 1 else (F - 1) * H + N - left
+        spec = torch.empty((1, F, plan.bins), dtype=torch.complex64, device=dev)
+        frames = torch.empty((1, F, N), dtype=torch.float32, device=dev)
+        out = torch.empty((1, n_out), dtype=torch.float32, device=dev)
+    else:
+        F = plan.n_frames(L)
+        spec = torch.empty((batch, F, plan.bins), dtype=torch.complex64, device=dev)
+        frames = torch.empty((batch, F, N), dtype=torch.float32, device=dev)
+        out = torch.empty((chans, plan.out_len(L)), dtype=torch.float32, device=dev)
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    kt = {"k1": [], "k2": [], "k3": []}
+
+    def step(record=False):
+        launches = 0
+        if args.workload == "c4":
+            if world > 1:
+                halo_exchange()
+            e = [ev() for _ in range(4)] if record else None
+            if record: e[0].record()
+            plan.stft(xbuf.unsqueeze(0), length=Ltot, n_frames=F, out=spec)
+            if record: e[1].record()
+            plan.istft_frames(spec, fuse_synthesis_window=True, out=frames)
+            if record: e[2].record()
+            plan.ola(frames, prewindowed=True, t_offset=rank * S, frame_t0=-left, n_out=n_out, out=out)
+            if record: e[3].record()
+            if record:
+                kt["_ev"].append(e)
+            return 3
+        for c0 in range(0, chans, batch):
+            xb = x[c0:c0 + batch]
+            e = [ev() for _ in range(4)] if record else None
+            if record: e[0].record()
+            plan.stft(xb, out=spec)
+            if record: e[1].record()
+            plan.istft_frames(spec, fuse_synthesis_window=True, out=frames)
+            if record: e[2].record()
+            plan.ola(frames, prewindowed=True, out=out[c0:c0 + batch])
+            if record: e[3].record()
+            if record:
+                kt["_ev"].append(e)
+            launches += 3
+        return launches
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sync_all()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    kt["_ev"] = []
+    t_beg, t_end = ev(), ev()
+    sync_all()
+    t_beg.record()
+    launches = 0
+    for _ in range(args.steps):
+        launches += step(record=True)
+    t_end.record()
+    sync_all()
+    clk = clocks.stop() if rank == 0 else None
+    ms = t_beg.elapsed_time(t_end)
+    for e in kt["_ev"]:
+        kt["k1"].append(e[0].elapsed_time(e[1])); kt["k2"].append(e[1].elapsed_time(e[2])); kt["k3"].append(e[2].elapsed_time(e[3]))
+    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms = float(tmax.item())
+    total_samples = local_samples * world
+    value = total_samples * args.steps / (ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (rank 0's launches) --------------------------------------
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    bins = N // 2 + 1
+    frames_per_launch = F * (batch if args.workload != "c4" else 1)
+    samples_per_launch = frames_per_launch * H             # new samples consumed per launch
+    alg = {"k1": 4.0 * samples_per_launch + 8.0 * bins * frames_per_launch,
+           "k2": (8.0 * bins + 4.0 * N) * frames_per_launch,
+           "k3": 4.0 * N * frames_per_launch + 4.0 * samples_per_launch}
+    kavg = {k: float(np.mean(kt[k])) for k in ("k1", "k2", "k3")}
+    dom = max(kavg, key=kavg.get)
+    names = {"k1": "stft_fwd_kernel (K1 frame+window+rFFT)", "k2": "istft_inv_kernel (K2 irFFT+synthesis window)",
+             "k3": "ola_gather_kernel (K3 gather overlap-add)"}
+    achieved = alg[dom] / (kavg[dom] * 1e-3) / 1e9
+    per_kernel = {k: {"ms": kavg[k], "alg_GB": alg[k] / 1e9, "GBps": alg[k] / (kavg[k] * 1e-3) / 1e9,
+                      "frac": alg[k] / (kavg[k] * 1e-3) / 1e9 / peak} for k in kavg}
+    path_gbps = dsp.bytes_per_sample(N, H) * (value / world) / 1e9
+    roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "per_kernel": per_kernel,
+                "path": {"bytes_per_sample": dsp.bytes_per_sample(N, H), "achieved_GBps_per_gpu": path_gbps,
+                         "frac_of_measured": path_gbps / peak, "frac_of_8TBps_nominal": path_gbps / 8000.0}}
+
+    # ---- e2e: host buffers through the C-ABI host entry point, copies inside the timed region -----
+    e2e = None
+    if not args.no_e2e:
+        Le = wl["length"] if args.workload != "c3" else wl["length"]
+        ce = 1 if args.workload != "c3" else min(chans, 4)
+        nbytes = ce * Le * 4
+        hin = torch.empty((ce, Le), dtype=torch.float32).pin_memory()
+        hin.copy_(x[:ce, :Le] if args.workload != "c4" else xbuf[left:left + Le].unsqueeze(0))
+        n_out_e = plan.out_len(Le)
+        hout = torch.empty((ce, n_out_e), dtype=torch.float32).pin_memory()
+        hin_np, hout_np = hin.numpy(), hout.numpy()
+        plan.roundtrip_host(hin_np, out=hout_np)                 # warm-up (allocates the slab workspace)
+        sync_all()
+        n_e2e = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            plan.roundtrip_host(hin_np, out=hout_np)             # synchronous: returns when h_out is complete
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": ce * Le * world * n_e2e / float(dt.item()) / 1e6, "unit": "Msamples/s",
+               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": ce * n_out_e * 4, "steps": n_e2e,
+               "api": "crlot_roundtrip_host (pinned host buffers, slabbed H2D/compute/D2H pipeline)",
+               "workload": f"{ce}ch x 2^{int(np.log2(Le))} samples per rank"}
+        del hin, hout
+
+    cpu = None
+    if rank == 0 and not args.no_cpu and world == 1:
+        threads = os.cpu_count() or 1
+        per = 1 << 24
+        v, kind, dt = cpu_roundtrip_throughput(N, H, per, threads)
+        cpu = {"value": v / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
+               "sample": f"{threads} threads x 2^24 samples, independent mono round trips, frame {N} hop {H} ({dt:.1f} s); "
+                         "Highway kernels replaced by the reference's scalar kernels (Highway not vendored)"}
+
+    if rank == 0:
+        line = {
+            "metric": "stft_istft_roundtrip_throughput", "value": value / 1e6, "unit": "Msamples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["name"], "frame": N, "hop": H, "channels_per_rank": chans,
+                       "samples_per_rank": local_samples, "frames_per_launch": frames_per_launch,
+                       "cache": "inputs larger than L2 (every buffer >> 126 MB), no flush needed",
+                       "generator": "counter hash uniform[-1,1), seed 0xC0FFEE"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

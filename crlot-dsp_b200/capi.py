@@ -1,0 +1,372 @@
+"""ctypes binding of include/crlot_cuda.h.  Host-side mirror of the reference's interface for
+the hot path: same names / argument meaning / error behaviour (status codes come back as the
+Python analogue of the reference's exception types)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+HANN, HAMMING, BLACKMAN, RECT, BLACKMAN_HARRIS = 0, 1, 2, 3, 4
+NORM_NONE, NORM_SUM_TO_ONE, NORM_L2, NORM_OLA_UNITY_GAIN, NORM_OLA_SUM_WSQ = 0, 1, 2, 3, 4
+ZERO_PAD, DROP = 0, 1
+
+
+class CrlotError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"crlot_cuda status {code}: {msg}")
+        self.code = code
+
+
+class CrlotInvalidArgument(CrlotError, ValueError):     # std::invalid_argument
+    pass
+
+
+class CrlotUnsupported(CrlotError):
+    pass
+
+
+def lib_path() -> str:
+    return os.path.join(HERE, "libcrlot_cuda.so")
+
+
+_lib = None
+
+
+class _Desc(C.Structure):
+    _fields_ = [("nfft", C.c_int), ("hop", C.c_int), ("boundary_mode", C.c_int),
+                ("analysis_window", C.c_void_p), ("ola_window", C.c_void_p), ("push_window", C.c_void_p),
+                ("apply_window_inside", C.c_int), ("gain", C.c_float), ("eps", C.c_float), ("scrub", C.c_int),
+                ("envelope", C.c_void_p), ("envelope_len", C.c_size_t), ("device", C.c_int)]
+
+
+class _Info(C.Structure):
+    _fields_ = [("nfft", C.c_int), ("hop", C.c_int), ("bins", C.c_int), ("ring_len", C.c_size_t),
+                ("synthesis_window_active", C.c_int), ("device", C.c_int)]
+
+
+def lib():
+    """Load the CUDA C-ABI library.  There is no fallback: a missing library is an error."""
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise ImportError(f"{p} not built: run `python crlot-dsp_b200/build.py` (the product has no CPU path)")
+        L = C.CDLL(p)
+        L.crlot_cuda_last_error.restype = C.c_char_p
+        L.crlot_frame_count.restype = C.c_longlong
+        L.crlot_ola_ring_len.restype = C.c_size_t
+        L.crlot_buf_device_ptr.restype = C.c_void_p
+        L.crlot_buf_bytes.restype = C.c_size_t
+        L.crlot_ola_get.restype = C.c_size_t
+        L.crlot_ola_meter_peak.restype = C.c_float
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        msg = lib().crlot_cuda_last_error().decode()
+        if rc == 1:
+            raise CrlotInvalidArgument(rc, msg)
+        if rc == 4:
+            raise CrlotUnsupported(rc, msg)
+        if rc == 3:
+            raise MemoryError(msg)
+        raise CrlotError(rc, msg)
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, np.float32)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+# ---- host-side table builders -----------------------------------------------------------------
+def window_make(wtype, n, periodic=False, norm=NORM_NONE):
+    out = np.empty(max(int(n), 0), np.float32)
+    _check(lib().crlot_window_make(C.c_int(wtype), C.c_size_t(n), C.c_int(int(periodic)), C.c_int(norm), _p(out)))
+    return out
+
+
+def ola_ring_len(frame, hop):
+    return int(lib().crlot_ola_ring_len(C.c_size_t(frame), C.c_size_t(hop)))
+
+
+def build_norm_linear(window, ring_len, frame, hop):
+    w = _f32(window)
+    norm = np.empty(ring_len, np.float32)
+    _check(lib().crlot_build_norm_linear(_p(norm), _p(w), C.c_size_t(ring_len), C.c_size_t(frame), C.c_size_t(hop)))
+    return norm
+
+
+def ola_envelope(window, frame, hop, apply_window_inside=True, eps=1e-8):
+    ring = ola_ring_len(frame, hop)
+    norm = np.empty(ring, np.float32)
+    w = _f32(window)
+    _check(lib().crlot_ola_envelope(_p(norm), _p(w), C.c_size_t(ring), C.c_size_t(frame), C.c_size_t(hop),
+                                    C.c_int(int(apply_window_inside)), C.c_float(eps)))
+    return norm
+
+
+def frame_count(length, frame, hop, mode):
+    return int(lib().crlot_frame_count(C.c_longlong(length), C.c_int(frame), C.c_int(hop), C.c_int(mode)))
+
+
+def bytes_per_sample(nfft, hop):
+    """Algorithmic HBM bytes per input sample of the three-kernel contract."""
+    return 8.0 + 16.0 * (nfft / 2 + 1) / hop + 8.0 * nfft / hop
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _stream_ptr(device):
+    torch = _torch()
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def synth_uniform(channels, n, seed=0xC0FFEE, channel0=0, i0=0, device=0, out=None):
+    torch = _torch()
+    if out is None:
+        out = torch.empty((channels, n), dtype=torch.float32, device=f"cuda:{device}")
+    _check(lib().crlot_synth_uniform(C.c_void_p(out.data_ptr()), C.c_longlong(out.stride(0) if out.dim() == 2 else n),
+                                     C.c_int(channels), C.c_longlong(n), C.c_ulonglong(seed), C.c_ulonglong(channel0),
+                                     C.c_ulonglong(i0), C.c_int(device), _stream_ptr(device)))
+    return out
+
+
+# ---- STFT plan ----------------------------------------------------------------------------------
+class Plan:
+    """crlot_stft_plan_*: tables for one (nfft, hop, windows, OLA policy) on one device.
+
+    analysis_window : what the caller multiplies frames by before forward()  (e2e_benchmark.cc:154-156)
+    ola_window      : what OLAAccumulator::set_window() received
+    push_window     : per-call window argument of add_frame_SoA (used when not apply_window_inside)
+    """
+
+    def __init__(self, nfft, hop, analysis_window=None, ola_window=None, push_window=None,
+                 apply_window_inside=True, gain=1.0, eps=1e-8, boundary_mode=DROP, scrub=True,
+                 envelope=None, device=0):
+        self._h = C.c_void_p()
+        self._keep = [_f32(analysis_window), _f32(ola_window), _f32(push_window), _f32(envelope)]
+        for w in self._keep[:3]:
+            if w is not None and w.size != nfft:
+                raise CrlotInvalidArgument(1, "Window size must match frame size")
+        d = _Desc(nfft, hop, boundary_mode, _p(self._keep[0]), _p(self._keep[1]), _p(self._keep[2]),
+                  int(apply_window_inside), gain, eps, int(scrub), _p(self._keep[3]),
+                  0 if envelope is None else self._keep[3].size, device)
+        _check(lib().crlot_stft_plan_create(C.byref(d), C.byref(self._h)))
+        info = _Info()
+        _check(lib().crlot_stft_plan_info(self._h, C.byref(info)))
+        self.nfft, self.hop, self.bins, self.ring_len = info.nfft, info.hop, info.bins, info.ring_len
+        self.synthesis_window_active = bool(info.synthesis_window_active)
+        self.device = device
+        self.boundary_mode = boundary_mode
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().crlot_stft_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def envelope(self):
+        out = np.empty(self.ring_len, np.float32)
+        _check(lib().crlot_stft_plan_envelope(self._h, _p(out)))
+        return out
+
+    def n_frames(self, length):
+        return frame_count(length, self.nfft, self.hop, self.boundary_mode)
+
+    def out_len(self, length):
+        f = self.n_frames(length)
+        return (f - 1) * self.hop + self.nfft if f > 0 else 0
+
+    # -- kernels, device tensors -------------------------------------------------------------
+    def stft(self, signal, length=None, n_frames=None, out=None):
+        """signal: cuda float32 [channels, L] (row stride multiple of 4) -> complex64 [channels, F, bins]."""
+        torch = _torch()
+        if signal.dim() == 1:
+            signal = signal.unsqueeze(0)
+        ch = signal.shape[0]
+        length = signal.shape[1] if length is None else length
+        F = self.n_frames(length) if n_frames is None else n_frames
+        if out is None:
+            out = torch.empty((ch, F, self.bins), dtype=torch.complex64, device=signal.device)
+        _check(lib().crlot_stft_execute(self._h, C.c_void_p(signal.data_ptr()), C.c_longlong(signal.stride(0) if ch > 1 else 0),
+                                        C.c_longlong(length), C.c_int(ch), C.c_longlong(F), C.c_void_p(out.data_ptr()),
+                                        _stream_ptr(self.device)))
+        return out
+
+    def istft_frames(self, spec, fuse_synthesis_window=False, out=None):
+        """spec: complex64 [..., bins] -> float32 [..., nfft] frames (1/N scaled, cleaned up)."""
+        torch = _torch()
+        rows = spec.numel() // self.bins
+        if out is None:
+            out = torch.empty(spec.shape[:-1] + (self.nfft,), dtype=torch.float32, device=spec.device)
+        _check(lib().crlot_istft_execute(self._h, C.c_void_p(spec.data_ptr()), C.c_longlong(rows), C.c_void_p(out.data_ptr()),
+                                         C.c_int(int(fuse_synthesis_window)), _stream_ptr(self.device)))
+        return out
+
+    def ola(self, frames, prewindowed=False, t_offset=0, frame_t0=0, n_out=None, out=None):
+        """frames: float32 [channels, F, nfft] -> float32 [channels, n_out]."""
+        torch = _torch()
+        if frames.dim() == 2:
+            frames = frames.unsqueeze(0)
+        ch, F = frames.shape[0], frames.shape[1]
+        if n_out is None:
+            n_out = (F - 1) * self.hop + self.nfft if F > 0 else 0
+        if out is None:
+            out = torch.empty((ch, n_out), dtype=torch.float32, device=frames.device)
+        _check(lib().crlot_ola_accumulate(self._h, C.c_void_p(frames.data_ptr()), C.c_longlong(F), C.c_longlong(F), C.c_int(ch),
+                                          C.c_int(int(prewindowed)), C.c_longlong(t_offset), C.c_longlong(frame_t0),
+                                          C.c_void_p(out.data_ptr()), C.c_longlong(out.stride(0) if ch > 1 else 0),
+                                          C.c_longlong(n_out), _stream_ptr(self.device)))
+        return out
+
+    def roundtrip(self, signal, spec=None, frames=None, out=None, length=None):
+        """K1 -> K2 (synthesis window fused) -> K3 on device tensors; returns (out, spec, frames)."""
+        torch = _torch()
+        if signal.dim() == 1:
+            signal = signal.unsqueeze(0)
+        ch = signal.shape[0]
+        length = signal.shape[1] if length is None else length
+        F = self.n_frames(length)
+        if spec is None:
+            spec = torch.empty((ch, F, self.bins), dtype=torch.complex64, device=signal.device)
+        if frames is None:
+            frames = torch.empty((ch, F, self.nfft), dtype=torch.float32, device=signal.device)
+        if out is None:
+            out = torch.empty((ch, self.out_len(length)), dtype=torch.float32, device=signal.device)
+        _check(lib().crlot_roundtrip_execute(self._h, C.c_void_p(signal.data_ptr()), C.c_longlong(signal.stride(0) if ch > 1 else 0),
+                                             C.c_longlong(length), C.c_int(ch), C.c_void_p(spec.data_ptr()),
+                                             C.c_void_p(frames.data_ptr()), C.c_void_p(out.data_ptr()),
+                                             C.c_longlong(out.stride(0) if ch > 1 else 0), _stream_ptr(self.device)))
+        return out, spec, frames
+
+    # -- host buffers (H2D / D2H inside the call) ----------------------------------------------
+    def roundtrip_host(self, x, out=None):
+        """x: numpy float32 [channels, L] or [L] (ideally page-locked) -> numpy [channels, n_out]."""
+        x = np.asarray(x)
+        assert x.dtype == np.float32 and x.flags.c_contiguous
+        x2 = x.reshape(1, -1) if x.ndim == 1 else x
+        ch, L = x2.shape
+        n_out = self.out_len(L)
+        if out is None:
+            out = np.empty((ch, n_out), np.float32)
+        got = C.c_longlong(0)
+        _check(lib().crlot_roundtrip_host(self._h, _p(x2), C.c_longlong(L), C.c_longlong(L), C.c_int(ch), _p(out),
+                                          C.c_longlong(out.shape[-1] if out.ndim == 2 else n_out), C.byref(got)))
+        assert got.value == n_out
+        return out
+
+
+# ---- drop-in FFT plan (dsp::fft::IFftPlan over host arrays) ---------------------------------------
+class FftPlan:
+    def __init__(self, nfft, batch=1, stride_in=1, stride_out=1, in_place=False, device=0):
+        self._h = C.c_void_p()
+        self.nfft, self.batch, self.si, self.so = nfft, batch, stride_in, stride_out
+        _check(lib().crlot_fft_plan_create(C.c_int(nfft), C.c_int(int(in_place)), C.c_int(batch), C.c_int(stride_in),
+                                           C.c_int(stride_out), C.c_int(device), C.byref(self._h)))
+
+    def __del__(self):
+        try:
+            if self._h.value:
+                lib().crlot_fft_plan_destroy(self._h)
+        except Exception:
+            pass
+
+    def size(self):
+        return self.nfft
+
+    def max_batch_size(self):
+        return 16
+
+    def forward(self, x, batch=1, out_len=None):
+        x = _f32(x)
+        nb = self.nfft // 2 + 1
+        out = np.zeros(2 * (out_len if out_len is not None else batch * self.so * nb), np.float32)
+        _check(lib().crlot_fft_forward(self._h, _p(x), _p(out), C.c_int(batch)))
+        return out.view(np.complex64)
+
+    def inverse(self, X, batch=1, out_len=None):
+        X = np.ascontiguousarray(X, np.complex64)
+        out = np.zeros(out_len if out_len is not None else batch * self.so * self.nfft, np.float32)
+        _check(lib().crlot_fft_inverse(self._h, _p(X.view(np.float32)), _p(out), C.c_int(batch)))
+        return out
+
+
+# ---- drop-in OLAAccumulator -----------------------------------------------------------------------
+class OlaAccumulator:
+    """dsp::OLAAccumulator with device-resident rings (crlot_ola_*)."""
+
+    def __init__(self, frame_size, hop_size, channels=1, sample_rate=48000, eps=1e-8, apply_window_inside=True,
+                 shadow_ring=False, device=0):
+        self._h = C.c_void_p()
+        self.N, self.H, self.C = frame_size, hop_size, channels
+        _check(lib().crlot_ola_create(C.c_int(sample_rate), C.c_size_t(frame_size), C.c_size_t(hop_size),
+                                      C.c_size_t(channels), C.c_float(eps), C.c_int(int(apply_window_inside)),
+                                      C.c_int(int(shadow_ring)), C.c_int(device), C.byref(self._h)))
+
+    def __del__(self):
+        try:
+            if self._h.value:
+                lib().crlot_ola_destroy(self._h)
+        except Exception:
+            pass
+
+    def set_window(self, w, wlen=None):
+        w = _f32(w)
+        _check(lib().crlot_ola_set_window(self._h, _p(w), C.c_int(w.size if wlen is None else wlen)))
+
+    def add_frame_SoA(self, ch_frames, window, start_sample, start_off, size, gain):
+        arrs = [_f32(a) for a in ch_frames]
+        ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+        w = _f32(window)
+        _check(lib().crlot_ola_add_frame_soa(self._h, ptrs, _p(w), C.c_size_t(start_sample), C.c_size_t(start_off),
+                                             C.c_size_t(size), C.c_float(gain)))
+
+    def push_frame_AoS(self, interleaved, window, start_sample, start_off, size, gain):
+        x = _f32(interleaved)
+        w = _f32(window)
+        _check(lib().crlot_ola_push_frame_aos(self._h, _p(x), _p(w), C.c_size_t(start_sample), C.c_size_t(start_off),
+                                              C.c_size_t(size), C.c_float(gain)))
+
+    def produce(self, n):
+        outs = [np.zeros(n, np.float32) for _ in range(self.C)]
+        ptrs = (C.c_void_p * self.C)(*[a.ctypes.data for a in outs])
+        got = C.c_size_t(0)
+        _check(lib().crlot_ola_produce(self._h, ptrs, C.c_size_t(n), C.byref(got)))
+        return [a[: got.value] for a in outs], got.value
+
+    def flush(self):
+        _check(lib().crlot_ola_flush(self._h))
+
+    def reset(self):
+        _check(lib().crlot_ola_reset(self._h))
+
+    def produced_samples(self):
+        return int(lib().crlot_ola_get(self._h, 0))
+
+    def read_pos(self):
+        return int(lib().crlot_ola_get(self._h, 1))
+
+    def ring_size(self):
+        return int(lib().crlot_ola_get(self._h, 2))
+
+    def has_window(self):
+        return bool(lib().crlot_ola_get(self._h, 3))
+
+    def meter_peak(self):
+        return float(lib().crlot_ola_meter_peak(self._h))

@@ -1,0 +1,99 @@
+// aux_kernels.cu -- small helpers around the three hot kernels: the counter-based synthetic
+// signal generator (same hash as oracle/crlot_oracle.c, so any slice of a 2^33-sample signal
+// can be regenerated on either side), and the device-resident ring operations that back the
+// OLAAccumulator facade and the streaming (config 5) path.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace crlot {
+
+namespace {
+
+__device__ __forceinline__ float synth_one(unsigned long long seed, unsigned long long ch, unsigned long long i) {
+  unsigned long long z = seed + ch * 0xD1B54A32D192ED03ull + i * 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  const unsigned int m = static_cast<unsigned int>(z >> 40);
+  return __fadd_rn(__fmul_rn(static_cast<float>(m), 1.0f / 8388608.0f), -1.0f);
+}
+
+__global__ void synth_uniform_kernel(float* out, long long chan_stride, long long n, unsigned long long seed,
+                                     unsigned long long channel0, unsigned long long i0) {
+  const int c = blockIdx.y;
+  float* dst = out + static_cast<long long>(c) * chan_stride;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = synth_one(seed, channel0 + c, i0 + static_cast<unsigned long long>(i));
+}
+
+// acc[(start+j) % ring_len] = fma( fl(frame[j]*w[j]) , gain, acc[...] )   (axpy_windowed), or
+// fma(frame[j], gain, acc) without a window (axpy).  One thread per (channel, j): no two threads
+// touch the same ring cell within a launch (n <= ring_len), so no atomics.
+__global__ void ring_axpy_kernel(float* ring, long long ring_len, const float* frames, long long frame_chan_stride,
+                                 const float* window, float gain, long long start, int n) {
+  const int c = blockIdx.y;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  float* acc = ring + static_cast<long long>(c) * ring_len + (start + j) % ring_len;
+  float f = frames[static_cast<long long>(c) * frame_chan_stride + j];
+  if (window) f = __fmul_rn(f, window[j]);
+  *acc = __fmaf_rn(f, gain, *acc);
+}
+
+// out[j] = acc[p] / max(norm[p], eps); acc[p] = 0; p = (read_pos + j) % ring_len   (normalize_and_clear)
+__global__ void ring_produce_kernel(float* ring, long long ring_len, const float* norm, float eps, long long read_pos,
+                                    int n, float* out, long long out_chan_stride) {
+  const int c = blockIdx.y;
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const long long pidx = (read_pos + j) % ring_len;
+  float* acc = ring + static_cast<long long>(c) * ring_len + pidx;
+  out[static_cast<long long>(c) * out_chan_stride + j] = __fdiv_rn(*acc, fmaxf(norm[pidx], eps));
+  *acc = 0.0f;
+}
+
+}  // namespace
+
+cudaError_t launch_synth_uniform(float* out, long long chan_stride, int channels, long long n, unsigned long long seed,
+                                 unsigned long long channel0, unsigned long long i0, cudaStream_t st) {
+  if (n <= 0 || channels <= 0) return cudaSuccess;
+  long long blocks = (n + 255) / 256;
+  const long long cap = static_cast<long long>(device_sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  synth_uniform_kernel<<<dim3(static_cast<unsigned>(blocks), channels), 256, 0, st>>>(out, chan_stride, n, seed,
+                                                                                      channel0, i0);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ring_axpy(float* ring, long long ring_len, int channels, const float* frames,
+                             long long frame_chan_stride, const float* window, float gain, long long start, int n,
+                             cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  ring_axpy_kernel<<<dim3((n + 255) / 256, channels), 256, 0, st>>>(ring, ring_len, frames, frame_chan_stride, window,
+                                                                   gain, start, n);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ring_produce(float* ring, long long ring_len, int channels, const float* norm, float eps,
+                                long long read_pos, int n, float* out, long long out_chan_stride, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  ring_produce_kernel<<<dim3((n + 255) / 256, channels), 256, 0, st>>>(ring, ring_len, norm, eps, read_pos, n, out,
+                                                                      out_chan_stride);
+  return cudaGetLastError();
+}
+
+int device_sm_count() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached = n;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+}  // namespace crlot

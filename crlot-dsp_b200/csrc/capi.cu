@@ -1,0 +1,713 @@
+// capi.cu -- implementation of include/crlot_cuda.h: the C-ABI over the sm_100a kernels.
+// No CPU fallback lives here: every compute entry point launches CUDA kernels or fails.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/crlot_cuda.h"
+#include "kernels.h"
+#include "tables.h"
+
+using namespace crlot;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+int fail_cuda(cudaError_t e, const char* where) {
+  g_err = std::string(where) + ": " + cudaGetErrorString(e);
+  cudaGetLastError();
+  return CRLOT_ERR_CUDA;
+}
+#define CU(call)                                          \
+  do {                                                    \
+    cudaError_t e__ = (call);                             \
+    if (e__ != cudaSuccess) return fail_cuda(e__, #call); \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+bool supported_nfft(int n) { return n == 256 || n == 512 || n == 1024 || n == 2048 || n == 4096; }
+
+template <class T> struct DevArr {
+  T* p = nullptr;
+  size_t n = 0;
+  ~DevArr() { if (p) cudaFree(p); }
+  cudaError_t alloc(size_t count) {
+    if (p) { cudaFree(p); p = nullptr; }
+    n = count;
+    return count ? cudaMalloc(&p, count * sizeof(T)) : cudaSuccess;
+  }
+  cudaError_t upload(const T* h, size_t count) {
+    cudaError_t e = alloc(count);
+    if (e != cudaSuccess) return e;
+    return count ? cudaMemcpy(p, h, count * sizeof(T), cudaMemcpyHostToDevice) : cudaSuccess;
+  }
+};
+
+}  // namespace
+
+struct crlot_buf_s {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  int device = 0;
+  bool owned = false;
+};
+
+// ---------------------------------------------------------------------------------------------
+// host table builders
+// ---------------------------------------------------------------------------------------------
+static int window_make_impl(int type, size_t n, int periodic, int norm, float* out) {
+  if (n == 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Window size must be greater than 0");
+  if (!out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "window output pointer is null");
+  if (type == CRLOT_WIN_BLACKMAN_HARRIS) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Blackman-Harris window not yet implemented");
+  if (type < CRLOT_WIN_HANN || type > CRLOT_WIN_BLACKMAN_HARRIS) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Unknown window type");
+  if (norm < CRLOT_NORM_NONE || norm > CRLOT_NORM_OLA_SUM_WSQ) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Unknown normalization type");
+  const double den = periodic ? static_cast<double>(n) : static_cast<double>(n - 1);
+  const double step = n > 1 ? 2.0 * M_PI / den : 0.0;
+  for (size_t i = 0; i < n; ++i) {
+    const double ang = step * static_cast<double>(i);
+    double v = 1.0;
+    if (n > 1) {
+      switch (type) {
+        case CRLOT_WIN_HANN: v = 0.5 * (1.0 - std::cos(ang)); break;
+        case CRLOT_WIN_HAMMING: v = 0.54 - 0.46 * std::cos(ang); break;
+        case CRLOT_WIN_BLACKMAN: { const double c1 = std::cos(ang), c2 = std::cos(2.0 * ang); v = 0.42 - 0.5 * c1 + 0.08 * c2; break; }
+        default: v = 1.0; break;
+      }
+    }
+    out[i] = static_cast<float>(v);
+  }
+  if (norm != CRLOT_NORM_NONE) {
+    double acc = 0.0;
+    if (norm == CRLOT_NORM_SUM_TO_ONE) for (size_t i = 0; i < n; ++i) acc += static_cast<double>(out[i]);
+    else for (size_t i = 0; i < n; ++i) acc += static_cast<double>(out[i]) * static_cast<double>(out[i]);
+    if (acc > 0.0) {
+      const float k = static_cast<float>(norm == CRLOT_NORM_SUM_TO_ONE ? 1.0 / acc : 1.0 / std::sqrt(acc));
+      for (size_t i = 0; i < n; ++i) out[i] *= k;
+    }
+  }
+  return CRLOT_OK;
+}
+
+static void norm_linear_impl(float* norm, const float* w, long long ring, long long N, long long H) {
+  std::fill(norm, norm + ring, 0.0f);
+  if (ring <= 0 || N <= 0 || H <= 0) return;
+  const long long k_first = -((N + H - 1) / H), k_last = (ring + N - 1 + H - 1) / H;
+  for (long long k = k_first; k <= k_last; ++k) {
+    long long s = (k * H) % ring;
+    if (s < 0) s += ring;
+    const long long head = std::min(N, ring - s);
+    for (long long i = 0; i < head; ++i) norm[s + i] += w[i];      // fp32 adds, k then i ascending
+    for (long long i = head; i < N; ++i) norm[i - head] += w[i];   // second span starts at ring[0]
+  }
+}
+
+static void envelope_impl(float* norm, const float* w, size_t ring, size_t N, size_t H, int inside, float eps) {
+  if (!w || !inside) {
+    std::fill(norm, norm + ring, 1.0f);
+  } else if (H == N) {
+    for (size_t i = 0; i < ring; ++i) norm[i] = std::max(w[i % N], eps);
+  } else {
+    norm_linear_impl(norm, w, static_cast<long long>(ring), static_cast<long long>(N), static_cast<long long>(H));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// plan
+// ---------------------------------------------------------------------------------------------
+struct HostSlot {
+  cudaStream_t stream = nullptr;
+  DevArr<float> in, frames, out;
+  DevArr<cpx> spec;
+};
+
+struct crlot_plan_s {
+  crlot_stft_desc d{};
+  int bins = 0;
+  size_t ring_len = 0;
+  bool syn_active = false;
+  DevArr<float> win_a, win_s, env;
+  DevArr<cpx> tw1, st, su, pre;
+  DevArr<unsigned int> counter;
+  std::vector<float> env_host;
+  HostSlot slot[2];
+  long long slot_frames = 0;   // capacity of the host-path workspace, in frames
+};
+
+static cudaError_t upload_cpx(DevArr<cpx>& dst, const std::vector<float>& v) {
+  return dst.upload(reinterpret_cast<const cpx*>(v.data()), v.size() / 2);
+}
+
+extern "C" {
+
+int crlot_cuda_abi_version(void) { return CRLOT_ABI_VERSION; }
+const char* crlot_cuda_last_error(void) { return g_err.c_str(); }
+
+int crlot_cuda_device_count(int* count) {
+  if (!count) return fail(CRLOT_ERR_INVALID_ARGUMENT, "count is null");
+  CU(cudaGetDeviceCount(count));
+  return CRLOT_OK;
+}
+int crlot_cuda_stream_sync(int device, void* stream) {
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
+  CU(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+// ---- buffers --------------------------------------------------------------------------------
+int crlot_buf_create(size_t bytes, int device, crlot_buf_t* out) {
+  if (!out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "out is null");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
+  auto* b = new (std::nothrow) crlot_buf_s;
+  if (!b) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
+  if (bytes) {
+    cudaError_t e = cudaMalloc(&b->ptr, bytes);
+    if (e != cudaSuccess) { delete b; fail_cuda(e, "cudaMalloc"); return e == cudaErrorMemoryAllocation ? CRLOT_ERR_ALLOC : CRLOT_ERR_CUDA; }
+  }
+  b->bytes = bytes; b->device = device; b->owned = true;
+  *out = b;
+  return CRLOT_OK;
+}
+int crlot_buf_wrap(void* device_ptr, size_t bytes, int device, crlot_buf_t* out) {
+  if (!out || (!device_ptr && bytes)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  auto* b = new (std::nothrow) crlot_buf_s;
+  if (!b) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
+  b->ptr = device_ptr; b->bytes = bytes; b->device = device; b->owned = false;
+  *out = b;
+  return CRLOT_OK;
+}
+int crlot_buf_destroy(crlot_buf_t buf) {
+  if (!buf) return CRLOT_OK;
+  if (buf->owned && buf->ptr) { DeviceGuard g(buf->device); cudaFree(buf->ptr); }
+  delete buf;
+  return CRLOT_OK;
+}
+int crlot_buf_upload(crlot_buf_t buf, size_t off, const void* host, size_t bytes, void* stream) {
+  if (!buf || (!host && bytes)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (off + bytes > buf->bytes) return fail(CRLOT_ERR_INVALID_ARGUMENT, "upload exceeds buffer");
+  DeviceGuard g(buf->device);
+  CU(cudaMemcpyAsync(static_cast<char*>(buf->ptr) + off, host, bytes, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+int crlot_buf_download(crlot_buf_t buf, size_t off, void* host, size_t bytes, void* stream) {
+  if (!buf || (!host && bytes)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (off + bytes > buf->bytes) return fail(CRLOT_ERR_INVALID_ARGUMENT, "download exceeds buffer");
+  DeviceGuard g(buf->device);
+  CU(cudaMemcpyAsync(host, static_cast<const char*>(buf->ptr) + off, bytes, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+int crlot_buf_zero(crlot_buf_t buf, size_t off, size_t bytes, void* stream) {
+  if (!buf) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null buffer");
+  if (off + bytes > buf->bytes) return fail(CRLOT_ERR_INVALID_ARGUMENT, "range exceeds buffer");
+  DeviceGuard g(buf->device);
+  CU(cudaMemsetAsync(static_cast<char*>(buf->ptr) + off, 0, bytes, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+void* crlot_buf_device_ptr(crlot_buf_t buf) { return buf ? buf->ptr : nullptr; }
+size_t crlot_buf_bytes(crlot_buf_t buf) { return buf ? buf->bytes : 0; }
+int crlot_host_alloc(size_t bytes, void** out) {
+  if (!out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "out is null");
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+  if (e != cudaSuccess) { fail_cuda(e, "cudaHostAlloc"); return CRLOT_ERR_ALLOC; }
+  return CRLOT_OK;
+}
+int crlot_host_free(void* p) {
+  if (p) CU(cudaFreeHost(p));
+  return CRLOT_OK;
+}
+
+// ---- tables ---------------------------------------------------------------------------------
+int crlot_window_make(int type, size_t n, int periodic, int norm, float* out) {
+  return window_make_impl(type, n, periodic, norm, out);
+}
+size_t crlot_ola_ring_len(size_t frame, size_t hop) {
+  if (hop == 0) return 0;
+  return ((frame + hop - 1) / hop + 20) * hop;
+}
+int crlot_build_norm_linear(float* norm, const float* window, size_t ring_len, size_t frame, size_t hop) {
+  if (!norm || (!window && frame)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  norm_linear_impl(norm, window, static_cast<long long>(ring_len), static_cast<long long>(frame), static_cast<long long>(hop));
+  return CRLOT_OK;
+}
+int crlot_ola_envelope(float* norm, const float* w, size_t ring_len, size_t frame, size_t hop, int inside, float eps) {
+  if (!norm) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  envelope_impl(norm, w, ring_len, frame, hop, inside, eps);
+  return CRLOT_OK;
+}
+long long crlot_frame_count(long long len, int frame, int hop, int mode) {
+  if (len <= 0 || frame <= 0 || hop <= 0) return 0;
+  if (mode == CRLOT_DROP) return len < frame ? 0 : (len - frame) / hop + 1;
+  return (len + hop - 1) / hop;
+}
+
+// ---- plan -----------------------------------------------------------------------------------
+int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
+  if (!desc || !out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (desc->nfft <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Frame size must be greater than 0");
+  if (desc->hop <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Hop size must be greater than 0");
+  if (!(desc->eps > 0.0f)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Invalid OLA configuration");
+  if (desc->boundary_mode != CRLOT_ZERO_PAD && desc->boundary_mode != CRLOT_DROP) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad boundary mode");
+  if (!supported_nfft(desc->nfft)) return fail(CRLOT_ERR_UNSUPPORTED, "nfft must be 256, 512, 1024, 2048 or 4096 on the GPU path");
+  if (desc->hop % 4 != 0 || desc->hop > desc->nfft) return fail(CRLOT_ERR_UNSUPPORTED, "hop must be a multiple of 4 and <= nfft on the GPU path");
+  DeviceGuard g(desc->device);
+  if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
+  std::unique_ptr<crlot_plan_s> p(new (std::nothrow) crlot_plan_s);
+  if (!p) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
+  p->d = *desc;
+  p->bins = desc->nfft / 2 + 1;
+  const int N = desc->nfft;
+  // analysis window (ones = none)
+  std::vector<float> wa(N, 1.0f);
+  if (desc->analysis_window) std::copy(desc->analysis_window, desc->analysis_window + N, wa.begin());
+  CU(p->win_a.upload(wa.data(), N));
+  // synthesis window policy, ref: OLAAccumulator.cc:82-83
+  const float* ws = desc->apply_window_inside ? desc->ola_window : desc->push_window;
+  p->syn_active = ws != nullptr;
+  if (ws) CU(p->win_s.upload(ws, N));
+  // envelope
+  if (desc->envelope) {
+    if (desc->envelope_len == 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "envelope_len is 0");
+    p->ring_len = desc->envelope_len;
+    p->env_host.assign(desc->envelope, desc->envelope + desc->envelope_len);
+  } else {
+    p->ring_len = crlot_ola_ring_len(N, desc->hop);
+    p->env_host.resize(p->ring_len);
+    envelope_impl(p->env_host.data(), desc->ola_window, p->ring_len, N, desc->hop, desc->apply_window_inside, desc->eps);
+  }
+  CU(p->env.upload(p->env_host.data(), p->env_host.size()));
+  const FftTables T = make_fft_tables(N);
+  CU(upload_cpx(p->tw1, T.tw1));
+  CU(upload_cpx(p->st, T.st));
+  CU(upload_cpx(p->su, T.su));
+  if (!T.pre.empty()) CU(upload_cpx(p->pre, T.pre));
+  CU(p->counter.alloc(4));
+  p->d.analysis_window = p->d.ola_window = p->d.push_window = p->d.envelope = nullptr;  // not retained
+  *out = p.release();
+  return CRLOT_OK;
+}
+
+int crlot_stft_plan_destroy(crlot_plan_t plan) {
+  if (!plan) return CRLOT_OK;
+  DeviceGuard g(plan->d.device);
+  for (auto& s : plan->slot) if (s.stream) cudaStreamDestroy(s.stream);
+  delete plan;
+  return CRLOT_OK;
+}
+int crlot_stft_plan_info(crlot_plan_t plan, crlot_plan_info* info) {
+  if (!plan || !info) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  info->nfft = plan->d.nfft; info->hop = plan->d.hop; info->bins = plan->bins;
+  info->ring_len = plan->ring_len; info->synthesis_window_active = plan->syn_active; info->device = plan->d.device;
+  return CRLOT_OK;
+}
+int crlot_stft_plan_envelope(crlot_plan_t plan, float* host_out) {
+  if (!plan || !host_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  std::copy(plan->env_host.begin(), plan->env_host.end(), host_out);
+  return CRLOT_OK;
+}
+
+// ---- execute --------------------------------------------------------------------------------
+int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
+                       long long n_frames, void* d_spec, void* stream) {
+  if (!plan || !d_signal || !d_spec) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || n_frames < 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (chan_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_signal) % 16 != 0 || reinterpret_cast<uintptr_t>(d_spec) % 8 != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "signal must be 16-byte aligned with chan_stride a multiple of 4 floats");
+  DeviceGuard g(plan->d.device);
+  K1Params k{};
+  k.sig = d_signal; k.chan_stride = chan_stride; k.len = len; k.channels = channels; k.frames = n_frames;
+  k.nfft = plan->d.nfft; k.hop = plan->d.hop;
+  k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
+  k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.st = plan->st.p; k.pre = plan->pre.p;
+  k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->d.scrub;
+  CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+int crlot_istft_execute(crlot_plan_t plan, const void* d_spec, long long rows, float* d_frames, int fuse_win, void* stream) {
+  if (!plan || !d_spec || !d_frames) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (rows < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (reinterpret_cast<uintptr_t>(d_spec) % 8 != 0 || reinterpret_cast<uintptr_t>(d_frames) % 8 != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "buffers must be 8-byte aligned");
+  DeviceGuard g(plan->d.device);
+  K2Params k{};
+  k.spec = static_cast<const cpx*>(d_spec); k.rows = rows; k.nfft = plan->d.nfft; k.frames = d_frames;
+  k.window = (fuse_win && plan->syn_active) ? plan->win_s.p : nullptr;
+  k.tw1 = plan->tw1.p; k.su = plan->su.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
+  CU(launch_istft_inv(k, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+int crlot_ola_accumulate(crlot_plan_t plan, const float* d_frames, long long frames_chan_rows, long long frames_per_chan,
+                         int channels, int prewindowed, long long t_offset, long long frame_t0, float* d_out,
+                         long long out_chan_stride, long long n_out, void* stream) {
+  if (!plan || !d_frames || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || frames_per_chan < 0 || n_out < 0 || t_offset < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  DeviceGuard g(plan->d.device);
+  K3Params k{};
+  k.frames = d_frames; k.frames_chan_rows = frames_chan_rows; k.frames_per_chan = frames_per_chan; k.channels = channels;
+  k.nfft = plan->d.nfft; k.hop = plan->d.hop;
+  k.window = (!prewindowed && plan->syn_active) ? plan->win_s.p : nullptr;
+  k.gain = plan->d.gain; k.eps = plan->d.eps; k.norm = plan->env.p; k.ring_len = static_cast<long long>(plan->ring_len);
+  k.t_offset = t_offset; k.frame_t0 = frame_t0; k.out = d_out; k.out_chan_stride = out_chan_stride; k.n_out = n_out;
+  CU(launch_ola_gather(k, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
+                            void* d_spec, float* d_frames, float* d_out, long long out_chan_stride, void* stream) {
+  if (!plan) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  const long long F = crlot_frame_count(len, plan->d.nfft, plan->d.hop, plan->d.boundary_mode);
+  if (F == 0) return CRLOT_OK;
+  int rc = crlot_stft_execute(plan, d_signal, chan_stride, len, channels, F, d_spec, stream);
+  if (rc) return rc;
+  rc = crlot_istft_execute(plan, d_spec, F * channels, d_frames, 1, stream);
+  if (rc) return rc;
+  const long long n_out = (F - 1) * plan->d.hop + plan->d.nfft;
+  return crlot_ola_accumulate(plan, d_frames, F, F, channels, 1, 0, 0, d_out, out_chan_stride, n_out, stream);
+}
+
+// Host-buffer round trip: time slabs through two workspace slots, one stream each, so the
+// H2D copy of slab i+1 and the D2H copy of slab i-1 overlap the kernels of slab i.
+int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_stride, long long len, int channels,
+                         float* h_out, long long out_chan_stride, long long* n_out_per_chan) {
+  if (!plan || !h_in || !h_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  const int N = plan->d.nfft, H = plan->d.hop;
+  const long long F = crlot_frame_count(len, N, H, plan->d.boundary_mode);
+  const long long n_out = F > 0 ? (F - 1) * H + N : 0;
+  if (n_out_per_chan) *n_out_per_chan = n_out;
+  if (F == 0) return CRLOT_OK;
+  DeviceGuard g(plan->d.device);
+  // slab = `slab_hops` hops of output; its frames are the ones overlapping that range
+  const long long overlap = (N + H - 1) / H - 1;
+  const long long slab_hops = std::min<long long>(std::max<long long>((1ll << 24) / H, 4 * (overlap + 1)), F + overlap);
+  const long long slab_frames = slab_hops + overlap;
+  if (plan->slot_frames < slab_frames) {
+    for (auto& s : plan->slot) {
+      if (!s.stream) CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+      CU(s.in.alloc(static_cast<size_t>((slab_frames - 1) * H + N)));
+      CU(s.spec.alloc(static_cast<size_t>(slab_frames) * plan->bins));
+      CU(s.frames.alloc(static_cast<size_t>(slab_frames) * N));
+      CU(s.out.alloc(static_cast<size_t>(slab_hops) * H + N));
+    }
+    plan->slot_frames = slab_frames;
+  }
+  // separate work counters per slot are not needed: kernel 1 of a slot resets the shared counter
+  // on its own stream, so give each slot its own counter word.
+  int it = 0;
+  for (int c = 0; c < channels; ++c) {
+    const float* xin = h_in + static_cast<long long>(c) * chan_stride;
+    float* yout = h_out + static_cast<long long>(c) * out_chan_stride;
+    for (long long t0 = 0; t0 < n_out; t0 += slab_hops * H, ++it) {
+      HostSlot& s = plan->slot[it & 1];
+      const long long t1 = std::min(n_out, t0 + slab_hops * H);
+      long long k_lo = t0 - N + 1 <= 0 ? 0 : (t0 - N + 1 + H - 1) / H;
+      long long k_hi = std::min(F - 1, (t1 - 1) / H);
+      const long long nf = k_hi - k_lo + 1;
+      const long long s0 = k_lo * H;                                   // first input sample of the slab
+      const long long s1 = std::min(len, k_hi * H + N);                // one past the last that exists
+      CU(cudaMemcpyAsync(s.in.p, xin + s0, static_cast<size_t>(s1 - s0) * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+      K1Params k1{};
+      k1.sig = s.in.p; k1.chan_stride = 0; k1.len = s1 - s0; k1.channels = 1; k1.frames = nf; k1.nfft = N; k1.hop = H;
+      k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.st = plan->st.p;
+      k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->d.scrub;
+      CU(launch_stft_fwd(k1, s.stream));
+      K2Params k2{};
+      k2.spec = s.spec.p; k2.rows = nf; k2.nfft = N; k2.frames = s.frames.p;
+      k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.su = plan->su.p; k2.pre = plan->pre.p;
+      k2.scrub = plan->d.scrub;
+      CU(launch_istft_inv(k2, s.stream));
+      K3Params k3{};
+      k3.frames = s.frames.p; k3.frames_chan_rows = nf; k3.frames_per_chan = nf; k3.channels = 1; k3.nfft = N; k3.hop = H;
+      k3.window = nullptr; k3.gain = plan->d.gain; k3.eps = plan->d.eps; k3.norm = plan->env.p;
+      k3.ring_len = static_cast<long long>(plan->ring_len); k3.t_offset = t0; k3.frame_t0 = s0 - t0; k3.out = s.out.p;
+      k3.out_chan_stride = 0; k3.n_out = t1 - t0;
+      CU(launch_ola_gather(k3, s.stream));
+      CU(cudaMemcpyAsync(yout + t0, s.out.p, static_cast<size_t>(t1 - t0) * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+    }
+  }
+  for (auto& s : plan->slot) if (s.stream) CU(cudaStreamSynchronize(s.stream));
+  return CRLOT_OK;
+}
+
+int crlot_synth_uniform(float* d_out, long long chan_stride, int channels, long long n, unsigned long long seed,
+                        unsigned long long channel0, unsigned long long i0, int device, void* stream) {
+  if (!d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  DeviceGuard g(device);
+  CU(launch_synth_uniform(d_out, chan_stride, channels, n, seed, channel0, i0, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// drop-in FFT plan (IFftPlan over host pointers)
+// ---------------------------------------------------------------------------------------------
+struct crlot_fft_s {
+  int nfft = 0, batch = 0, si = 0, so = 0, device = 0;
+  crlot_plan_t plan = nullptr;
+  DevArr<float> d_time;
+  DevArr<cpx> d_freq;
+  std::vector<float> h_time;
+  std::vector<float> h_freq;
+};
+
+extern "C" {
+
+int crlot_fft_plan_create(int nfft, int in_place, int batch, int stride_in, int stride_out, int device, crlot_fft_t* out) {
+  if (!out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  // same order of checks and messages as the reference adapter (kissfft_adapter.cc:13-39)
+  if (batch < 1 || batch > 16) return fail(CRLOT_ERR_RUNTIME, "Batch size must be between 1 and 16");
+  if (stride_in < 1 || stride_out < 1) return fail(CRLOT_ERR_RUNTIME, "Stride must be at least 1");
+  if (in_place) return fail(CRLOT_ERR_RUNTIME, "In-place FFT is not yet supported");
+  if (nfft % 2 != 0) return fail(CRLOT_ERR_RUNTIME, "FFT size must be even for real FFT");
+  if (!supported_nfft(nfft)) return fail(CRLOT_ERR_UNSUPPORTED, "nfft must be 256, 512, 1024, 2048 or 4096 on the GPU path");
+  std::unique_ptr<crlot_fft_s> f(new (std::nothrow) crlot_fft_s);
+  if (!f) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
+  f->nfft = nfft; f->batch = batch; f->si = stride_in; f->so = stride_out; f->device = device;
+  crlot_stft_desc d{};
+  d.nfft = nfft; d.hop = nfft; d.boundary_mode = CRLOT_DROP; d.apply_window_inside = 0; d.gain = 1.0f; d.eps = 1e-8f;
+  d.scrub = 1; d.device = device;
+  int rc = crlot_stft_plan_create(&d, &f->plan);
+  if (rc) return rc;
+  DeviceGuard g(device);
+  cudaError_t e = f->d_time.alloc(static_cast<size_t>(batch) * nfft);
+  if (e == cudaSuccess) e = f->d_freq.alloc(static_cast<size_t>(batch) * (nfft / 2 + 1));
+  if (e != cudaSuccess) { crlot_stft_plan_destroy(f->plan); return fail_cuda(e, "cudaMalloc"); }
+  f->h_time.resize(static_cast<size_t>(batch) * nfft);
+  f->h_freq.resize(static_cast<size_t>(batch) * (nfft / 2 + 1) * 2);
+  *out = f.release();
+  return CRLOT_OK;
+}
+int crlot_fft_plan_destroy(crlot_fft_t f) {
+  if (!f) return CRLOT_OK;
+  crlot_stft_plan_destroy(f->plan);
+  { DeviceGuard g(f->device); delete f; }
+  return CRLOT_OK;
+}
+// forward: batch b reads in + b*si*n with element stride si; writes out + b*so*(n/2+1) with
+// element stride so (ref: kissfft_adapter.cc:97-98,103,118)
+int crlot_fft_forward(crlot_fft_t f, const float* h_in, float* h_out_ri, int batch) {
+  if (!f || !h_in || !h_out_ri) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (batch < 1 || batch > f->batch) return fail(CRLOT_ERR_RUNTIME, "Invalid batch size");
+  const int n = f->nfft, nb = n / 2 + 1;
+  for (int b = 0; b < batch; ++b)
+    for (int i = 0; i < n; ++i) f->h_time[static_cast<size_t>(b) * n + i] = h_in[static_cast<long long>(b) * f->si * n + static_cast<long long>(i) * f->si];
+  DeviceGuard g(f->device);
+  CU(cudaMemcpy(f->d_time.p, f->h_time.data(), sizeof(float) * batch * n, cudaMemcpyHostToDevice));
+  int rc = crlot_stft_execute(f->plan, f->d_time.p, 0, static_cast<long long>(batch) * n, 1, batch, f->d_freq.p, nullptr);
+  if (rc) return rc;
+  CU(cudaMemcpy(f->h_freq.data(), f->d_freq.p, sizeof(float) * 2 * batch * nb, cudaMemcpyDeviceToHost));
+  for (int b = 0; b < batch; ++b)
+    for (int i = 0; i < nb; ++i) {
+      const long long o = 2 * (static_cast<long long>(b) * f->so * nb + static_cast<long long>(i) * f->so);
+      h_out_ri[o] = f->h_freq[2 * (static_cast<size_t>(b) * nb + i)];
+      h_out_ri[o + 1] = f->h_freq[2 * (static_cast<size_t>(b) * nb + i) + 1];
+    }
+  return CRLOT_OK;
+}
+// inverse: batch b reads in + b*si*(n/2+1) with element stride si; writes out + b*so*n with
+// element stride so (ref: kissfft_adapter.cc:139-147,154-165)
+int crlot_fft_inverse(crlot_fft_t f, const float* h_in_ri, float* h_out, int batch) {
+  if (!f || !h_in_ri || !h_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (batch < 1 || batch > f->batch) return fail(CRLOT_ERR_RUNTIME, "Invalid batch size");
+  const int n = f->nfft, nb = n / 2 + 1;
+  for (int b = 0; b < batch; ++b)
+    for (int i = 0; i < nb; ++i) {
+      const long long s = 2 * (static_cast<long long>(b) * f->si * nb + static_cast<long long>(i) * f->si);
+      f->h_freq[2 * (static_cast<size_t>(b) * nb + i)] = h_in_ri[s];
+      f->h_freq[2 * (static_cast<size_t>(b) * nb + i) + 1] = h_in_ri[s + 1];
+    }
+  DeviceGuard g(f->device);
+  CU(cudaMemcpy(f->d_freq.p, f->h_freq.data(), sizeof(float) * 2 * batch * nb, cudaMemcpyHostToDevice));
+  int rc = crlot_istft_execute(f->plan, f->d_freq.p, batch, f->d_time.p, 0, nullptr);
+  if (rc) return rc;
+  CU(cudaMemcpy(f->h_time.data(), f->d_time.p, sizeof(float) * batch * n, cudaMemcpyDeviceToHost));
+  for (int b = 0; b < batch; ++b)
+    for (int i = 0; i < n; ++i) h_out[static_cast<long long>(b) * f->so * n + static_cast<long long>(i) * f->so] = f->h_time[static_cast<size_t>(b) * n + i];
+  return CRLOT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// drop-in OLAAccumulator state: device rings, reference bookkeeping on the host
+// ---------------------------------------------------------------------------------------------
+struct crlot_ola_s {
+  int sample_rate = 0, device = 0;
+  size_t N = 0, H = 0, C = 0, ring_len = 0;
+  float eps = 1e-8f;
+  bool inside = false, shadow = false, has_window = false;
+  size_t read_pos = 0, produced = 0;
+  float peak = 0.0f;
+  DevArr<float> ring, norm, win, call_win, stage;
+  std::vector<float> h_stage, h_norm, h_win;
+  void rebuild_norm() {   // ref: OLAAccumulator::initialize_normalization
+    h_norm.resize(ring_len);
+    envelope_impl(h_norm.data(), has_window ? h_win.data() : nullptr, ring_len, N, H, inside, eps);
+  }
+};
+
+extern "C" {
+
+int crlot_ola_create(int sample_rate, size_t frame_size, size_t hop_size, size_t channels, float eps,
+                     int apply_window_inside, int shadow_ring, int device, crlot_ola_t* out) {
+  if (!out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (!(sample_rate > 0 && frame_size > 0 && hop_size > 0 && channels > 0 && eps > 0.0f))
+    return fail(CRLOT_ERR_INVALID_ARGUMENT, "Invalid OLA configuration");
+  std::unique_ptr<crlot_ola_s> o(new (std::nothrow) crlot_ola_s);
+  if (!o) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
+  o->sample_rate = sample_rate; o->device = device; o->N = frame_size; o->H = hop_size; o->C = channels;
+  o->eps = eps; o->inside = apply_window_inside != 0; o->shadow = shadow_ring != 0;
+  o->ring_len = crlot_ola_ring_len(frame_size, hop_size);
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
+  CU(o->ring.alloc(o->ring_len * channels));
+  CU(cudaMemset(o->ring.p, 0, o->ring_len * channels * sizeof(float)));
+  o->rebuild_norm();
+  CU(o->norm.upload(o->h_norm.data(), o->ring_len));
+  CU(o->win.alloc(frame_size));
+  CU(o->call_win.alloc(frame_size));
+  CU(o->stage.alloc(std::max(o->ring_len, frame_size) * channels));
+  o->h_stage.resize(std::max(o->ring_len, frame_size) * channels);
+  *out = o.release();
+  return CRLOT_OK;
+}
+int crlot_ola_destroy(crlot_ola_t o) {
+  if (!o) return CRLOT_OK;
+  { DeviceGuard g(o->device); delete o; }
+  return CRLOT_OK;
+}
+int crlot_ola_set_window(crlot_ola_t o, const float* w, int wlen) {
+  if (!o) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (!w) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Window pointer cannot be null");
+  if (wlen != static_cast<int>(o->N)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Window size must match frame size");
+  DeviceGuard g(o->device);
+  o->h_win.assign(w, w + wlen);
+  o->has_window = true;
+  CU(cudaMemcpy(o->win.p, w, sizeof(float) * wlen, cudaMemcpyHostToDevice));
+  o->rebuild_norm();
+  CU(cudaMemcpy(o->norm.p, o->h_norm.data(), sizeof(float) * o->ring_len, cudaMemcpyHostToDevice));
+  return CRLOT_OK;
+}
+
+static int ola_add_staged(crlot_ola_t o, const float* window, size_t start, size_t off, size_t size, float gain) {
+  // h_stage holds [C][size] planar samples already offset by `off`
+  const bool use = o->inside ? o->has_window : (window != nullptr);
+  const float* dwin = nullptr;
+  if (use) {
+    if (o->inside) dwin = o->win.p + off;
+    else {
+      CU(cudaMemcpy(o->call_win.p, window + off, sizeof(float) * size, cudaMemcpyHostToDevice));
+      dwin = o->call_win.p;
+    }
+  }
+  const size_t n = std::min(size, o->ring_len);    // RingBuffer::split clamps to capacity
+  CU(cudaMemcpy(o->stage.p, o->h_stage.data(), sizeof(float) * size * o->C, cudaMemcpyHostToDevice));
+  CU(launch_ring_axpy(o->ring.p, static_cast<long long>(o->ring_len), static_cast<int>(o->C), o->stage.p,
+                      static_cast<long long>(size), dwin, gain, static_cast<long long>(start % o->ring_len),
+                      static_cast<int>(n), nullptr));
+  CU(cudaStreamSynchronize(nullptr));
+  o->produced = std::max(o->produced, start + size);
+  return CRLOT_OK;
+}
+
+int crlot_ola_add_frame_soa(crlot_ola_t o, const float* const* ch_frames, const float* window, size_t start_sample,
+                            size_t start_off, size_t size, float gain) {
+  if (!o) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (!ch_frames) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Channel frames pointer cannot be null");
+  if (size == 0 || start_off >= o->N) return CRLOT_OK;
+  if (start_off + size > o->N) size = o->N - start_off;
+  for (size_t c = 0; c < o->C; ++c) {
+    if (!ch_frames[c]) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Channel frame pointer cannot be null");
+    std::copy(ch_frames[c] + start_off, ch_frames[c] + start_off + size, o->h_stage.begin() + c * size);
+  }
+  DeviceGuard g(o->device);
+  return ola_add_staged(o, window, start_sample, start_off, size, gain);
+}
+int crlot_ola_push_frame_aos(crlot_ola_t o, const float* interleaved, const float* window, size_t start_sample,
+                             size_t start_off, size_t size, float gain) {
+  if (!o) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (!interleaved) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Interleaved input pointer cannot be null");
+  if (size == 0 || start_off >= o->N) return CRLOT_OK;
+  if (start_off + size > o->N) size = o->N - start_off;
+  const float* src = interleaved + start_off * o->C;      // ref: aos_to_soa.cc:13-17
+  for (size_t c = 0; c < o->C; ++c)
+    for (size_t i = 0; i < size; ++i) o->h_stage[c * size + i] = src[i * o->C + c];
+  DeviceGuard g(o->device);
+  // the reference re-enters add_frame_SoA with start_off = 0 on the de-interleaved scratch, so the
+  // window (stored or per-call) is indexed from 0 there (OLAAccumulator.cc:159)
+  return ola_add_staged(o, window, start_sample, 0, size, gain);
+}
+int crlot_ola_produce(crlot_ola_t o, float* const* ch_out, size_t n, size_t* produced_out) {
+  if (produced_out) *produced_out = 0;
+  if (!o) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (!ch_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Output channel buffer cannot be null");
+  if (n == 0) return CRLOT_OK;
+  for (size_t c = 0; c < o->C; ++c)
+    if (!ch_out[c]) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Output channel buffer cannot be null");
+  const size_t avail = o->produced > o->read_pos ? o->produced - o->read_pos : 0;
+  if (avail == 0) return CRLOT_OK;
+  if (avail < n) n = avail;
+  const size_t m = std::min(n, o->ring_len);
+  DeviceGuard g(o->device);
+  CU(launch_ring_produce(o->ring.p, static_cast<long long>(o->ring_len), static_cast<int>(o->C), o->norm.p, o->eps,
+                         static_cast<long long>(o->read_pos % o->ring_len), static_cast<int>(m), o->stage.p,
+                         static_cast<long long>(m), nullptr));
+  CU(cudaMemcpy(o->h_stage.data(), o->stage.p, sizeof(float) * m * o->C, cudaMemcpyDeviceToHost));
+  for (size_t c = 0; c < o->C; ++c) std::copy(o->h_stage.begin() + c * m, o->h_stage.begin() + (c + 1) * m, ch_out[c]);
+  o->read_pos = (o->read_pos + n) % o->ring_len;
+  for (size_t i = 0; i < m; ++i) o->peak = std::max(o->peak, std::fabs(ch_out[0][i]));
+  if (produced_out) *produced_out = n;
+  return CRLOT_OK;
+}
+int crlot_ola_flush(crlot_ola_t o) {
+  if (!o) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  o->produced = std::max(o->produced, o->read_pos + o->N);
+  return CRLOT_OK;
+}
+int crlot_ola_reset(crlot_ola_t o) {
+  if (!o) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  DeviceGuard g(o->device);
+  CU(cudaMemset(o->ring.p, 0, o->ring_len * o->C * sizeof(float)));
+  o->read_pos = 0; o->produced = 0; o->peak = 0.0f;
+  o->has_window = false; o->h_win.clear();               // reset() also forgets the window (OLAAccumulator.cc:244-246)
+  o->rebuild_norm();
+  CU(cudaMemcpy(o->norm.p, o->h_norm.data(), sizeof(float) * o->ring_len, cudaMemcpyHostToDevice));
+  return CRLOT_OK;
+}
+size_t crlot_ola_get(crlot_ola_t o, int what) {
+  if (!o) return 0;
+  switch (what) {
+    case 0: return o->produced;
+    case 1: return o->read_pos;
+    case 2: return o->ring_len;
+    case 3: return o->has_window ? 1 : 0;
+    default: return 0;
+  }
+}
+float crlot_ola_meter_peak(crlot_ola_t o) { return o ? o->peak : 0.0f; }
+
+}  // extern "C"

@@ -1,0 +1,218 @@
+// k1_stft.cu -- kernel 1: fused frame extraction + analysis window + forward real FFT (sm_100a).
+//
+// Replaces, per frame, the reference chain Framer::pop -> window multiply loop -> KissFftPlan::
+// forward -> kiss_fftr (reference: dsp/frame/framer.cc:128-182, bench/e2e_benchmark.cc:152-156,
+// dsp/fft/backends/kissfft_adapter.cc:83-122, third_party/kissfft/kiss_fftr.c:63-117).
+//
+// Design (see DESIGN.md "Kernel 1"):
+//  * warp-autonomous: every warp is its own streaming pipeline over a run ("chunk") of
+//    consecutive frames of one channel; there is no block-level barrier after start-up.
+//  * the warp keeps the samples of its current G frames in a private shared-memory ring and only
+//    the G*hop NEW samples per step are fetched from global memory, by one 1-D bulk async copy
+//    (cp.async.bulk -> SASS UBLKCP) completing on the warp's own mbarrier.  The copy for step s+1
+//    is issued as soon as step s has been read into registers, so it overlaps the whole FFT.
+//    Every input sample therefore crosses L2->SM once per chunk (not nfft/hop times).
+//  * 1024 complex points per warp-step live in registers (32 per lane); the transform is two
+//    in-register passes with one shared-memory transposition in between (warpfft.cuh), the
+//    real split uses warp shuffles, and the spectrum is stored straight from registers as
+//    contiguous 8-byte-per-lane rows.
+#include "common.cuh"
+#include "kernels.h"
+#include "warpfft.cuh"
+
+namespace crlot {
+
+namespace {
+
+constexpr int kK1Warps = 12;
+
+__host__ __device__ inline int next_pow2(int v) {
+  int r = 1;
+  while (r < v) r <<= 1;
+  return r;
+}
+
+template <int NFFT>
+struct K1Smem {
+  using X = GeoX<NFFT>;
+  static constexpr int kTableBytes = NFFT * 4 + X::C * 8 + X::C * 8;
+  __host__ __device__ static int per_warp_bytes(int rcap) { return rcap * 4 + X::XCPX * 8 + 16; }
+  __host__ __device__ static int total(int rcap, int nwarps) { return kTableBytes + nwarps * per_warp_bytes(rcap); }
+};
+
+// Fill ring positions of absolute samples [abs0, abs0+count) of this channel: the 16-byte
+// multiple that exists in the signal by bulk copy, a ragged remainder by plain loads, zeros
+// beyond the end of the signal.  All lanes call this after a __syncwarp() that follows their
+// last read of the overwritten region.
+__device__ __forceinline__ void ring_fill(float* ring, int mask, const float* sig, long long len, long long abs0,
+                                          int count, uint32_t bar, int lane) {
+  long long avail = len - abs0;
+  if (avail < 0) avail = 0;
+  if (avail > count) avail = count;
+  const int nb = static_cast<int>(avail) & ~3;
+  if (lane == 0) {
+    fence_proxy_async_smem();
+    mbar_arrive_expect_tx(bar, static_cast<uint32_t>(nb) * 4u);
+    if (nb > 0) {
+      const int r0 = static_cast<int>(abs0 & mask);
+      const int first = min(nb, mask + 1 - r0);
+      bulk_g2s(smem_u32(ring + r0), sig + abs0, static_cast<uint32_t>(first) * 4u, bar);
+      if (nb > first) bulk_g2s(smem_u32(ring), sig + abs0 + first, static_cast<uint32_t>(nb - first) * 4u, bar);
+    }
+  }
+  if (nb < count) {   // only at the tail of a channel
+    for (int i = nb + lane; i < count; i += 32) {
+      const long long a = abs0 + i;
+      ring[a & mask] = (a < len) ? __ldg(sig + a) : 0.0f;
+    }
+  }
+}
+
+template <int NFFT, bool SCRUB>
+__global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Params p, const int rcap) {
+  using X = GeoX<NFFT>;
+  constexpr int C = X::C, G = X::G, A = X::A, B = X::B;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* s_win = reinterpret_cast<float*>(smem_raw);
+  cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
+  cpx* s_st = s_tw1 + C;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_st + C) + warp * K1Smem<NFFT>::per_warp_bytes(rcap);
+  float* ring = reinterpret_cast<float*>(wb);
+  cpx* ex = reinterpret_cast<cpx*>(ring + rcap);
+  const uint32_t bar = smem_u32(ex + X::XCPX);
+  const int mask = rcap - 1;
+
+  for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    s_tw1[i] = p.tw1[i];
+    s_st[i] = p.st[i];
+  }
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const int H = p.hop;
+  const int S = (G - 1) * H + NFFT;                     // samples spanned by the G frames of one step
+  const long long frames_per_chunk = static_cast<long long>(p.chunk_steps) * G;
+  const long long chunks_per_chan = (p.frames + frames_per_chunk - 1) / frames_per_chunk;
+  const long long total_chunks = chunks_per_chan * p.channels;
+  const int lp = mirror_lane<B>(lane);
+  uint32_t parity = 0;
+
+  // per-lane constant offsets of the pass-1 items (frame g, point a): float offset g*H + 2a
+  int in_off[X::M1];
+#pragma unroll
+  for (int j = 0; j < X::M1; ++j) {
+    const int i1 = lane + 32 * j;
+    in_off[j] = (i1 / A) * H + 2 * (i1 % A);
+  }
+  const int a_lane = lane % A;
+
+  for (;;) {
+    unsigned long long q = 0;
+    if (lane == 0) q = atomicAdd(p.counter, 1u);
+    q = __shfl_sync(0xffffffffu, q, 0);
+    if (static_cast<long long>(q) >= total_chunks) break;
+    const long long c = q / chunks_per_chan;
+    const long long first = (q % chunks_per_chan) * frames_per_chunk;
+    const long long nfr = min(frames_per_chunk, p.frames - first);
+    const float* sig = p.sig + c * p.chan_stride;
+    cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (C + 1);
+    long long pos = first * H;
+    const int nsteps = static_cast<int>((nfr + G - 1) / G);
+
+    __syncwarp();
+    ring_fill(ring, mask, sig, p.len, pos, S, bar, lane);
+
+    for (int s = 0; s < nsteps; ++s) {
+      mbar_wait(bar, parity);
+      parity ^= 1u;
+      __syncwarp();
+
+      cpx v[32];
+#pragma unroll
+      for (int j = 0; j < X::M1; ++j) {
+#pragma unroll
+        for (int b = 0; b < B; ++b) {
+          const int ridx = static_cast<int>((pos + in_off[j] + 2 * A * b) & mask);
+          const float2 x = *reinterpret_cast<const float2*>(ring + ridx);
+          const float2 w = *reinterpret_cast<const float2*>(s_win + 2 * a_lane + 2 * A * b);
+          float px = x.x * w.x, py = x.y * w.y;
+          if (SCRUB) {
+            px = scrub(px);
+            py = scrub(py);
+          }
+          v[j * B + b] = mk(px, py);
+        }
+      }
+      __syncwarp();
+      if (s + 1 < nsteps) ring_fill(ring, mask, sig, p.len, pos + S, G * H, bar, lane);
+
+      pass1<X, false>(v);
+      twiddle1<X, false>(v, lane, s_tw1);
+      xchg_write<X>(v, lane, ex);
+      __syncwarp();
+      xchg_read<X>(v, lane, ex);
+      __syncwarp();
+      pass2<X, false>(v);
+      cpx nyq[X::M2];
+      fwd_split<X>(v, lane, s_st,
+                   [&](int r) {
+                     return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
+                   },
+                   nyq);
+
+      const long long left = nfr - static_cast<long long>(s) * G;
+#pragma unroll
+      for (int j = 0; j < X::M2; ++j) {
+        const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
+        if (g < left) {
+          cpx* row = spec + static_cast<long long>(g) * (C + 1);
+#pragma unroll
+          for (int oa = 0; oa < A; ++oa) stg_stream(row + ob + B * oa, v[j * A + oa]);
+          if (ob == 0) stg_stream(row + C, nyq[j]);
+        }
+      }
+      pos += static_cast<long long>(G) * H;
+      spec += static_cast<long long>(G) * (C + 1);
+    }
+  }
+}
+
+template <int NFFT>
+cudaError_t launch_k1(const K1Params& p, cudaStream_t st) {
+  using X = GeoX<NFFT>;
+  const int S = (X::G - 1) * p.hop + NFFT;
+  const int rcap = next_pow2(S);
+  const int smem = K1Smem<NFFT>::total(rcap, kK1Warps);
+  if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
+  auto kern = p.scrub ? stft_fwd_kernel<NFFT, true> : stft_fwd_kernel<NFFT, false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
+  if (e != cudaSuccess) return e;
+  const long long frames_per_chunk = static_cast<long long>(p.chunk_steps) * X::G;
+  const long long total_chunks = ((p.frames + frames_per_chunk - 1) / frames_per_chunk) * p.channels;
+  const long long want_blocks = (total_chunks + kK1Warps - 1) / kK1Warps;
+  const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
+  kern<<<grid > 0 ? grid : 1, kK1Warps * 32, smem, st>>>(p, rcap);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st) {
+  if (p.frames <= 0 || p.channels <= 0) return cudaSuccess;
+  switch (p.nfft) {
+    case 256: return launch_k1<256>(p, st);
+    case 512: return launch_k1<512>(p, st);
+    case 1024: return launch_k1<1024>(p, st);
+    case 2048: return launch_k1<2048>(p, st);
+    default: return cudaErrorNotSupported;
+  }
+}
+
+}  // namespace crlot

@@ -1,0 +1,129 @@
+// k2_istft.cu -- kernel 2: inverse real FFT, 1/N scale, clean-up, optional synthesis window.
+//
+// Replaces, per frame, KissFftPlan::inverse -> kiss_fftri (reference:
+// dsp/fft/backends/kissfft_adapter.cc:124-168, third_party/kissfft/kiss_fftr.c:119-155) and,
+// when a synthesis window is given, the `src*win` half of axpy_windowed
+// (dsp/ola/kernels.cc:24-28): the product is rounded to fp32 here exactly as
+// std::fma(src, win, 0.0f) rounds it there, so kernel 3 can finish with fma(p, gain, acc).
+//
+// Same warp-autonomous structure as kernel 1 (warpfft.cuh): a warp-step is 1024 complex
+// points; spectrum rows are read straight into registers as contiguous 8-byte-per-lane
+// segments, the mirror bins come from one warp shuffle per value, frames are written straight
+// from registers.  Warp-steps are interleaved over the grid so neighbouring warps stream
+// neighbouring rows.
+#include "common.cuh"
+#include "kernels.h"
+#include "warpfft.cuh"
+
+namespace crlot {
+
+namespace {
+
+constexpr int kK2Warps = 12;
+
+template <int NFFT, bool WIN, bool SCRUB>
+__global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Params p) {
+  using X = GeoX<NFFT>;
+  constexpr int C = X::C, G = X::G, A = X::A, B = X::B;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* s_win = reinterpret_cast<float*>(smem_raw);
+  cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
+  cpx* s_su = s_tw1 + C;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  cpx* ex = s_su + C + warp * X::XCPX;
+
+  if (WIN)
+    for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    s_tw1[i] = p.tw1[i];
+    s_su[i] = p.su[i];
+  }
+  __syncthreads();
+
+  const long long total_steps = (p.rows + G - 1) / G;
+  const long long stride = static_cast<long long>(gridDim.x) * kK2Warps;
+  const int lp = mirror_lane<A>(lane);
+  const float scale = 1.0f / static_cast<float>(NFFT);
+
+  for (long long step = static_cast<long long>(blockIdx.x) * kK2Warps + warp; step < total_steps; step += stride) {
+    const long long row0 = step * G;
+    const long long left = p.rows - row0;
+    cpx v[32];
+    cpx nyq[X::M1];
+#pragma unroll
+    for (int j = 0; j < X::M1; ++j) {
+      const int i1 = lane + 32 * j, g = i1 / A, a = i1 % A;
+      const bool ok = g < left;
+      const cpx* row = p.spec + (row0 + g) * (C + 1);
+#pragma unroll
+      for (int b = 0; b < B; ++b) v[j * B + b] = ok ? ldg_stream(row + a + A * b) : mk(0.f, 0.f);
+      nyq[j] = (ok && a == 0) ? ldg_stream(row + C) : mk(0.f, 0.f);
+    }
+    inv_split<X>(v, lane, s_su,
+                 [&](int r) {
+                   return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
+                 },
+                 nyq);
+    pass1<X, true>(v);
+    twiddle1<X, true>(v, lane, s_tw1);
+    __syncwarp();                 // previous step's exchange reads are complete
+    xchg_write<X>(v, lane, ex);
+    __syncwarp();
+    xchg_read<X>(v, lane, ex);
+    pass2<X, true>(v);
+#pragma unroll
+    for (int j = 0; j < X::M2; ++j) {
+      const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
+      if (g < left) {
+        float* dst = p.frames + (row0 + g) * NFFT;
+#pragma unroll
+        for (int oa = 0; oa < A; ++oa) {
+          const int o = ob + B * oa;
+          float y0 = v[j * A + oa].x * scale, y1 = v[j * A + oa].y * scale;
+          if (SCRUB) {
+            y0 = scrub(y0);
+            y1 = scrub(y1);
+          }
+          if (WIN) {
+            const float2 w = *reinterpret_cast<const float2*>(s_win + 2 * o);
+            y0 = __fmul_rn(y0, w.x);
+            y1 = __fmul_rn(y1, w.y);
+          }
+          stg_stream(reinterpret_cast<cpx*>(dst + 2 * o), mk(y0, y1));
+        }
+      }
+    }
+  }
+}
+
+template <int NFFT>
+cudaError_t launch_k2(const K2Params& p, cudaStream_t st) {
+  using X = GeoX<NFFT>;
+  const bool win = p.window != nullptr;
+  const int smem = (win ? NFFT * 4 : 0) + X::C * 16 + kK2Warps * X::XCPX * 8;
+  void (*kern)(const K2Params) = nullptr;
+  if (win) kern = p.scrub ? istft_inv_kernel<NFFT, true, true> : istft_inv_kernel<NFFT, true, false>;
+  else     kern = p.scrub ? istft_inv_kernel<NFFT, false, true> : istft_inv_kernel<NFFT, false, false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  const long long total_steps = (p.rows + X::G - 1) / X::G;
+  const long long want_blocks = (total_steps + kK2Warps - 1) / kK2Warps;
+  const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
+  kern<<<grid > 0 ? grid : 1, kK2Warps * 32, smem, st>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st) {
+  if (p.rows <= 0) return cudaSuccess;
+  switch (p.nfft) {
+    case 256: return launch_k2<256>(p, st);
+    case 512: return launch_k2<512>(p, st);
+    case 1024: return launch_k2<1024>(p, st);
+    case 2048: return launch_k2<2048>(p, st);
+    default: return cudaErrorNotSupported;
+  }
+}
+
+}  // namespace crlot

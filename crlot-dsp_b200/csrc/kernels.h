@@ -1,0 +1,85 @@
+// kernels.h -- internal (C++) launch interface between the C-ABI layer (capi.cu) and the three
+// hot-path kernels + helpers.  Not installed; the public boundary is include/crlot_cuda.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "regfft.cuh"
+
+namespace crlot {
+
+// ---- kernel 1: fused frame extraction + analysis window + forward real FFT ---------------------
+// Frame k of channel c = samples sig[c*chan_stride + k*hop + (0..nfft)), zero beyond `len`
+// (ZERO_PAD tail; DROP callers simply pass a frame count that never reaches past len).
+// spec row (c*spec_chan_rows + k) holds nfft/2+1 interleaved (re,im) bins.
+struct K1Params {
+  const float* sig;
+  long long chan_stride;     // floats between channels (multiple of 4)
+  long long len;             // valid samples per channel
+  int channels;
+  long long frames;          // frames per channel to compute
+  int nfft, hop;
+  cpx* spec;
+  long long spec_chan_rows;  // rows between channels in spec
+  const float* window;       // device, nfft floats (all ones = no window)
+  const cpx* tw1;            // device tables (tables.h)
+  const cpx* st;
+  const cpx* pre;            // nfft == 4096 only
+  unsigned int* counter;     // zeroed work counter (dynamic chunk scheduling)
+  int chunk_steps;           // steps (of G frames) per scheduled chunk
+  int scrub;                 // apply the adapter's NaN/Inf/tiny clean-up to the windowed input
+};
+cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st);
+
+// ---- kernel 2: inverse real FFT * (1/nfft) + clean-up (+ synthesis window) --------------------
+struct K2Params {
+  const cpx* spec;           // rows of nfft/2+1 bins, `rows` of them, contiguous
+  long long rows;
+  int nfft;
+  float* frames;             // rows of nfft floats
+  const float* window;       // device, nfft floats, or nullptr: no synthesis window here
+  const cpx* tw1;
+  const cpx* su;
+  const cpx* pre;
+  int scrub;
+};
+cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st);
+
+// ---- kernel 3: gather overlap-add + envelope normalisation ------------------------------------
+// out[c][j] = ( sum_k' fma( f(k',u) , gain, acc ) ) / max(norm[(t_offset + j) % ring_len], eps),
+//   u = j - frame_t0 - k'*hop in [0,nfft), k' ascending in [0,frames),
+//   f = frames[c][k'][u] * window[u] rounded to fp32 when window != nullptr, else frames[c][k'][u].
+struct K3Params {
+  const float* frames;
+  long long frames_chan_rows;   // rows between channels
+  long long frames_per_chan;
+  int channels;
+  int nfft, hop;
+  const float* window;          // device or nullptr (frames already carry the synthesis window)
+  float gain, eps;
+  const float* norm;            // device envelope, ring_len floats
+  long long ring_len;
+  long long t_offset;           // absolute sample index of out[.][0] (envelope phase)
+  long long frame_t0;           // local output index of the first sample of local frame 0 (may be < 0)
+  float* out;
+  long long out_chan_stride;
+  long long n_out;              // samples per channel to produce
+};
+cudaError_t launch_ola_gather(const K3Params& p, cudaStream_t st);
+
+// ---- helpers ----------------------------------------------------------------------------------
+// x[c][i] = uniform[-1,1) from hash(seed, channel0 + c, i0 + i); same function as oracle/crlot_oracle.c
+cudaError_t launch_synth_uniform(float* out, long long chan_stride, int channels, long long n,
+                                 unsigned long long seed, unsigned long long channel0,
+                                 unsigned long long i0, cudaStream_t st);
+// device-resident OLAAccumulator ring ops (facade + streaming path)
+cudaError_t launch_ring_axpy(float* ring, long long ring_len, int channels, const float* frames,
+                             long long frame_chan_stride, const float* window, float gain,
+                             long long start, int n, cudaStream_t st);
+cudaError_t launch_ring_produce(float* ring, long long ring_len, int channels, const float* norm,
+                                float eps, long long read_pos, int n, float* out,
+                                long long out_chan_stride, cudaStream_t st);
+
+int device_sm_count();
+
+}  // namespace crlot

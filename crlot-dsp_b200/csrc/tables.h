@@ -1,0 +1,58 @@
+// tables.h -- host-side (double precision) construction of the constant tables the kernels
+// read from shared memory.  Used by capi.cu (uploaded once per plan) and by tests/cpu_emu.
+#pragma once
+#include <cmath>
+#include <vector>
+
+namespace crlot {
+
+struct FftTables {
+  int nfft = 0, C = 0, A = 0, B = 0;
+  std::vector<float> tw1;   // [B][A] cpx : exp(-2 pi i a*ob / C)      inter-pass twiddle (forward)
+  std::vector<float> st;    // [C]    cpx : 0.5*exp(-i pi (k/C + 1/2)) forward real split
+  std::vector<float> su;    // [C]    cpx : exp(+i pi (k/C + 1/2))     inverse real split
+  std::vector<float> pre;   // [1024] cpx : exp(-2 pi i n / 2048)      N=4096 radix-2 pre-stage
+};
+
+// C = complex length of the real split (nfft/2); Cw = complex length one warp transforms
+// (== C except nfft=4096 where the warp transforms 1024 points after the radix-2 pre-stage).
+inline FftTables make_fft_tables(int nfft) {
+  const double pi = 3.141592653589793238462643383279502884;
+  FftTables t;
+  t.nfft = nfft;
+  t.C = nfft / 2;
+  const int Cw = t.C > 1024 ? 1024 : t.C;
+  switch (Cw) {
+    case 1024: t.A = 32; t.B = 32; break;
+    case 512:  t.A = 32; t.B = 16; break;
+    case 256:  t.A = 16; t.B = 16; break;
+    default:   t.A = 16; t.B = 8;  break;
+  }
+  t.tw1.resize(2 * (size_t)t.A * t.B);
+  for (int ob = 0; ob < t.B; ++ob)
+    for (int a = 0; a < t.A; ++a) {
+      const double ph = -2.0 * pi * (double)a * (double)ob / (double)Cw;
+      t.tw1[2 * (ob * t.A + a)] = (float)std::cos(ph);
+      t.tw1[2 * (ob * t.A + a) + 1] = (float)std::sin(ph);
+    }
+  t.st.resize(2 * (size_t)t.C);
+  t.su.resize(2 * (size_t)t.C);
+  for (int k = 0; k < t.C; ++k) {
+    const double ph = pi * ((double)k / (double)t.C + 0.5);
+    t.st[2 * k] = (float)(0.5 * std::cos(-ph));
+    t.st[2 * k + 1] = (float)(0.5 * std::sin(-ph));
+    t.su[2 * k] = (float)std::cos(ph);
+    t.su[2 * k + 1] = (float)std::sin(ph);
+  }
+  if (nfft == 4096) {
+    t.pre.resize(2 * 1024);
+    for (int n = 0; n < 1024; ++n) {
+      const double ph = -2.0 * pi * (double)n / 2048.0;
+      t.pre[2 * n] = (float)std::cos(ph);
+      t.pre[2 * n + 1] = (float)std::sin(ph);
+    }
+  }
+  return t;
+}
+
+}  // namespace crlot

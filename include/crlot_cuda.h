@@ -1,0 +1,190 @@
+/* include/crlot_cuda.h -- C-ABI of the B200 (sm_100a) implementation of crlot-dsp's
+ * STFT -> iSTFT hot path:  Framer frame extraction, WindowLUT application, batched real
+ * FFT / inverse FFT, OLAAccumulator overlap-add with the NormBuilder envelope.
+ *
+ * This is the ONE boundary between host code (the reference's C++ classes, kept as thin
+ * facades in crlot-dsp_b200/host/, or any other language's FFI) and the CUDA side.  Plain
+ * pointers and sizes only; every call returns an int status (0 = ok) and never throws;
+ * crlot_cuda_last_error() gives the message for the calling thread.  There is no CPU
+ * fallback behind any entry point: without a CUDA device every compute call fails.
+ *
+ * Each entry point names the reference interface it replaces ("ref:" = path relative to
+ * the crlot-dsp tree).  INTEGRATION.md shows the reference-side binding.
+ */
+#ifndef CRLOT_CUDA_H_
+#define CRLOT_CUDA_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CRLOT_ABI_VERSION 1
+
+/* status codes; the C++ facades map them back to the reference's exception types */
+enum {
+  CRLOT_OK = 0,
+  CRLOT_ERR_INVALID_ARGUMENT = 1, /* -> std::invalid_argument (ref: framer.cc:17-25, OLAAccumulator.cc:19,40,43,57) */
+  CRLOT_ERR_RUNTIME = 2,          /* -> std::runtime_error    (ref: kissfft_adapter.cc:16-45,85-131)             */
+  CRLOT_ERR_ALLOC = 3,            /* -> std::bad_alloc        (ref: aligned_alloc.h:21,32)                         */
+  CRLOT_ERR_UNSUPPORTED = 4,      /* shape not implemented on the GPU path (no fallback by design)                */
+  CRLOT_ERR_CUDA = 5              /* CUDA runtime failure; message carries cudaGetErrorString                     */
+};
+
+/* ref: dsp/window/WindowLUT.h:13-30 */
+enum { CRLOT_WIN_HANN = 0, CRLOT_WIN_HAMMING = 1, CRLOT_WIN_BLACKMAN = 2, CRLOT_WIN_RECT = 3, CRLOT_WIN_BLACKMAN_HARRIS = 4 };
+enum { CRLOT_NORM_NONE = 0, CRLOT_NORM_SUM_TO_ONE = 1, CRLOT_NORM_L2 = 2, CRLOT_NORM_OLA_UNITY_GAIN = 3, CRLOT_NORM_OLA_SUM_WSQ = 4 };
+/* ref: dsp/frame/framer.h:11-14 */
+enum { CRLOT_ZERO_PAD = 0, CRLOT_DROP = 1 };
+
+/* ---- library ------------------------------------------------------------------------------- */
+int crlot_cuda_abi_version(void);
+const char* crlot_cuda_last_error(void);
+int crlot_cuda_device_count(int* count);
+/* cudaStreamSynchronize(stream) on `device` (stream NULL = default stream) */
+int crlot_cuda_stream_sync(int device, void* stream);
+
+/* ---- device buffer handles ------------------------------------------------------------------ */
+typedef struct crlot_buf_s* crlot_buf_t;
+int crlot_buf_create(size_t bytes, int device, crlot_buf_t* out);               /* owns cudaMalloc memory   */
+int crlot_buf_wrap(void* device_ptr, size_t bytes, int device, crlot_buf_t* out); /* borrows caller's memory */
+int crlot_buf_destroy(crlot_buf_t buf);
+int crlot_buf_upload(crlot_buf_t buf, size_t dst_offset, const void* host, size_t bytes, void* stream);
+int crlot_buf_download(crlot_buf_t buf, size_t src_offset, void* host, size_t bytes, void* stream);
+int crlot_buf_zero(crlot_buf_t buf, size_t offset, size_t bytes, void* stream);
+void* crlot_buf_device_ptr(crlot_buf_t buf);
+size_t crlot_buf_bytes(crlot_buf_t buf);
+/* page-locked host staging memory for the host-buffer entry points */
+int crlot_host_alloc(size_t bytes, void** out);
+int crlot_host_free(void* p);
+
+/* ---- host-side table builders (tiny, double precision; uploaded once per plan) ---------------- */
+/* ref: WindowLUT::createWindow + generators + applyNormalization, dsp/window/WindowLUT.cc:215-388 */
+int crlot_window_make(int type, size_t n, int periodic, int norm, float* out);
+/* ref: OLAAccumulator::calculate_ring_size, dsp/ola/OLAAccumulator.cc:249-258 */
+size_t crlot_ola_ring_len(size_t frame, size_t hop);
+/* ref: dsp::ola::build_norm_linear, dsp/ola/norm_builder.cc:8-52 (double count at the seam included) */
+int crlot_build_norm_linear(float* norm, const float* window, size_t ring_len, size_t frame, size_t hop);
+/* ref: OLAAccumulator::initialize_normalization, dsp/ola/OLAAccumulator.cc:260-288 */
+int crlot_ola_envelope(float* norm, const float* window_or_null, size_t ring_len, size_t frame, size_t hop,
+                       int apply_window_inside, float eps);
+/* ref: Framer::calculate_available_frames after one push of `len` samples, dsp/frame/framer.cc:88-118 */
+long long crlot_frame_count(long long len, int frame, int hop, int boundary_mode);
+
+/* ---- STFT plan ------------------------------------------------------------------------------ */
+typedef struct crlot_plan_s* crlot_plan_t;
+
+typedef struct crlot_stft_desc {
+  int nfft;                      /* frame size N: 256, 512, 1024, 2048 or 4096                       */
+  int hop;                       /* hop H: multiple of 4, 0 < H <= N                                  */
+  int boundary_mode;             /* CRLOT_ZERO_PAD / CRLOT_DROP (Framer boundary mode)                 */
+  const float* analysis_window;  /* host, N floats, or NULL (no multiply before the FFT)              */
+                                 /*   ref: bench/e2e_benchmark.cc:154-156                             */
+  const float* ola_window;       /* host, N floats, what OLAAccumulator::set_window received, or NULL */
+  const float* push_window;      /* host, N floats, the per-call `window` argument of add_frame_SoA   */
+                                 /*   (honoured only when !apply_window_inside), or NULL              */
+  int apply_window_inside;       /* OLAConfig::apply_window_inside, ref: OLAAccumulator.h:21          */
+  float gain;                    /* gain argument of add_frame_SoA / push_frame_AoS                   */
+  float eps;                     /* OLAConfig::eps (default 1e-8f)                                    */
+  int scrub;                     /* 1: NaN/Inf/|v|<1e-30 -> 0 on FFT input and inverse output         */
+                                 /*   ref: kissfft_adapter.cc:104-108,159-163                         */
+  const float* envelope;         /* host override of the normalisation envelope, or NULL = reference  */
+  size_t envelope_len;           /*   rule (crlot_ola_envelope over crlot_ola_ring_len)               */
+  int device;                    /* CUDA device ordinal                                               */
+} crlot_stft_desc;
+
+typedef struct crlot_plan_info {
+  int nfft, hop, bins;           /* bins = nfft/2 + 1                                                  */
+  size_t ring_len;               /* envelope period                                                    */
+  int synthesis_window_active;   /* the window policy resolved (OLAAccumulator.cc:82-83)               */
+  int device;
+} crlot_plan_info;
+
+int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out);
+int crlot_stft_plan_destroy(crlot_plan_t plan);
+int crlot_stft_plan_info(crlot_plan_t plan, crlot_plan_info* info);
+/* copies the plan's envelope (ring_len floats) to host */
+int crlot_stft_plan_envelope(crlot_plan_t plan, float* host_out);
+
+/* Kernel 1.  Frame k of channel c = d_signal[c*chan_stride + k*hop + (0..nfft)), samples at or
+ * beyond `len` read as zero.  d_spec: [channels][n_frames][nfft/2+1] interleaved (re,im) fp32.
+ * replaces: Framer::pop + analysis-window loop + IFftPlan::forward
+ *   ref: dsp/frame/framer.cc:61-67,128-182; bench/e2e_benchmark.cc:152-156;
+ *        dsp/fft/backends/kissfft_adapter.cc:83-122 */
+int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
+                       long long n_frames, void* d_spec, void* stream);
+
+/* Kernel 2.  rows spectra -> rows frames of nfft floats, scaled by 1/nfft and cleaned up;
+ * with fuse_synthesis_window != 0 each sample is additionally multiplied (one rounding) by the
+ * plan's resolved synthesis window, so that crlot_ola_accumulate can be told frames are
+ * pre-windowed.
+ * replaces: IFftPlan::inverse   ref: dsp/fft/backends/kissfft_adapter.cc:124-168 */
+int crlot_istft_execute(crlot_plan_t plan, const void* d_spec, long long rows, float* d_frames,
+                        int fuse_synthesis_window, void* stream);
+
+/* Kernel 3.  Gather overlap-add of local frames [0,frames_per_chan) of each channel into n_out
+ * samples per channel.  Local frame k starts at local output index frame_t0 + k*hop; output
+ * sample j has absolute index t_offset + j (selects the envelope phase).
+ * replaces: OLAAccumulator::add_frame_SoA / push_frame_AoS + produce in the streaming drive
+ *   ref: dsp/ola/OLAAccumulator.cc:54-122,162-221; dsp/ola/kernels.cc:18-36 */
+int crlot_ola_accumulate(crlot_plan_t plan, const float* d_frames, long long frames_chan_rows,
+                         long long frames_per_chan, int channels, int frames_prewindowed, long long t_offset,
+                         long long frame_t0, float* d_out, long long out_chan_stride, long long n_out, void* stream);
+
+/* The composed round trip on device buffers (K1 -> K2 -> K3 on `stream`).  d_spec and d_frames
+ * are caller-provided materialisation buffers ([channels][n_frames][bins] complex and
+ * [channels][n_frames][nfft] fp32).  n_frames = crlot_frame_count(len,...); output length per
+ * channel = (n_frames-1)*hop + nfft.
+ * replaces the composition in bench/e2e_benchmark.cc:138-186 (driven in the order of
+ * bench/ola_benchmark.cc:150-157). */
+int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
+                            int channels, void* d_spec, float* d_frames, float* d_out, long long out_chan_stride,
+                            void* stream);
+
+/* Same round trip with HOST buffers: host->device and device->host copies are inside the call,
+ * processed in time slabs through an internal double-buffered workspace so transfers overlap
+ * compute.  h_out receives (n_frames-1)*hop + nfft samples per channel; *n_out_per_chan is set.
+ * h_in / h_out should be page-locked (crlot_host_alloc) for full PCIe rate. */
+int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_stride, long long len, int channels,
+                         float* h_out, long long out_chan_stride, long long* n_out_per_chan);
+
+/* Device generator of the benchmark signal: x[c][i] = uniform[-1,1) from a counter hash of
+ * (seed, channel0 + c, i0 + i); identical to oracle/crlot_oracle.c:orc_synth_uniform. */
+int crlot_synth_uniform(float* d_out, long long chan_stride, int channels, long long n, unsigned long long seed,
+                        unsigned long long channel0, unsigned long long i0, int device, void* stream);
+
+/* ---- drop-in FFT plan (host pointers, reference batch/stride layout) --------------------------- */
+/* replaces dsp::fft::MakeFftPlan / IFftPlan::{forward,inverse} for FftDomain::Real
+ *   ref: dsp/fft/api/fft_api.h:16-51; dsp/fft/backends/kissfft_adapter.cc:13-63,83-168
+ * Argument rules and their failures (CRLOT_ERR_RUNTIME) mirror the adapter: batch 1..16,
+ * strides >= 1, in_place unsupported, even nfft.  nfft must also be one the GPU path has. */
+typedef struct crlot_fft_s* crlot_fft_t;
+int crlot_fft_plan_create(int nfft, int in_place, int batch, int stride_in, int stride_out, int device,
+                          crlot_fft_t* out);
+int crlot_fft_plan_destroy(crlot_fft_t plan);
+int crlot_fft_forward(crlot_fft_t plan, const float* h_in, float* h_out_ri, int batch);
+int crlot_fft_inverse(crlot_fft_t plan, const float* h_in_ri, float* h_out, int batch);
+
+/* ---- drop-in OLAAccumulator state (device rings, host pointers at the calls) -------------------- */
+/* replaces dsp::OLAAccumulator   ref: dsp/ola/OLAAccumulator.h:15-164, .cc:13-295 */
+typedef struct crlot_ola_s* crlot_ola_t;
+int crlot_ola_create(int sample_rate, size_t frame_size, size_t hop_size, size_t channels, float eps,
+                     int apply_window_inside, int shadow_ring, int device, crlot_ola_t* out);
+int crlot_ola_destroy(crlot_ola_t ola);
+int crlot_ola_set_window(crlot_ola_t ola, const float* w, int wlen);
+int crlot_ola_add_frame_soa(crlot_ola_t ola, const float* const* ch_frames, const float* window,
+                            size_t start_sample, size_t start_off, size_t size, float gain);
+int crlot_ola_push_frame_aos(crlot_ola_t ola, const float* interleaved, const float* window, size_t start_sample,
+                             size_t start_off, size_t size, float gain);
+int crlot_ola_produce(crlot_ola_t ola, float* const* ch_out, size_t n, size_t* produced);
+int crlot_ola_flush(crlot_ola_t ola);
+int crlot_ola_reset(crlot_ola_t ola);
+/* what = 0 produced_samples, 1 read_pos, 2 ring_size, 3 has_window */
+size_t crlot_ola_get(crlot_ola_t ola, int what);
+float crlot_ola_meter_peak(crlot_ola_t ola);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CRLOT_CUDA_H_ */

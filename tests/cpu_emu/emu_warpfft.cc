@@ -1,0 +1,120 @@
+// tests/cpu_emu/emu_warpfft.cc -- runs the per-lane code of csrc/warpfft.cuh lane by lane on
+// the CPU (a warp = 32 sequential lanes per phase; a shuffle = reading another lane's array)
+// and compares with a double-precision DFT.  Checks the index algebra (four-step mapping,
+// exchange addressing incl. bank-conflict freedom, mirror lanes) without a GPU.
+#include <cmath>
+#include <complex>
+#include <cstdio>
+#include <cstdlib>
+#include <set>
+#include <vector>
+
+#include "../../crlot-dsp_b200/csrc/tables.h"
+#include "../../crlot-dsp_b200/csrc/warpfft.cuh"
+
+using namespace crlot;
+typedef std::complex<double> cd;
+
+static double frand() { return 2.0 * rand() / (double)RAND_MAX - 1.0; }
+
+template <int NFFT> static int run() {
+  typedef GeoX<NFFT> X;
+  const int C = X::C, G = X::G, N = NFFT;
+  FftTables T = make_fft_tables(N);
+  const cpx* tw1 = reinterpret_cast<const cpx*>(T.tw1.data());
+  const cpx* st = reinterpret_cast<const cpx*>(T.st.data());
+  const cpx* su = reinterpret_cast<const cpx*>(T.su.data());
+  std::vector<std::vector<float>> x(G, std::vector<float>(N));
+  for (auto& f : x) for (auto& s : f) s = (float)frand();
+  // reference spectra in double
+  std::vector<std::vector<cd>> Xr(G, std::vector<cd>(C + 1));
+  for (int g = 0; g < G; ++g)
+    for (int k = 0; k <= C; ++k) {
+      cd s = 0;
+      for (int n = 0; n < N; ++n) s += (double)x[g][n] * std::polar(1.0, -2.0 * M_PI * (double)n * k / N);
+      Xr[g][k] = s;
+    }
+  // ---------------- forward ----------------
+  std::vector<cpx> ex(X::XCPX);
+  cpx v[32][32];
+  for (int l = 0; l < 32; ++l)
+    for (int r = 0; r < 32; ++r) {
+      int g, i; in_coord<X>(l, r, g, i);
+      v[l][r] = mk(x[g][2 * i], x[g][2 * i + 1]);
+    }
+  for (int l = 0; l < 32; ++l) { pass1<X, false>(v[l]); twiddle1<X, false>(v[l], l, tw1); }
+  // bank-conflict check on the exchange pattern (8-byte accesses: per half-warp 16 distinct pairs)
+  int conflicts = 0;
+  for (int j = 0; j < X::M1; ++j) for (int ob = 0; ob < X::B; ++ob) for (int h = 0; h < 2; ++h) {
+    std::set<int> banks;
+    for (int l = 16 * h; l < 16 * h + 16; ++l) { int i1 = l + 32 * j; banks.insert(X::xaddr(i1 / X::A, i1 % X::A, ob) % 16); }
+    if (banks.size() != 16) ++conflicts;
+  }
+  for (int j = 0; j < X::M2; ++j) for (int a = 0; a < X::A; ++a) for (int h = 0; h < 2; ++h) {
+    std::set<int> banks;
+    for (int l = 16 * h; l < 16 * h + 16; ++l) { int i2 = l + 32 * j; banks.insert(X::xaddr(i2 / X::B, a, i2 % X::B) % 16); }
+    if (banks.size() != 16) ++conflicts;
+  }
+  for (int l = 0; l < 32; ++l) xchg_write<X>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) xchg_read<X>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) pass2<X, false>(v[l]);
+  cpx snap[32][32];
+  for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
+  cpx nyq[32][X::M2];
+  for (int l = 0; l < 32; ++l) {
+    const int lp = mirror_lane<X::B>(l);
+    fwd_split<X>(v[l], l, st, [&](int r) { return snap[lp][r]; }, nyq[l]);
+  }
+  double err = 0, nrm = 0;
+  std::vector<std::vector<cd>> Xg(G, std::vector<cd>(C + 1));
+  for (int l = 0; l < 32; ++l)
+    for (int r = 0; r < 32; ++r) {
+      int g, o; out_coord<X>(l, r, g, o);
+      Xg[g][o] = cd(v[l][r].x, v[l][r].y);
+      if (o == 0) Xg[g][C] = cd(nyq[l][r / X::A].x, nyq[l][r / X::A].y);
+    }
+  for (int g = 0; g < G; ++g) for (int k = 0; k <= C; ++k) { err += std::norm(Xg[g][k] - Xr[g][k]); nrm += std::norm(Xr[g][k]); }
+  const double fwd_rel = std::sqrt(err / nrm);
+  int exact0 = 1;
+  for (int g = 0; g < G; ++g) if (Xg[g][0].imag() != 0.0 || Xg[g][C].imag() != 0.0) exact0 = 0;
+  // ---------------- inverse (from the double-precision spectrum rounded to float) ----------------
+  cpx nq[32][X::M1];
+  for (int l = 0; l < 32; ++l)
+    for (int r = 0; r < 32; ++r) {
+      int g, i; in_coord<X>(l, r, g, i);
+      v[l][r] = mk((float)Xr[g][i].real(), (float)Xr[g][i].imag());
+      if (i == 0) { v[l][r].y = 123.0f; nq[l][r / X::B] = mk((float)Xr[g][C].real(), -77.0f); }  // imag of DC/Nyquist must be ignored
+    }
+  for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
+  for (int l = 0; l < 32; ++l) {
+    const int lp = mirror_lane<X::A>(l);
+    inv_split<X>(v[l], l, su, [&](int r) { return snap[lp][r]; }, nq[l]);
+  }
+  for (int l = 0; l < 32; ++l) { pass1<X, true>(v[l]); twiddle1<X, true>(v[l], l, tw1); }
+  for (int l = 0; l < 32; ++l) xchg_write<X>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) xchg_read<X>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) pass2<X, true>(v[l]);
+  err = 0; nrm = 0;
+  for (int l = 0; l < 32; ++l)
+    for (int r = 0; r < 32; ++r) {
+      int g, o; out_coord<X>(l, r, g, o);
+      const double y0 = v[l][r].x / (double)N, y1 = v[l][r].y / (double)N;
+      err += (y0 - x[g][2 * o]) * (y0 - x[g][2 * o]) + (y1 - x[g][2 * o + 1]) * (y1 - x[g][2 * o + 1]);
+      nrm += (double)x[g][2 * o] * x[g][2 * o] + (double)x[g][2 * o + 1] * x[g][2 * o + 1];
+    }
+  const double inv_rel = std::sqrt(err / nrm);
+  const int ok = fwd_rel < 5e-7 && inv_rel < 5e-7 && conflicts == 0 && exact0;
+  printf("N=%4d G=%d A=%2d B=%2d  fwd rel-L2 %.3e  inv rel-L2 %.3e  xchg conflicts %d  exact-zero imag %d  %s\n", N, G,
+         X::A, X::B, fwd_rel, inv_rel, conflicts, exact0, ok ? "OK" : "FAIL");
+  return ok ? 0 : 1;
+}
+
+int main() {
+  srand(1234);
+  int bad = 0;
+  bad += run<256>();
+  bad += run<512>();
+  bad += run<1024>();
+  bad += run<2048>();
+  return bad;
+}

@@ -1,0 +1,65 @@
+"""Randomised bit-for-bit comparison of the plain-C oracle with the unmodified reference
+compiled from /root/reference (oracle/_ref/libcrlot_ref_strict.so).  Skipped where the
+reference build is absent; the golden-vector tests pin the same thing there."""
+import numpy as np
+import pyoracle as po
+import pytest
+from conftest import bits
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_fft_random_sizes(oracle, ref_strict, seed):
+    rng = np.random.default_rng(seed)
+    for n in [2, 4, 6, 8, 10, 30, 64, 100, 250, 256, 1000, 1024, 2048, 4096, 2 * 7 * 11, 2 * 13, 8192]:
+        x = (rng.standard_normal(n) * 10.0 ** rng.integers(-3, 3)).astype(np.float32)
+        X = ref_strict.rfft(x, n)
+        assert np.array_equal(bits(oracle.rfft(x, n)), bits(X)), n
+        assert np.array_equal(bits(oracle.irfft(X, n)), bits(ref_strict.irfft(X, n))), n
+
+
+def test_framer_random(oracle, ref_strict):
+    rng = np.random.default_rng(7)
+    for _ in range(40):
+        L, N, H, Cn = int(rng.integers(1, 3000)), int(rng.integers(1, 400)), int(rng.integers(1, 200)), int(rng.integers(1, 4))
+        x = rng.standard_normal(L * Cn).astype(np.float32)
+        for mode in (po.ZERO_PAD, po.DROP):
+            a, b = oracle.framer(x, N, H, Cn, mode), ref_strict.framer(x, N, H, Cn, mode)
+            assert a.shape == b.shape and np.array_equal(a, b), (L, N, H, Cn, mode)
+
+
+def test_norm_and_stream_random(oracle, ref_strict):
+    rng = np.random.default_rng(11)
+    for N, H in [(1024, 256), (2048, 512), (4096, 1024), (256, 64), (1024, 512), (1000, 300), (64, 64), (96, 40)]:
+        w = rng.uniform(0, 1, N).astype(np.float32)
+        ring = oracle.ring_len(N, H)
+        assert ring == ref_strict.ring_len(N, H)
+        assert np.array_equal(bits(oracle.build_norm_linear(w, ring, N, H)), bits(ref_strict.build_norm_linear(w, ring, N, H)))
+        for Cn, inside, setw, passw in [(1, 1, 1, 0), (2, 0, 1, 1), (1, 0, 0, 0), (3, 1, 0, 0)]:
+            fr = rng.standard_normal((70, Cn, N)).astype(np.float32)
+            a = oracle.ola_stream(fr, N, H, Cn, w, setw, passw, inside, gain=0.8)
+            b = ref_strict.ola_stream(fr, N, H, Cn, w, setw, passw, inside, gain=0.8)
+            assert a[1] == b[1] and a[2] == b[2] and np.array_equal(bits(a[0]), bits(b[0])), (N, H, Cn, inside, setw, passw)
+            # shadow ring changes nothing observable (tests/ola_accumulator_test.cc:1079-1122)
+            c = ref_strict.ola_stream(fr, N, H, Cn, w, setw, passw, inside, gain=0.8, shadow_ring=True)
+            assert np.array_equal(bits(c[0]), bits(b[0]))
+
+
+def test_aos_equals_soa(ref_strict):
+    # tests/ola_accumulator_test.cc:439-548
+    rng = np.random.default_rng(5)
+    N, H, Cn = 256, 64, 3
+    fr = rng.standard_normal((30, Cn, N)).astype(np.float32)
+    w = rng.uniform(0, 1, N).astype(np.float32)
+    soa = ref_strict.ola_stream(fr, N, H, Cn, w, True, False, True, gain=1.3)[0]
+    aos = ref_strict.ola_stream_aos(np.ascontiguousarray(fr.transpose(0, 2, 1)), N, H, Cn, w, True, gain=1.3)[0]
+    assert np.array_equal(bits(soa), bits(aos))
+
+
+def test_roundtrip_random(oracle, ref_strict):
+    rng = np.random.default_rng(13)
+    for N, H, L, mode in [(1024, 256, 20000, po.DROP), (2048, 512, 30000, po.ZERO_PAD), (256, 64, 5000, po.DROP), (4096, 1024, 30000, po.DROP)]:
+        x = rng.uniform(-1, 1, L).astype(np.float32)
+        w = oracle.window(po.HANN, N)
+        a, b = oracle.roundtrip(x, N, H, w, mode), ref_strict.roundtrip(x, N, H, w, mode)
+        for k in ("spectra", "iframes", "out"):
+            assert np.array_equal(bits(a[k]), bits(b[k])), (N, H, k)
