@@ -147,7 +147,7 @@ struct crlot_plan_s {
   size_t ring_len = 0;
   bool syn_active = false;
   DevArr<float> win_a, win_s, env;
-  DevArr<cpx> tw1, st, su, pre;
+  DevArr<cpx> tw1, sa, pre;
   DevArr<unsigned int> counter;
   std::vector<float> env_host;
   HostSlot slot[2];
@@ -299,8 +299,7 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
   CU(p->env.upload(p->env_host.data(), p->env_host.size()));
   const FftTables T = make_fft_tables(N);
   CU(upload_cpx(p->tw1, T.tw1));
-  CU(upload_cpx(p->st, T.st));
-  CU(upload_cpx(p->su, T.su));
+  CU(upload_cpx(p->sa, T.sa));
   if (!T.pre.empty()) CU(upload_cpx(p->pre, T.pre));
   CU(p->counter.alloc(4));
   p->d.analysis_window = p->d.ola_window = p->d.push_window = p->d.envelope = nullptr;  // not retained
@@ -339,7 +338,7 @@ int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_
   k.sig = d_signal; k.chan_stride = chan_stride; k.len = len; k.channels = channels; k.frames = n_frames;
   k.nfft = plan->d.nfft; k.hop = plan->d.hop;
   k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
-  k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.st = plan->st.p; k.pre = plan->pre.p;
+  k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p;
   k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->d.scrub;
   CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
@@ -354,7 +353,7 @@ int crlot_istft_execute(crlot_plan_t plan, const void* d_spec, long long rows, f
   K2Params k{};
   k.spec = static_cast<const cpx*>(d_spec); k.rows = rows; k.nfft = plan->d.nfft; k.frames = d_frames;
   k.window = (fuse_win && plan->syn_active) ? plan->win_s.p : nullptr;
-  k.tw1 = plan->tw1.p; k.su = plan->su.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
+  k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
   CU(launch_istft_inv(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
@@ -431,12 +430,12 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
       CU(cudaMemcpyAsync(s.in.p, xin + s0, static_cast<size_t>(s1 - s0) * sizeof(float), cudaMemcpyHostToDevice, s.stream));
       K1Params k1{};
       k1.sig = s.in.p; k1.chan_stride = 0; k1.len = s1 - s0; k1.channels = 1; k1.frames = nf; k1.nfft = N; k1.hop = H;
-      k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.st = plan->st.p;
+      k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p;
       k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->d.scrub;
       CU(launch_stft_fwd(k1, s.stream));
       K2Params k2{};
       k2.spec = s.spec.p; k2.rows = nf; k2.nfft = N; k2.frames = s.frames.p;
-      k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.su = plan->su.p; k2.pre = plan->pre.p;
+      k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.sa = plan->sa.p; k2.pre = plan->pre.p;
       k2.scrub = plan->d.scrub;
       CU(launch_istft_inv(k2, s.stream));
       K3Params k3{};

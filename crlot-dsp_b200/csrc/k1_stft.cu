@@ -75,9 +75,9 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
-  cpx* s_st = s_tw1 + C;
+  cpx* s_sa = s_tw1 + C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wb = reinterpret_cast<unsigned char*>(s_st + C) + warp * K1Smem<NFFT>::per_warp_bytes(rcap);
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_sa + C) + warp * K1Smem<NFFT>::per_warp_bytes(rcap);
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + rcap);
   const uint32_t bar = smem_u32(ex + X::XCPX);
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     s_tw1[i] = p.tw1[i];
-    s_st[i] = p.st[i];
+    s_sa[i] = p.sa[i];
   }
   if (lane == 0) {
     mbar_init(bar, 1);
@@ -138,14 +138,11 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
 #pragma unroll
         for (int b = 0; b < B; ++b) {
           const int ridx = static_cast<int>((pos + in_off[j] + 2 * A * b) & mask);
-          const float2 x = *reinterpret_cast<const float2*>(ring + ridx);
-          const float2 w = *reinterpret_cast<const float2*>(s_win + 2 * a_lane + 2 * A * b);
-          float px = x.x * w.x, py = x.y * w.y;
-          if (SCRUB) {
-            px = scrub(px);
-            py = scrub(py);
-          }
-          v[j * B + b] = mk(px, py);
+          const cpx x = *reinterpret_cast<const cpx*>(ring + ridx);
+          const cpx w = *reinterpret_cast<const cpx*>(s_win + 2 * a_lane + 2 * A * b);
+          cpx pw = mul2(x, w);                 // one rounding per sample, as frame[i]*window[i]
+          if (SCRUB) pw = mk(scrub(pw.x), scrub(pw.y));
+          v[j * B + b] = pw;
         }
       }
       __syncwarp();
@@ -159,7 +156,7 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
       __syncwarp();
       pass2<X, false>(v);
       cpx nyq[X::M2];
-      fwd_split<X>(v, lane, s_st,
+      fwd_split<X>(v, lane, s_sa,
                    [&](int r) {
                      return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
                    },

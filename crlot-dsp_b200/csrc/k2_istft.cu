@@ -28,22 +28,22 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
-  cpx* s_su = s_tw1 + C;
+  cpx* s_sa = s_tw1 + C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  cpx* ex = s_su + C + warp * X::XCPX;
+  cpx* ex = s_sa + C + warp * X::XCPX;
 
   if (WIN)
     for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     s_tw1[i] = p.tw1[i];
-    s_su[i] = p.su[i];
+    s_sa[i] = p.sa[i];
   }
   __syncthreads();
 
   const long long total_steps = (p.rows + G - 1) / G;
   const long long stride = static_cast<long long>(gridDim.x) * kK2Warps;
   const int lp = mirror_lane<A>(lane);
-  const float scale = 1.0f / static_cast<float>(NFFT);
+  const float scale = 2.0f / static_cast<float>(NFFT);   // inv_split hands over halved values
 
   for (long long step = static_cast<long long>(blockIdx.x) * kK2Warps + warp; step < total_steps; step += stride) {
     const long long row0 = step * G;
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
       for (int b = 0; b < B; ++b) v[j * B + b] = ok ? ldg_stream(row + a + A * b) : mk(0.f, 0.f);
       nyq[j] = (ok && a == 0) ? ldg_stream(row + C) : mk(0.f, 0.f);
     }
-    inv_split<X>(v, lane, s_su,
+    inv_split<X>(v, lane, s_sa,
                  [&](int r) {
                    return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
                  },

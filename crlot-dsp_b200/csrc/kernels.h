@@ -23,7 +23,7 @@ struct K1Params {
   long long spec_chan_rows;  // rows between channels in spec
   const float* window;       // device, nfft floats (all ones = no window)
   const cpx* tw1;            // device tables (tables.h)
-  const cpx* st;
+  const cpx* sa;             // real-split table A_k (tables.h)
   const cpx* pre;            // nfft == 4096 only
   unsigned int* counter;     // zeroed work counter (dynamic chunk scheduling)
   int chunk_steps;           // steps (of G frames) per scheduled chunk
@@ -39,7 +39,7 @@ struct K2Params {
   float* frames;             // rows of nfft floats
   const float* window;       // device, nfft floats, or nullptr: no synthesis window here
   const cpx* tw1;
-  const cpx* su;
+  const cpx* sa;
   const cpx* pre;
   int scrub;
 };

@@ -1,16 +1,24 @@
 // regfft.cuh -- straight-line complex DFTs of 2..32 points held entirely in registers.
 //
 // Every index below is a compile-time constant after unrolling, so `cpx v[R]` never touches
-// local memory: a "permutation" is only a renaming of registers.  The same header compiles
-// as plain C++ (CRLOT_HD empty) for the CPU lane-emulator in tests/cpu_emu, which checks
-// the index algebra of the warp kernels without a GPU.
+// local memory: a "permutation" is only a renaming of registers.
 //
-// Convention: dft<R,false> computes X[k] = sum_n x[n] exp(-2 pi i n k / R)  (forward),
-//             dft<R,true>  the conjugate kernel (unnormalised inverse).  Natural order in
+// Blackwell-native arithmetic: on sm_100a a complex value is one 64-bit register pair and
+// every complex add/sub is ONE packed instruction (FADD2), every complex multiply TWO
+// (FMUL2 + FFMA2, using the .F32 splat and .LO_HI swap operand modifiers), every
+// "+/- i times" rotation is folded into an FFMA2 with a (+1,-1) constant pair.  That halves
+// the issue slots of the FFT, which is what bounds kernel 1 (profiles/README.md).
+//
+// The same header compiles as plain C++ (scalar fallbacks) for the CPU lane-emulator in
+// tests/cpu_emu, which checks the index algebra of the warp kernels without a GPU.
+//
+// Convention: Dft<R,false> computes X[k] = sum_n x[n] exp(-2 pi i n k / R)  (forward),
+//             Dft<R,true>  the conjugate kernel (unnormalised inverse).  Natural order in
 //             and out.
 #pragma once
 
 #if defined(__CUDACC__)
+#include <cuda_runtime.h>
 #define CRLOT_HD __host__ __device__ __forceinline__
 #else
 #define CRLOT_HD inline
@@ -23,15 +31,40 @@ struct alignas(8) cpx {
 };
 
 CRLOT_HD cpx mk(float a, float b) { cpx r; r.x = a; r.y = b; return r; }
+
+#if defined(__CUDA_ARCH__)
+// ---- packed f32x2 backend (sm_100a) ---------------------------------------------------------
+__device__ __forceinline__ float2 f2(cpx a) { return make_float2(a.x, a.y); }
+__device__ __forceinline__ cpx c2(float2 a) { return mk(a.x, a.y); }
+CRLOT_HD cpx operator+(cpx a, cpx b) { return c2(__fadd2_rn(f2(a), f2(b))); }
+CRLOT_HD cpx operator-(cpx a, cpx b) { return c2(__fadd2_rn(f2(a), make_float2(-b.x, -b.y))); }
+// c + a*(s.x, s.y) element-wise
+CRLOT_HD cpx fma2(cpx a, cpx s, cpx c) { return c2(__ffma2_rn(f2(a), f2(s), f2(c))); }
+CRLOT_HD cpx mul2(cpx a, cpx s) { return c2(__fmul2_rn(f2(a), f2(s))); }
+#else
 CRLOT_HD cpx operator+(cpx a, cpx b) { return mk(a.x + b.x, a.y + b.y); }
 CRLOT_HD cpx operator-(cpx a, cpx b) { return mk(a.x - b.x, a.y - b.y); }
-CRLOT_HD cpx cmul(cpx a, cpx b) { return mk(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
-CRLOT_HD cpx cmulc(cpx a, cpx b) { return mk(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y); }  // a*conj(b)
-CRLOT_HD cpx conj(cpx a) { return mk(a.x, -a.y); }
-// multiply by -i (forward quarter turn) or +i
-template <bool INV> CRLOT_HD cpx rot90(cpx a) { return INV ? mk(-a.y, a.x) : mk(a.y, -a.x); }
+CRLOT_HD cpx fma2(cpx a, cpx s, cpx c) { return mk(a.x * s.x + c.x, a.y * s.y + c.y); }
+CRLOT_HD cpx mul2(cpx a, cpx s) { return mk(a.x * s.x, a.y * s.y); }
+#endif
 
-// cos(2 pi k/32), sin(2 pi k/32), k = 0..8 (first octant + 1); everything else by symmetry.
+CRLOT_HD cpx swp(cpx a) { return mk(a.y, a.x); }           // .LO_HI operand modifier on the device
+CRLOT_HD cpx splat(float s) { return mk(s, s); }           // .F32 operand modifier on the device
+CRLOT_HD cpx conj(cpx a) { return mk(a.x, -a.y); }
+
+// a*w = a.x*(w.x, w.y) + a.y*(-w.y, w.x)
+CRLOT_HD cpx cmul(cpx a, cpx w) { return fma2(splat(a.y), mk(-w.y, w.x), mul2(splat(a.x), w)); }
+// a*conj(w) = a.x*(w.x, -w.y) + a.y*(w.y, w.x)
+CRLOT_HD cpx cmulc(cpx a, cpx w) { return fma2(splat(a.y), mk(w.y, w.x), mul2(splat(a.x), mk(w.x, -w.y))); }
+// c + a*w  and  c + a*conj(w)
+CRLOT_HD cpx cfma(cpx a, cpx w, cpx c) { return fma2(splat(a.y), mk(-w.y, w.x), fma2(splat(a.x), w, c)); }
+CRLOT_HD cpx cfmac(cpx a, cpx w, cpx c) { return fma2(splat(a.y), mk(w.y, w.x), fma2(splat(a.x), mk(w.x, -w.y), c)); }
+// s + (-i)^(+/-1) * t :  forward uses -i (t.y, -t.x), inverse +i (-t.y, t.x)
+template <bool INV> CRLOT_HD cpx add_rot(cpx s, cpx t) { return fma2(swp(t), INV ? mk(-1.f, 1.f) : mk(1.f, -1.f), s); }
+template <bool INV> CRLOT_HD cpx sub_rot(cpx s, cpx t) { return fma2(swp(t), INV ? mk(1.f, -1.f) : mk(-1.f, 1.f), s); }
+template <bool INV> CRLOT_HD cpx rot90(cpx a) { return mul2(swp(a), INV ? mk(-1.f, 1.f) : mk(1.f, -1.f)); }
+
+// cos(2 pi k/32), k = 0..8; everything else by symmetry.
 #define CRLOT_C32_0 1.0f
 #define CRLOT_C32_1 0.98078528040323044913f
 #define CRLOT_C32_2 0.92387953251128675613f
@@ -50,80 +83,81 @@ template <int K> struct W32 {
     return j == 0 ? CRLOT_C32_0 : j == 1 ? CRLOT_C32_1 : j == 2 ? CRLOT_C32_2 : j == 3 ? CRLOT_C32_3
          : j == 4 ? CRLOT_C32_4 : j == 5 ? CRLOT_C32_5 : j == 6 ? CRLOT_C32_6 : j == 7 ? CRLOT_C32_7 : 0.0f;
   }
-  // angle = -(q*90 + r*11.25) degrees.  base = (cos r, -sin r); each quadrant multiplies by -i.
-  CRLOT_HD static float re() {
-    return q == 0 ? c8(r) : q == 1 ? -c8(8 - r) : q == 2 ? -c8(r) : c8(8 - r);
-  }
-  CRLOT_HD static float im() {
-    return q == 0 ? -c8(8 - r) : q == 1 ? -c8(r) : q == 2 ? c8(8 - r) : c8(r);
-  }
+  CRLOT_HD static float re() { return q == 0 ? c8(r) : q == 1 ? -c8(8 - r) : q == 2 ? -c8(r) : c8(8 - r); }
+  CRLOT_HD static float im() { return q == 0 ? -c8(8 - r) : q == 1 ? -c8(r) : q == 2 ? c8(8 - r) : c8(r); }
+  template <bool INV> CRLOT_HD static cpx w() { return mk(re(), INV ? -im() : im()); }
 };
 
-// a * exp(-/+ 2 pi i K/32) with the free cases folded.
+// The butterfly "a' = a + w b, b' = a - w b" with w = exp(-/+ 2 pi i K/32), trivial cases folded.
+template <int K, bool INV> CRLOT_HD void bfly2w(cpx& a, cpx& b) {
+  constexpr int k = ((K % 32) + 32) % 32;
+  if (k == 0) {
+    const cpx t = a - b;
+    a = a + b;
+    b = t;
+  } else if (k == 8) {
+    const cpx t = sub_rot<INV>(a, b);
+    a = add_rot<INV>(a, b);
+    b = t;
+  } else if (k == 16) {
+    const cpx t = a + b;
+    a = a - b;
+    b = t;
+  } else if (k == 24) {
+    const cpx t = add_rot<INV>(a, b);
+    a = sub_rot<INV>(a, b);
+    b = t;
+  } else {
+    const cpx w = W32<k>::template w<INV>();
+    const cpx t = cmul(b, w);
+    b = a - t;
+    a = a + t;
+  }
+}
+
+// b * exp(-/+ 2 pi i K/32), trivial cases folded (general case: 2 packed instructions)
 template <int K, bool INV> CRLOT_HD cpx mulw32(cpx a) {
   constexpr int k = ((K % 32) + 32) % 32;
   if (k == 0) return a;
   if (k == 8) return rot90<INV>(a);
   if (k == 16) return mk(-a.x, -a.y);
   if (k == 24) return rot90<!INV>(a);
-  if (k == 4) {   // (1 -/+ i)/sqrt2
-    const float h = CRLOT_C32_4;
-    return INV ? mk(h * (a.x - a.y), h * (a.x + a.y)) : mk(h * (a.x + a.y), h * (a.y - a.x));
-  }
-  if (k == 12) {  // (-1 -/+ i)/sqrt2
-    const float h = CRLOT_C32_4;
-    return INV ? mk(-h * (a.x + a.y), h * (a.x - a.y)) : mk(h * (a.y - a.x), -h * (a.x + a.y));
-  }
-  if (k == 20) {
-    const float h = CRLOT_C32_4;
-    return INV ? mk(h * (a.y - a.x), -h * (a.x + a.y)) : mk(-h * (a.x + a.y), h * (a.x - a.y));
-  }
-  if (k == 28) {
-    const float h = CRLOT_C32_4;
-    return INV ? mk(h * (a.x + a.y), h * (a.y - a.x)) : mk(h * (a.x - a.y), h * (a.x + a.y));
-  }
-  const cpx w = mk(W32<k>::re(), INV ? -W32<k>::im() : W32<k>::im());
-  return cmul(a, w);
+  return cmul(a, W32<k>::template w<INV>());
 }
 
-// 4-point butterfly on (a,b,c,d) -> natural order outputs.
+// 4-point butterfly on (a,b,c,d) -> natural order outputs (8 packed instructions).
 template <bool INV> CRLOT_HD void bfly4(cpx& a, cpx& b, cpx& c, cpx& d) {
-  const cpx s0 = a + c, s1 = a - c, s2 = b + d, s3 = rot90<INV>(b - d);
+  const cpx s0 = a + c, s1 = a - c, s2 = b + d, t = b - d;
   a = s0 + s2;
   c = s0 - s2;
-  b = s1 + s3;
-  d = s1 - s3;
+  b = add_rot<INV>(s1, t);
+  d = sub_rot<INV>(s1, t);
 }
 
 template <int R, bool INV> struct Dft;
 
 template <bool INV> struct Dft<2, INV> {
-  CRLOT_HD static void run(cpx (&v)[2]) {
-    const cpx t = v[0] - v[1];
-    v[0] = v[0] + v[1];
-    v[1] = t;
-  }
+  CRLOT_HD static void run(cpx (&v)[2]) { bfly2w<0, INV>(v[0], v[1]); }
 };
 template <bool INV> struct Dft<4, INV> {
   CRLOT_HD static void run(cpx (&v)[4]) { bfly4<INV>(v[0], v[1], v[2], v[3]); }
 };
-
-// R = 4*M, decimation in time: four M-point transforms of x[4j+q], twiddle, M radix-4 butterflies.
-// R = 8 uses radix 2 on two 4-point transforms.
+// R = 8: radix 2 on two 4-point transforms, twiddles fused into the butterflies.
 template <bool INV> struct Dft<8, INV> {
   CRLOT_HD static void run(cpx (&v)[8]) {
     cpx e[4] = {v[0], v[2], v[4], v[6]};
     cpx o[4] = {v[1], v[3], v[5], v[7]};
     Dft<4, INV>::run(e);
     Dft<4, INV>::run(o);
-    const cpx t0 = o[0], t1 = mulw32<4, INV>(o[1]), t2 = mulw32<8, INV>(o[2]), t3 = mulw32<12, INV>(o[3]);
-    v[0] = e[0] + t0; v[4] = e[0] - t0;
-    v[1] = e[1] + t1; v[5] = e[1] - t1;
-    v[2] = e[2] + t2; v[6] = e[2] - t2;
-    v[3] = e[3] + t3; v[7] = e[3] - t3;
+    bfly2w<0, INV>(e[0], o[0]);
+    bfly2w<4, INV>(e[1], o[1]);
+    bfly2w<8, INV>(e[2], o[2]);
+    bfly2w<12, INV>(e[3], o[3]);
+    v[0] = e[0]; v[1] = e[1]; v[2] = e[2]; v[3] = e[3];
+    v[4] = o[0]; v[5] = o[1]; v[6] = o[2]; v[7] = o[3];
   }
 };
-
+// R = 4*M (16, 32): four M-point transforms of x[4j+q], twiddle, M radix-4 butterflies.
 template <int R, bool INV> struct Dft {
   static constexpr int M = R / 4;
   static constexpr int S = 32 / R;   // twiddle stride in units of 2 pi/32
@@ -152,8 +186,7 @@ template <int R, bool INV> struct Dft {
   }
 };
 
-// DFT over a strided sub-array living inside a larger register file: elements
-// v[OFF + STRIDE*i], i < R.
+// DFT over a strided sub-array living inside a larger register file: v[OFF + STRIDE*i], i < R.
 template <int R, bool INV, int OFF, int STRIDE, int TOTAL> CRLOT_HD void dft_sub(cpx (&v)[TOTAL]) {
   cpx t[R];
 #pragma unroll

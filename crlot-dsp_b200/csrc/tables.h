@@ -9,8 +9,7 @@ namespace crlot {
 struct FftTables {
   int nfft = 0, C = 0, A = 0, B = 0;
   std::vector<float> tw1;   // [B][A] cpx : exp(-2 pi i a*ob / C)      inter-pass twiddle (forward)
-  std::vector<float> st;    // [C]    cpx : 0.5*exp(-i pi (k/C + 1/2)) forward real split
-  std::vector<float> su;    // [C]    cpx : exp(+i pi (k/C + 1/2))     inverse real split
+  std::vector<float> sa;    // [C]    cpx : 0.5*(1 + exp(-i pi (k/C + 1/2)))  real split (inverse uses conj)
   std::vector<float> pre;   // [1024] cpx : exp(-2 pi i n / 2048)      N=4096 radix-2 pre-stage
 };
 
@@ -35,14 +34,11 @@ inline FftTables make_fft_tables(int nfft) {
       t.tw1[2 * (ob * t.A + a)] = (float)std::cos(ph);
       t.tw1[2 * (ob * t.A + a) + 1] = (float)std::sin(ph);
     }
-  t.st.resize(2 * (size_t)t.C);
-  t.su.resize(2 * (size_t)t.C);
+  t.sa.resize(2 * (size_t)t.C);
   for (int k = 0; k < t.C; ++k) {
-    const double ph = pi * ((double)k / (double)t.C + 0.5);
-    t.st[2 * k] = (float)(0.5 * std::cos(-ph));
-    t.st[2 * k + 1] = (float)(0.5 * std::sin(-ph));
-    t.su[2 * k] = (float)std::cos(ph);
-    t.su[2 * k + 1] = (float)std::sin(ph);
+    const double ph = -pi * ((double)k / (double)t.C + 0.5);
+    t.sa[2 * k] = (float)(0.5 * (1.0 + std::cos(ph)));
+    t.sa[2 * k + 1] = (float)(0.5 * std::sin(ph));
   }
   if (nfft == 4096) {
     t.pre.resize(2 * 1024);

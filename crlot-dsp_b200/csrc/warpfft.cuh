@@ -102,13 +102,15 @@ template <class X> CRLOT_HD void out_coord(int lane, int r, int& g, int& o) {
 // A-1-oa, except for ob == 0 where it is the lane's own register (A-oa)%A.  Same algebra
 // with (A,a,b) for the pass-1 view.
 //
-// Forward (after pass 2), k = o:   X[k] = 0.5*(Z[k] + conj(Z[C-k])) + 0.5*t_k*(Z[k] - conj(Z[C-k])),
-//   t_k = exp(-i pi (k/C + 1/2))      (kiss_fftr.c:53-59,101-116 of the reference, restated)
+// Forward (after pass 2), k = o, M = Z[C-k]:
+//   X[k] = 0.5*(Z + conj M) + 0.5*t_k*(Z - conj M),  t_k = exp(-i pi (k/C + 1/2))
+//        = conj(M) + A_k*(Z - conj M),               A_k = 0.5*(1 + t_k)
+//   (kiss_fftr.c:53-59,101-116 of the reference, restated; 5 packed instructions per bin)
 //   k = 0 gives X[0] = Re+Im, X[C] = Re-Im with exactly zero imaginary parts.
-// st[] is the table st[k] = 0.5*t_k, k in [0,C)  (the 0.5 folded in).
+// sa[] is the table sa[k] = A_k, k in [0,C).
 // `peer(r)` returns register r of the partner lane (a warp shuffle on the device).
 template <class X, class Peer>
-CRLOT_HD void fwd_split(cpx (&v)[32], int lane, const cpx* st, Peer peer, cpx (&nyq)[X::M2]) {
+CRLOT_HD void fwd_split(cpx (&v)[32], int lane, const cpx* sa, Peer peer, cpx (&nyq)[X::M2]) {
   cpx out[32];
 #pragma unroll
   for (int j = 0; j < X::M2; ++j) {
@@ -119,31 +121,32 @@ CRLOT_HD void fwd_split(cpx (&v)[32], int lane, const cpx* st, Peer peer, cpx (&
       const cpx far = peer(j * X::A + (X::A - 1 - oa));
       const cpx own = v[j * X::A + (X::A - oa) % X::A];
       const cpx m = (ob == 0) ? own : far;                   // Z[C-k]
-      const cpx e = mk(z.x + m.x, z.y - m.y);                // Z + conj(M)
-      const cpx d = mk(z.x - m.x, z.y + m.y);                // Z - conj(M)
-      const cpx t = cmul(d, st[ob + X::B * oa]);             // 0.5*t_k*d
-      out[j * X::A + oa] = mk(0.5f * e.x + t.x, 0.5f * e.y + t.y);
+      const cpx ds = fma2(m, mk(-1.f, 1.f), z);              // Z - conj(M)
+      const cpx mc = mul2(m, mk(1.f, -1.f));                 // conj(M)
+      out[j * X::A + oa] = cfma(ds, sa[ob + X::B * oa], mc);
     }
   }
 #pragma unroll
   for (int j = 0; j < X::M2; ++j) {
     const int ob = (lane + 32 * j) % X::B;
-    if (ob == 0) {   // k = 0 of frame g: exact DC and Nyquist
+    if (ob == 0) {   // k = 0 of frame g: exact DC and Nyquist (ob = lane % B for every j)
       const cpx z = v[j * X::A];
       out[j * X::A] = mk(z.x + z.y, 0.0f);
-      nyq[j] = mk(z.x - z.y, 0.0f);   // ob = lane % B for every j: each item of this lane has its own
+      nyq[j] = mk(z.x - z.y, 0.0f);
     }
   }
 #pragma unroll
   for (int r = 0; r < 32; ++r) v[r] = out[r];
 }
 
-// Inverse (before pass 1), k = i:  Z'[k] = (X[k] + conj(X[C-k])) + u_k*(X[k] - conj(X[C-k])),
-//   u_k = exp(+i pi (k/C + 1/2))      (kiss_fftr.c:119-155 restated); k = 0 uses only the real
-//   parts of X[0] and X[C]:  Z'[0] = (X0.r + XC.r, X0.r - XC.r).
-// su[] is the table su[k] = u_k, k in [0,C).
+// Inverse (before pass 1), k = i, M = X[C-k]:
+//   Z'[k] = (X + conj M) + u_k*(X - conj M),  u_k = exp(+i pi (k/C + 1/2)) = conj(t_k)
+//   Z'[k]/2 = conj(M) + conj(A_k)*(X - conj M)
+//   (kiss_fftr.c:119-155 restated).  The HALVED values are produced (exact power-of-two
+//   scaling) and the caller folds the 2 into its final 1/N scale.  k = 0 uses only the real
+//   parts of X[0] and X[C]:  Z'[0]/2 = ((X0.r + XC.r)/2, (X0.r - XC.r)/2).
 template <class X, class Peer>
-CRLOT_HD void inv_split(cpx (&v)[32], int lane, const cpx* su, Peer peer, const cpx (&nyq)[X::M1]) {
+CRLOT_HD void inv_split(cpx (&v)[32], int lane, const cpx* sa, Peer peer, const cpx (&nyq)[X::M1]) {
   cpx out[32];
 #pragma unroll
   for (int j = 0; j < X::M1; ++j) {
@@ -154,12 +157,11 @@ CRLOT_HD void inv_split(cpx (&v)[32], int lane, const cpx* su, Peer peer, const 
       const cpx far = peer(j * X::B + (X::B - 1 - b));
       const cpx own = v[j * X::B + (X::B - b) % X::B];
       const cpx m = (a == 0) ? own : far;                    // X[C-k]
-      const cpx e = mk(x.x + m.x, x.y - m.y);
-      const cpx d = mk(x.x - m.x, x.y + m.y);
-      const cpx t = cmul(d, su[a + X::A * b]);
-      out[j * X::B + b] = e + t;
+      const cpx ds = fma2(m, mk(-1.f, 1.f), x);
+      const cpx mc = mul2(m, mk(1.f, -1.f));
+      out[j * X::B + b] = cfmac(ds, sa[a + X::A * b], mc);
     }
-    if (a == 0) out[j * X::B] = mk(v[j * X::B].x + nyq[j].x, v[j * X::B].x - nyq[j].x);
+    if (a == 0) out[j * X::B] = mk(0.5f * (v[j * X::B].x + nyq[j].x), 0.5f * (v[j * X::B].x - nyq[j].x));
   }
 #pragma unroll
   for (int r = 0; r < 32; ++r) v[r] = out[r];

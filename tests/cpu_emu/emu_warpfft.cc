@@ -22,8 +22,8 @@ template <int NFFT> static int run() {
   const int C = X::C, G = X::G, N = NFFT;
   FftTables T = make_fft_tables(N);
   const cpx* tw1 = reinterpret_cast<const cpx*>(T.tw1.data());
-  const cpx* st = reinterpret_cast<const cpx*>(T.st.data());
-  const cpx* su = reinterpret_cast<const cpx*>(T.su.data());
+  const cpx* st = reinterpret_cast<const cpx*>(T.sa.data());
+  const cpx* su = st;
   std::vector<std::vector<float>> x(G, std::vector<float>(N));
   for (auto& f : x) for (auto& s : f) s = (float)frand();
   // reference spectra in double
@@ -98,7 +98,7 @@ template <int NFFT> static int run() {
   for (int l = 0; l < 32; ++l)
     for (int r = 0; r < 32; ++r) {
       int g, o; out_coord<X>(l, r, g, o);
-      const double y0 = v[l][r].x / (double)N, y1 = v[l][r].y / (double)N;
+      const double y0 = 2.0 * v[l][r].x / (double)N, y1 = 2.0 * v[l][r].y / (double)N;   // inv_split yields halves
       err += (y0 - x[g][2 * o]) * (y0 - x[g][2 * o]) + (y1 - x[g][2 * o + 1]) * (y1 - x[g][2 * o + 1]);
       nrm += (double)x[g][2 * o] * x[g][2 * o] + (double)x[g][2 * o + 1] * x[g][2 * o + 1];
     }
