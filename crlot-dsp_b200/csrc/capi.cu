@@ -149,6 +149,8 @@ struct crlot_plan_s {
   DevArr<float> win_a, win_s, env;
   DevArr<cpx> tw1, sa, pre;
   DevArr<unsigned int> counter;
+  int k1_scrub = 0;            // kernel-1 clean-up mode (kernels.h)
+  unsigned int tiny2 = 0;
   std::vector<float> env_host;
   HostSlot slot[2];
   long long slot_frames = 0;   // capacity of the host-path workspace, in frames
@@ -282,6 +284,31 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
   std::vector<float> wa(N, 1.0f);
   if (desc->analysis_window) std::copy(desc->analysis_window, desc->analysis_window + N, wa.begin());
   CU(p->win_a.upload(wa.data(), N));
+  // Kernel-1 clean-up mode.  Screening (mode 2) is exact when every windowed product that the
+  // reference rule would alter comes from a raw sample that is non-finite or 0 < |x| < thr with
+  // thr = 1e-30 / min non-zero |w| (plus a relative margin for the rounding of x*w); it needs
+  // |w| <= 1 (no overflow of finite samples) and finite window values.
+  p->k1_scrub = desc->scrub ? 1 : 0;
+  if (desc->scrub) {
+    float wmin = 0.0f, wmax = 0.0f;
+    bool finite = true;
+    for (float v : wa) {
+      const float a = std::fabs(v);
+      if (!std::isfinite(v)) finite = false;
+      if (a > 0.0f && (wmin == 0.0f || a < wmin)) wmin = a;
+      wmax = std::max(wmax, a);
+    }
+    if (finite && wmax <= 1.0f && wmin > 0.0f) {
+      const double thr = 1e-30 / static_cast<double>(wmin) * (1.0 + 1e-5);
+      if (thr < 1e30) {
+        const float t = static_cast<float>(thr);
+        unsigned int bits;
+        std::memcpy(&bits, &t, 4);
+        p->tiny2 = 2u * bits - 2u;
+        p->k1_scrub = 2;
+      }
+    }
+  }
   // synthesis window policy, ref: OLAAccumulator.cc:82-83
   const float* ws = desc->apply_window_inside ? desc->ola_window : desc->push_window;
   p->syn_active = ws != nullptr;
@@ -339,7 +366,7 @@ int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_
   k.nfft = plan->d.nfft; k.hop = plan->d.hop;
   k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
   k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p;
-  k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->d.scrub;
+  k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
   CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
@@ -431,7 +458,7 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
       K1Params k1{};
       k1.sig = s.in.p; k1.chan_stride = 0; k1.len = s1 - s0; k1.channels = 1; k1.frames = nf; k1.nfft = N; k1.hop = H;
       k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p;
-      k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->d.scrub;
+      k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2;
       CU(launch_stft_fwd(k1, s.stream));
       K2Params k2{};
       k2.spec = s.spec.p; k2.rows = nf; k2.nfft = N; k2.frames = s.frames.p;

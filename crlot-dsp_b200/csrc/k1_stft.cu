@@ -68,7 +68,14 @@ __device__ __forceinline__ void ring_fill(float* ring, int mask, const float* si
   }
 }
 
-template <int NFFT, bool SCRUB>
+// SCRUB: 0 = none; 1 = the reference clean-up rule applied to every windowed sample;
+//        2 = same results as 1, but samples are SCREENED once, when they first enter the ring
+//            (requires nfft == 4*hop): a raw sample can only make a windowed product that the
+//            rule would change if it is non-finite or 0 < |x| < tiny_thr (= 1e-30 / smallest
+//            non-zero |window|, set by the host).  Only the registers holding the newest hop are
+//            screened (2 integer ops + half a packed FMA per sample); when a warp sees a suspect
+//            it applies rule 1 to whole frames until the suspect has left the ring.
+template <int NFFT, int SCRUB>
 __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Params p, const int rcap) {
   using X = GeoX<NFFT>;
   constexpr int C = X::C, G = X::G, A = X::A, B = X::B;
@@ -124,6 +131,7 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
     long long pos = first * H;
     const int nsteps = static_cast<int>((nfr + G - 1) / G);
 
+    int dirty = 0;
     __syncwarp();
     ring_fill(ring, mask, sig, p.len, pos, S, bar, lane);
 
@@ -133,16 +141,36 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
       __syncwarp();
 
       cpx v[32];
+      unsigned int wmin = 0xffffffffu;       // min over screened samples of 2*|bits| - 2 (0 maps to max)
+      cpx nf = mk(0.f, 0.f);                 // sum of 0*x: becomes NaN iff a screened sample is NaN/Inf
 #pragma unroll
       for (int j = 0; j < X::M1; ++j) {
+        // frames of this item across lanes: g in [32j/A, (31+32j)/A]; newest hop of frame g
+        // starts at point (3-g)*C/4 (nfft == 4*hop), i.e. register b >= (3-g)*B/4
+        const int g_hi = (31 + 32 * j) / A;
+        const int newb = g_hi >= 3 ? 0 : (3 - g_hi) * B / 4;
 #pragma unroll
         for (int b = 0; b < B; ++b) {
           const int ridx = static_cast<int>((pos + in_off[j] + 2 * A * b) & mask);
           const cpx x = *reinterpret_cast<const cpx*>(ring + ridx);
           const cpx w = *reinterpret_cast<const cpx*>(s_win + 2 * a_lane + 2 * A * b);
           cpx pw = mul2(x, w);                 // one rounding per sample, as frame[i]*window[i]
-          if (SCRUB) pw = mk(scrub(pw.x), scrub(pw.y));
+          if (SCRUB == 1) pw = mk(scrub(pw.x), scrub(pw.y));
+          if (SCRUB == 2 && b >= newb) {
+            const unsigned int u0 = __float_as_uint(x.x), u1 = __float_as_uint(x.y);
+            wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));   // sign bit leaves by wrap-around
+            nf = fma2(x, mk(0.f, 0.f), nf);
+          }
           v[j * B + b] = pw;
+        }
+      }
+      if (SCRUB == 2) {
+        const bool suspect = (wmin < p.tiny2) || (nf.x != 0.0f) || (nf.y != 0.0f);
+        if (__any_sync(0xffffffffu, suspect)) dirty = 3 / G + 2;
+        if (dirty > 0 || s == 0) {             // s == 0: the whole ring is new
+#pragma unroll
+          for (int r = 0; r < 32; ++r) v[r] = mk(scrub(v[r].x), scrub(v[r].y));
+          if (dirty > 0) --dirty;
         }
       }
       __syncwarp();
@@ -186,7 +214,9 @@ cudaError_t launch_k1(const K1Params& p, cudaStream_t st) {
   const int rcap = next_pow2(S);
   const int smem = K1Smem<NFFT>::total(rcap, kK1Warps);
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-  auto kern = p.scrub ? stft_fwd_kernel<NFFT, true> : stft_fwd_kernel<NFFT, false>;
+  // screening mode needs nfft == 4*hop and a finite threshold; otherwise the per-sample rule
+  const int mode = !p.scrub ? 0 : (p.scrub == 2 && NFFT == 4 * p.hop) ? 2 : 1;
+  auto kern = mode == 0 ? stft_fwd_kernel<NFFT, 0> : mode == 1 ? stft_fwd_kernel<NFFT, 1> : stft_fwd_kernel<NFFT, 2>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);

@@ -27,7 +27,8 @@ struct K1Params {
   const cpx* pre;            // nfft == 4096 only
   unsigned int* counter;     // zeroed work counter (dynamic chunk scheduling)
   int chunk_steps;           // steps (of G frames) per scheduled chunk
-  int scrub;                 // apply the adapter's NaN/Inf/tiny clean-up to the windowed input
+  int scrub;                 // 0 none, 1 reference clean-up on every windowed sample, 2 same via screening
+  unsigned int tiny2;        // scrub == 2: 2*bits(tiny_thr) - 2 (see k1_stft.cu)
 };
 cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st);
 

@@ -248,3 +248,31 @@ def test_large_signal_properties(cuda, dsp, oracle):
     xh = x[0, : (1 << 22) + 777].cpu().numpy()
     o_dev = plan.roundtrip(dev(cuda, xh))[0].cpu().numpy()
     assert np.array_equal(bits(plan.roundtrip_host(xh)), bits(o_dev))
+
+
+@pytest.mark.parametrize("N,H", [(2048, 512), (1024, 256), (512, 128), (256, 64), (1024, 512)])
+def test_k1_cleanup_inside_a_stream(cuda, dsp, oracle, N, H):
+    """NaN / +-Inf / sub-1e-30 samples scattered through a long stream: every frame that contains one
+    must come out exactly as the reference's per-sample clean-up makes it (kernel 1 screens samples
+    once, on entry, when nfft == 4*hop; the (1024,512) case runs the per-sample rule)."""
+    rng = np.random.default_rng(N + H)
+    L = 300 * H + N
+    x = rng.uniform(-1, 1, L).astype(np.float32)
+    w = oracle.window(po.HANN, N)
+    bad = {5: np.nan, 3 * H + 17: np.inf, 3 * H + 18: -np.inf, 40 * H: 1e-33, 40 * H + 1: -3e-36, 41 * H - 1: 1e-39,
+           100 * H + N // 2: np.nan, 200 * H + 1: 1e-27, 250 * H: 3e38, L - 2: np.inf, 64 * H + 5: 2e-31}
+    for i, v in bad.items():
+        x[i] = v
+    x[150 * H:150 * H + N] = 0.0
+    x[150 * H + 7] = 1e-32
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w)
+    S = plan.stft(dev(cuda, x)).cpu().numpy()[0]
+    with np.errstate(invalid="ignore", over="ignore"):
+        ref = oracle.rfft_many(oracle.framer(x, N, H, 1, po.DROP) * w, N)
+    assert np.isfinite(S.view(np.float32)).all()
+    for k in range(S.shape[0]):
+        den = np.linalg.norm(ref[k])
+        err = np.linalg.norm(S[k] - ref[k])
+        assert (err / den < TOL) if den > 0 else (err == 0), k
+    # the all-zero-but-one-tiny frame comes out exactly zero, as the reference's does
+    assert not ref[150].any() and not S[150].any()
