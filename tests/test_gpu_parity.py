@@ -260,7 +260,7 @@ def test_k1_cleanup_inside_a_stream(cuda, dsp, oracle, N, H):
     x = rng.uniform(-1, 1, L).astype(np.float32)
     w = oracle.window(po.HANN, N)
     bad = {5: np.nan, 3 * H + 17: np.inf, 3 * H + 18: -np.inf, 40 * H: 1e-33, 40 * H + 1: -3e-36, 41 * H - 1: 1e-39,
-           100 * H + N // 2: np.nan, 200 * H + 1: 1e-27, 250 * H: 3e38, L - 2: np.inf, 64 * H + 5: 2e-31}
+           100 * H + N // 2: np.nan, 200 * H + 1: 1e-27, 250 * H: 1e30, L - 2: np.inf, 64 * H + 5: 2e-31}
     for i, v in bad.items():
         x[i] = v
     x[150 * H:150 * H + N] = 0.0
