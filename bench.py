@@ -117,7 +117,7 @@ class Clocks:
 
     def start(self):
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                                        "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.p = None
@@ -201,11 +201,12 @@ def main():
         x = dsp.synth_uniform(chans, L, seed=SEED, channel0=rank * chans, device=local)
         local_samples = chans * L
         scaling = "strong"
-    else:  # c4: rank r owns output/time range [r*S, (r+1)*S); receives N-H input samples from BOTH neighbours
+    else:  # c4: rank r owns the output/time range [r*S, (r+1)*S); halos from BOTH neighbours (sharding.py)
+        from crlot_dsp_b200 import sharding
         chans, batch = 1, 1
         S = wl["length"]
-        left = halo if rank > 0 else 0
-        right = halo if rank < world - 1 else 0
+        sh = sharding.make_time_shard(S * world, N, H, rank, world)
+        left, right = sh.left_halo, sh.right_halo
         xbuf = torch.zeros(left + S + right, dtype=torch.float32, device=dev)
         dsp.synth_uniform(1, S, seed=SEED, channel0=0, i0=rank * S, device=local, out=xbuf[left:left + S].unsqueeze(0))
         local_samples = S
@@ -213,25 +214,12 @@ def main():
 
     def halo_exchange():
         """NCCL send/recv of the (frame-hop)-sample halos between neighbouring ranks."""
-        ops = []
-        if rank > 0:
-            ops.append(dist.P2POp(dist.isend, xbuf[left:left + halo], rank - 1))
-            ops.append(dist.P2POp(dist.irecv, xbuf[:left], rank - 1))
-        if rank < world - 1:
-            ops.append(dist.P2POp(dist.isend, xbuf[left + S - halo:left + S], rank + 1))
-            ops.append(dist.P2POp(dist.irecv, xbuf[left + S:], rank + 1))
-        if ops:
-            for r in dist.batch_isend_irecv(ops):
-                r.wait()
+        sharding.halo_exchange(xbuf, sh)
 
     # workspaces
     if args.workload == "c4":
         Ltot = left + S + right
-        # local frames: global frame k with k*H in [r*S - halo, (r+1)*S) (left-halo frames are recomputed so
-        # every rank sums the same terms in the same order as one GPU would); last rank follows DROP
-        F = dsp.frame_count(Ltot, N, H, dsp.DROP) if rank == world - 1 else (Ltot - halo) // H if right else dsp.frame_count(Ltot, N, H, dsp.DROP)
-        F = min(F, dsp.frame_count(Ltot, N, H, dsp.DROP))
-        n_out = S if rank < world - 1 else (F - 1) * H + N - left
+        F, n_out = sh.n_frames, sh.n_out
         spec = torch.empty((1, F, plan.bins), dtype=torch.complex64, device=dev)
         frames = torch.empty((1, F, N), dtype=torch.float32, device=dev)
         out = torch.empty((1, n_out), dtype=torch.float32, device=dev)
@@ -255,7 +243,7 @@ def main():
             if record: e[1].record()
             plan.istft_frames(spec, fuse_synthesis_window=True, out=frames)
             if record: e[2].record()
-            plan.ola(frames, prewindowed=True, t_offset=rank * S, frame_t0=-left, n_out=n_out, out=out)
+            plan.ola(frames, prewindowed=True, t_offset=sh.t0, frame_t0=sh.frame_t0, n_out=n_out, out=out)
             if record: e[3].record()
             if record:
                 kt["_ev"].append(e)

@@ -50,6 +50,13 @@ __device__ __forceinline__ void ring_fill(float* ring, int mask, const float* si
   if (avail < 0) avail = 0;
   if (avail > count) avail = count;
   const int nb = static_cast<int>(avail) & ~3;
+  if (nb < count) {   // only at the tail of a channel
+    for (int i = nb + lane; i < count; i += 32) {
+      const long long a = abs0 + i;
+      ring[a & mask] = (a < len) ? __ldg(sig + a) : 0.0f;
+    }
+    __syncwarp();     // the tail is in place before the barrier phase can complete
+  }
   if (lane == 0) {
     fence_proxy_async_smem();
     mbar_arrive_expect_tx(bar, static_cast<uint32_t>(nb) * 4u);
@@ -58,12 +65,6 @@ __device__ __forceinline__ void ring_fill(float* ring, int mask, const float* si
       const int first = min(nb, mask + 1 - r0);
       bulk_g2s(smem_u32(ring + r0), sig + abs0, static_cast<uint32_t>(first) * 4u, bar);
       if (nb > first) bulk_g2s(smem_u32(ring), sig + abs0 + first, static_cast<uint32_t>(nb - first) * 4u, bar);
-    }
-  }
-  if (nb < count) {   // only at the tail of a channel
-    for (int i = nb + lane; i < count; i += 32) {
-      const long long a = abs0 + i;
-      ring[a & mask] = (a < len) ? __ldg(sig + a) : 0.0f;
     }
   }
 }
@@ -207,6 +208,127 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
   }
 }
 
+// ---- N = 4096: two warps per frame (warpfft.cuh "N = 4096") ------------------------------------
+// A warp pair shares one ring (the frame's 4096 samples) and one mbarrier; parity 0 transforms
+// z[n]+z[n+1024] into the even bins, parity 1 transforms (z[n]-z[n+1024])*W_2048^n into the odd
+// bins.  The only coupling between the two warps is a 64-thread named barrier per step ("both
+// have read the ring") and the shared chunk index.
+constexpr int kK1Warps4096 = 10;
+
+__device__ __forceinline__ void pair_sync(int pair) {
+  asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+}
+
+template <bool SCRUB>
+__global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(const K1Params p) {
+  using X = GeoX<2048>;                      // the 1024-point machinery
+  constexpr int NFFT = 4096, CB = 2048, RCAP = 4096, NPAIR = kK1Warps4096 / 2;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* s_win = reinterpret_cast<float*>(smem_raw);
+  cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
+  cpx* s_sa = s_tw1 + 1024;
+  cpx* s_pre = s_sa + CB;
+  float* rings = reinterpret_cast<float*>(s_pre + 1024);
+  cpx* exs = reinterpret_cast<cpx*>(rings + NPAIR * RCAP);
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(exs + kK1Warps4096 * X::XCPX);
+  unsigned int* pair_q = reinterpret_cast<unsigned int*>(bars + NPAIR);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, pair = warp >> 1, parity = warp & 1;
+  float* ring = rings + pair * RCAP;
+  cpx* ex = exs + warp * X::XCPX;
+  const uint32_t bar = smem_u32(bars + pair);
+  constexpr int mask = RCAP - 1;
+
+  for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+  for (int i = threadIdx.x; i < CB; i += blockDim.x) s_sa[i] = p.sa[i];
+  for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
+    s_tw1[i] = p.tw1[i];
+    s_pre[i] = p.pre[i];
+  }
+  if (parity == 0 && lane == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const int H = p.hop;
+  const long long frames_per_chunk = p.chunk_steps;
+  const long long chunks_per_chan = (p.frames + frames_per_chunk - 1) / frames_per_chunk;
+  const long long total_chunks = chunks_per_chan * p.channels;
+  const int lp = parity == 0 ? mirror_lane<32>(lane) : 31 - lane;
+  uint32_t phase = 0;
+
+  for (;;) {
+    if (parity == 0 && lane == 0) pair_q[pair] = atomicAdd(p.counter, 1u);
+    pair_sync(pair);                         // chunk index published; previous chunk's ring reads done
+    const long long q = *reinterpret_cast<volatile unsigned int*>(pair_q + pair);
+    if (q >= total_chunks) break;
+    const long long c = q / chunks_per_chan;
+    const long long first = (q % chunks_per_chan) * frames_per_chunk;
+    const int nsteps = static_cast<int>(min(frames_per_chunk, p.frames - first));
+    const float* sig = p.sig + c * p.chan_stride;
+    cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (CB + 1);
+    long long pos = first * H;
+    if (parity == 0) ring_fill(ring, mask, sig, p.len, pos, NFFT, bar, lane);
+
+    for (int s = 0; s < nsteps; ++s) {
+      mbar_wait(bar, phase);
+      phase ^= 1u;
+      __syncwarp();
+      cpx v[32];
+#pragma unroll
+      for (int b = 0; b < 32; ++b) {
+        const int n = lane + 32 * b;
+        const cpx x0 = *reinterpret_cast<const cpx*>(ring + ((pos + 2 * n) & mask));
+        const cpx x1 = *reinterpret_cast<const cpx*>(ring + ((pos + 2 * n + 2048) & mask));
+        cpx p0 = mul2(x0, *reinterpret_cast<const cpx*>(s_win + 2 * n));
+        cpx p1 = mul2(x1, *reinterpret_cast<const cpx*>(s_win + 2 * n + 2048));
+        if (SCRUB) {
+          p0 = mk(scrub(p0.x), scrub(p0.y));
+          p1 = mk(scrub(p1.x), scrub(p1.y));
+        }
+        v[b] = parity == 0 ? p0 + p1 : cmul(p0 - p1, s_pre[n]);
+      }
+      pair_sync(pair);                       // both warps have read the ring
+      if (parity == 0 && s + 1 < nsteps) ring_fill(ring, mask, sig, p.len, pos + NFFT, H, bar, lane);
+
+      pass1<X, false>(v);
+      twiddle1<X, false>(v, lane, s_tw1);
+      xchg_write<X>(v, lane, ex);
+      __syncwarp();
+      xchg_read<X>(v, lane, ex);
+      __syncwarp();
+      pass2<X, false>(v);
+      cpx nyq = mk(0.f, 0.f);
+      fwd_split_4096(v, lane, parity, s_sa,
+                     [&](int r) {
+                       return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
+                     },
+                     nyq);
+#pragma unroll
+      for (int oa = 0; oa < 32; ++oa) stg_stream(spec + 2 * (lane + 32 * oa) + parity, v[oa]);
+      if (parity == 0 && lane == 0) stg_stream(spec + CB, nyq);
+      pos += H;
+      spec += CB + 1;
+    }
+  }
+}
+
+static cudaError_t launch_k1_4096(const K1Params& p, cudaStream_t st) {
+  using X = GeoX<2048>;
+  constexpr int NPAIR = kK1Warps4096 / 2;
+  const int smem = 4096 * 4 + 1024 * 8 + 2048 * 8 + 1024 * 8 + NPAIR * 4096 * 4 + kK1Warps4096 * X::XCPX * 8 + NPAIR * 8 + NPAIR * 4 + 16;
+  auto kern = p.scrub ? stft_fwd_kernel_4096<true> : stft_fwd_kernel_4096<false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
+  if (e != cudaSuccess) return e;
+  const long long total_chunks = ((p.frames + p.chunk_steps - 1) / p.chunk_steps) * p.channels;
+  const long long want_blocks = (total_chunks + NPAIR - 1) / NPAIR;
+  const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
+  kern<<<grid > 0 ? grid : 1, kK1Warps4096 * 32, smem, st>>>(p);
+  return cudaGetLastError();
+}
+
 template <int NFFT>
 cudaError_t launch_k1(const K1Params& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
@@ -238,6 +360,7 @@ cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st) {
     case 512: return launch_k1<512>(p, st);
     case 1024: return launch_k1<1024>(p, st);
     case 2048: return launch_k1<2048>(p, st);
+    case 4096: return launch_k1_4096(p, st);
     default: return cudaErrorNotSupported;
   }
 }

@@ -96,6 +96,88 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
   }
 }
 
+// ---- N = 4096: two independent warps per frame (warpfft.cuh "N = 4096") -------------------------
+// Work item = (row, parity).  Each warp reads X[k], X[k+1024] and the mirrors X[2048-k], X[1024-k]
+// straight from global memory (both orders are contiguous across the lanes; the second touch of a
+// line hits L1/L2), builds its half of the radix-2 pre-stage, runs the 1024-point inverse and
+// writes samples 4n+2*parity, 4n+2*parity+1.  No communication between the two warps.
+template <bool WIN, bool SCRUB>
+__global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel_4096(const K2Params p) {
+  using X = GeoX<2048>;
+  constexpr int NFFT = 4096, CB = 2048;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* s_win = reinterpret_cast<float*>(smem_raw);
+  cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
+  cpx* s_sa = s_tw1 + 1024;
+  cpx* s_pre = s_sa + CB;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  cpx* ex = s_pre + 1024 + warp * X::XCPX;
+  if (WIN)
+    for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+  for (int i = threadIdx.x; i < CB; i += blockDim.x) s_sa[i] = p.sa[i];
+  for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
+    s_tw1[i] = p.tw1[i];
+    s_pre[i] = p.pre[i];
+  }
+  __syncthreads();
+  const long long total_items = p.rows * 2;
+  const long long stride = static_cast<long long>(gridDim.x) * kK2Warps;
+  const float scale = 2.0f / static_cast<float>(NFFT);
+  for (long long item = static_cast<long long>(blockIdx.x) * kK2Warps + warp; item < total_items; item += stride) {
+    const long long rowi = item >> 1;
+    const int parity = static_cast<int>(item & 1);
+    const cpx* row = p.spec + rowi * (CB + 1);
+    cpx v[32];
+#pragma unroll
+    for (int b = 0; b < 32; ++b) {
+      const int k = lane + 32 * b;
+      const cpx xlo = row[k];
+      const cpx mlo = row[2048 - k];
+      const cpx xhi = row[k + 1024];
+      const cpx mhi = row[1024 - k];
+      v[b] = inv_pre_4096(k, parity, xlo, mlo, xhi, mhi, s_sa[k], s_sa[k + 1024], s_pre[k]);
+    }
+    pass1<X, true>(v);
+    twiddle1<X, true>(v, lane, s_tw1);
+    __syncwarp();
+    xchg_write<X>(v, lane, ex);
+    __syncwarp();
+    xchg_read<X>(v, lane, ex);
+    pass2<X, true>(v);
+    float* dst = p.frames + rowi * NFFT + 2 * parity;
+#pragma unroll
+    for (int oa = 0; oa < 32; ++oa) {
+      const int n = lane + 32 * oa;
+      float y0 = v[oa].x * scale, y1 = v[oa].y * scale;
+      if (SCRUB) {
+        y0 = scrub(y0);
+        y1 = scrub(y1);
+      }
+      if (WIN) {
+        const float2 w = *reinterpret_cast<const float2*>(s_win + 4 * n + 2 * parity);
+        y0 = __fmul_rn(y0, w.x);
+        y1 = __fmul_rn(y1, w.y);
+      }
+      stg_stream(reinterpret_cast<cpx*>(dst + 4 * n), mk(y0, y1));
+    }
+  }
+}
+
+static cudaError_t launch_k2_4096(const K2Params& p, cudaStream_t st) {
+  using X = GeoX<2048>;
+  const bool win = p.window != nullptr;
+  const int smem = (win ? 4096 * 4 : 0) + 1024 * 8 + 2048 * 8 + 1024 * 8 + kK2Warps * X::XCPX * 8;
+  void (*kern)(const K2Params) = nullptr;
+  if (win) kern = p.scrub ? istft_inv_kernel_4096<true, true> : istft_inv_kernel_4096<true, false>;
+  else     kern = p.scrub ? istft_inv_kernel_4096<false, true> : istft_inv_kernel_4096<false, false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  const long long want_blocks = (p.rows * 2 + kK2Warps - 1) / kK2Warps;
+  const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
+  kern<<<grid > 0 ? grid : 1, kK2Warps * 32, smem, st>>>(p);
+  return cudaGetLastError();
+}
+
 template <int NFFT>
 cudaError_t launch_k2(const K2Params& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
@@ -122,6 +204,7 @@ cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st) {
     case 512: return launch_k2<512>(p, st);
     case 1024: return launch_k2<1024>(p, st);
     case 2048: return launch_k2<2048>(p, st);
+    case 4096: return launch_k2_4096(p, st);
     default: return cudaErrorNotSupported;
   }
 }

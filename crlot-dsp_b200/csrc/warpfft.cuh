@@ -167,6 +167,57 @@ CRLOT_HD void inv_split(cpx (&v)[32], int lane, const cpx* sa, Peer peer, const 
   for (int r = 0; r < 32; ++r) v[r] = out[r];
 }
 
+// ---- N = 4096: two warps per frame ------------------------------------------------------------
+// The 2048-point complex transform is split by one radix-2 decimation-in-frequency stage done at
+// load time:  a[n] = z[n] + z[n+1024],  b[n] = (z[n] - z[n+1024]) * W_2048^n  (n < 1024);
+// warp parity 0 transforms a -> bins 2k', parity 1 transforms b -> bins 2k'+1, each with the
+// 1024-point machinery above (Geo<2048>).  Mirror pairs keep their parity, so the real split
+// stays inside one warp: even bins pair as in fwd_split, odd bins pair (ob,oa) <-> (31-ob,31-oa)
+// with no special lane.  sa[] has 2048 entries indexed by the true bin.
+template <class Peer>
+CRLOT_HD void fwd_split_4096(cpx (&v)[32], int lane, int parity, const cpx* sa, Peer peer, cpx& nyq) {
+  cpx out[32];
+  const int ob = lane;
+  if (parity == 0) {
+#pragma unroll
+    for (int oa = 0; oa < 32; ++oa) {
+      const cpx z = v[oa];
+      const cpx far = peer(31 - oa);
+      const cpx own = v[(32 - oa) % 32];
+      const cpx m = (ob == 0) ? own : far;
+      const cpx ds = fma2(m, mk(-1.f, 1.f), z);
+      const cpx mc = mul2(m, mk(1.f, -1.f));
+      out[oa] = cfma(ds, sa[2 * (ob + 32 * oa)], mc);
+    }
+    if (ob == 0) {
+      out[0] = mk(v[0].x + v[0].y, 0.0f);
+      nyq = mk(v[0].x - v[0].y, 0.0f);
+    }
+  } else {
+#pragma unroll
+    for (int oa = 0; oa < 32; ++oa) {
+      const cpx z = v[oa];
+      const cpx m = peer(31 - oa);
+      const cpx ds = fma2(m, mk(-1.f, 1.f), z);
+      const cpx mc = mul2(m, mk(1.f, -1.f));
+      out[oa] = cfma(ds, sa[2 * (ob + 32 * oa) + 1], mc);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 32; ++r) v[r] = out[r];
+}
+
+// Inverse pre-pass for N = 4096, one register: from X[k], X[k+1024] and their mirrors
+// X[2048-k], X[1024-k] (all read straight from global memory, k = a + 32 b < 1024) build the
+// halved Z'[k], Z'[k+1024] and combine them for this warp's parity:
+//   parity 0: Z'[k] + Z'[k+1024]            parity 1: (Z'[k] - Z'[k+1024]) * conj(W_2048^k)
+CRLOT_HD cpx inv_pre_4096(int k, int parity, cpx xlo, cpx mlo, cpx xhi, cpx mhi, cpx alo, cpx ahi, cpx pre) {
+  cpx zlo = cfmac(fma2(mlo, mk(-1.f, 1.f), xlo), alo, mul2(mlo, mk(1.f, -1.f)));
+  if (k == 0) zlo = mk(0.5f * (xlo.x + mlo.x), 0.5f * (xlo.x - mlo.x));   // mlo = X[2048]: real parts only
+  const cpx zhi = cfmac(fma2(mhi, mk(-1.f, 1.f), xhi), ahi, mul2(mhi, mk(1.f, -1.f)));
+  return parity == 0 ? zlo + zhi : cmulc(zlo - zhi, pre);
+}
+
 // partner lane for the mirror: pass-2 view uses B, pass-1 view uses A (lane + 32*j keeps j).
 template <int D> CRLOT_HD int mirror_lane(int lane) {
   const int base = lane - lane % D;

@@ -109,6 +109,81 @@ template <int NFFT> static int run() {
   return ok ? 0 : 1;
 }
 
+// N = 4096: two emulated warps per frame (parity 0 / 1), see warpfft.cuh.
+static int run4096() {
+  typedef GeoX<2048> X;
+  const int N = 4096, C = 2048;
+  FftTables T = make_fft_tables(N);
+  const cpx* tw1 = reinterpret_cast<const cpx*>(T.tw1.data());
+  const cpx* sa = reinterpret_cast<const cpx*>(T.sa.data());
+  const cpx* pre = reinterpret_cast<const cpx*>(T.pre.data());
+  std::vector<float> x(N);
+  for (auto& s : x) s = (float)frand();
+  std::vector<cd> Xr(C + 1);
+  for (int k = 0; k <= C; ++k) {
+    cd s = 0;
+    for (int n = 0; n < N; ++n) s += (double)x[n] * std::polar(1.0, -2.0 * M_PI * (double)n * k / N);
+    Xr[k] = s;
+  }
+  std::vector<cd> Xg(C + 1);
+  std::vector<cpx> ex(X::XCPX);
+  for (int parity = 0; parity < 2; ++parity) {
+    cpx v[32][32];
+    for (int l = 0; l < 32; ++l)
+      for (int r = 0; r < 32; ++r) {
+        const int n = l + 32 * r;
+        const cpx p0 = mk(x[2 * n], x[2 * n + 1]), p1 = mk(x[2 * (n + 1024)], x[2 * (n + 1024) + 1]);
+        v[l][r] = parity == 0 ? p0 + p1 : cmul(p0 - p1, pre[n]);
+      }
+    for (int l = 0; l < 32; ++l) { pass1<X, false>(v[l]); twiddle1<X, false>(v[l], l, tw1); }
+    for (int l = 0; l < 32; ++l) xchg_write<X>(v[l], l, ex.data());
+    for (int l = 0; l < 32; ++l) xchg_read<X>(v[l], l, ex.data());
+    for (int l = 0; l < 32; ++l) pass2<X, false>(v[l]);
+    cpx snap[32][32];
+    for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
+    for (int l = 0; l < 32; ++l) {
+      const int lp = parity == 0 ? mirror_lane<32>(l) : 31 - l;
+      cpx nyq = mk(0, 0);
+      fwd_split_4096(v[l], l, parity, sa, [&](int r) { return snap[lp][r]; }, nyq);
+      for (int r = 0; r < 32; ++r) Xg[2 * (l + 32 * r) + parity] = cd(v[l][r].x, v[l][r].y);
+      if (parity == 0 && l == 0) Xg[C] = cd(nyq.x, nyq.y);
+    }
+  }
+  double err = 0, nrm = 0;
+  for (int k = 0; k <= C; ++k) { err += std::norm(Xg[k] - Xr[k]); nrm += std::norm(Xr[k]); }
+  const double fwd_rel = std::sqrt(err / nrm);
+  const int exact0 = Xg[0].imag() == 0.0 && Xg[C].imag() == 0.0;
+  // inverse
+  std::vector<cpx> Xf(C + 1);
+  for (int k = 0; k <= C; ++k) Xf[k] = mk((float)Xr[k].real(), (float)Xr[k].imag());
+  Xf[0].y = 55.0f; Xf[C].y = -9.0f;    // must be ignored
+  std::vector<double> y(N);
+  for (int parity = 0; parity < 2; ++parity) {
+    cpx v[32][32];
+    for (int l = 0; l < 32; ++l)
+      for (int r = 0; r < 32; ++r) {
+        const int k = l + 32 * r;
+        v[l][r] = inv_pre_4096(k, parity, Xf[k], Xf[2048 - k], Xf[k + 1024], Xf[1024 - k], sa[k], sa[k + 1024], pre[k]);
+      }
+    for (int l = 0; l < 32; ++l) { pass1<X, true>(v[l]); twiddle1<X, true>(v[l], l, tw1); }
+    for (int l = 0; l < 32; ++l) xchg_write<X>(v[l], l, ex.data());
+    for (int l = 0; l < 32; ++l) xchg_read<X>(v[l], l, ex.data());
+    for (int l = 0; l < 32; ++l) pass2<X, true>(v[l]);
+    for (int l = 0; l < 32; ++l)
+      for (int r = 0; r < 32; ++r) {
+        const int n = l + 32 * r;            // z[2n + parity]
+        y[2 * (2 * n + parity)] = 2.0 * v[l][r].x / N;
+        y[2 * (2 * n + parity) + 1] = 2.0 * v[l][r].y / N;
+      }
+  }
+  err = 0; nrm = 0;
+  for (int i = 0; i < N; ++i) { err += (y[i] - x[i]) * (y[i] - x[i]); nrm += (double)x[i] * x[i]; }
+  const double inv_rel = std::sqrt(err / nrm);
+  const int ok = fwd_rel < 5e-7 && inv_rel < 5e-7 && exact0;
+  printf("N=4096 (2 warps/frame)  fwd rel-L2 %.3e  inv rel-L2 %.3e  exact-zero imag %d  %s\n", fwd_rel, inv_rel, exact0, ok ? "OK" : "FAIL");
+  return ok ? 0 : 1;
+}
+
 int main() {
   srand(1234);
   int bad = 0;
@@ -116,5 +191,6 @@ int main() {
   bad += run<512>();
   bad += run<1024>();
   bad += run<2048>();
+  bad += run4096();
   return bad;
 }
