@@ -8,7 +8,7 @@ torch.distributed plumbing.  It never computes on the CPU: if the library is mis
 CUDA device is present, compute calls raise.
 """
 from .capi import (  # noqa: F401
-    CrlotError, Plan, FftPlan, OlaAccumulator, lib, lib_path, frame_count, ola_ring_len, window_make,
+    CrlotError, CrlotInvalidArgument, CrlotUnsupported, Plan, FftPlan, OlaAccumulator, Stream, lib, lib_path, frame_count, ola_ring_len, window_make,
     build_norm_linear, ola_envelope, synth_uniform, HANN, HAMMING, BLACKMAN, RECT, ZERO_PAD, DROP,
     bytes_per_sample,
 )

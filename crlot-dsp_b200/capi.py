@@ -62,6 +62,7 @@ def lib():
         L.crlot_buf_bytes.restype = C.c_size_t
         L.crlot_ola_get.restype = C.c_size_t
         L.crlot_ola_meter_peak.restype = C.c_float
+        L.crlot_stream_get.restype = C.c_longlong
         _lib = L
     return _lib
 
@@ -370,3 +371,92 @@ class OlaAccumulator:
 
     def meter_peak(self):
         return float(lib().crlot_ola_meter_peak(self._h))
+
+
+# ---- streaming state (config 5) --------------------------------------------------------------------
+class Stream:
+    """crlot_stream_*: `n_streams` concurrent streams fed in chunks (device tensors in / out).
+
+    Per stream this is the reference's chunk-fed DROP Framer -> window -> forward -> inverse ->
+    OLAAccumulator.push_frame_AoS(k*hop) -> produce(hop) drive with device-resident rings."""
+
+    def __init__(self, plan: Plan, n_streams: int, max_chunk: int):
+        self._h = C.c_void_p()
+        self.plan, self.n_streams, self.max_chunk = plan, n_streams, max_chunk
+        _check(lib().crlot_stream_create(plan._h, C.c_int(n_streams), C.c_int(max_chunk), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().crlot_stream_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        _check(lib().crlot_stream_reset(self._h, _stream_ptr(self.plan.device)))
+
+    def frames_ready(self, chunk_len):
+        return int(lib().crlot_stream_frames_ready(self._h, C.c_int(chunk_len)))
+
+    def tick(self, chunk, out=None):
+        """chunk: cuda float32 [n_streams, chunk_len] (row stride free) -> view of out [n_streams, n_out]."""
+        torch = _torch()
+        chunk_len = chunk.shape[1]
+        if out is None:
+            out = torch.empty((self.n_streams, max(self.frames_ready(chunk_len), 1) * self.plan.hop),
+                              dtype=torch.float32, device=chunk.device)
+        n = C.c_int(0)
+        _check(lib().crlot_stream_tick(self._h, C.c_void_p(chunk.data_ptr()), C.c_longlong(chunk.stride(0)),
+                                       C.c_int(chunk_len), C.c_void_p(out.data_ptr()), C.c_longlong(out.stride(0)),
+                                       C.byref(n), _stream_ptr(self.plan.device)))
+        return out[:, :n.value]
+
+    def run(self, signal, chunk_len, n_ticks=None, out=None):
+        """Feed signal [n_streams, >= n_ticks*chunk_len] in n_ticks chunks; returns out[:, :n_out]."""
+        torch = _torch()
+        if n_ticks is None:
+            n_ticks = signal.shape[1] // chunk_len
+        if out is None:
+            n_max = (n_ticks * chunk_len // self.plan.hop + 1) * self.plan.hop
+            out = torch.empty((self.n_streams, n_max), dtype=torch.float32, device=signal.device)
+        n = C.c_longlong(0)
+        _check(lib().crlot_stream_run(self._h, C.c_void_p(signal.data_ptr()), C.c_longlong(signal.stride(0)),
+                                      C.c_int(chunk_len), C.c_longlong(n_ticks), C.c_void_p(out.data_ptr()),
+                                      C.c_longlong(out.stride(0)), C.byref(n), _stream_ptr(self.plan.device)))
+        return out[:, :n.value]
+
+    def tick_host(self, chunk, out):
+        """chunk/out: numpy float32 [n_streams, chunk_len] / [n_streams, >= frames*hop] (ideally pinned)."""
+        n = C.c_int(0)
+        _check(lib().crlot_stream_tick_host(self._h, _p(chunk), C.c_longlong(chunk.strides[0] // 4), C.c_int(chunk.shape[1]),
+                                            _p(out), C.c_longlong(out.strides[0] // 4), C.byref(n)))
+        return n.value
+
+    def drain(self, out=None):
+        torch = _torch()
+        if out is None:
+            out = torch.empty((self.n_streams, max(self.plan.nfft - self.plan.hop, 4)), dtype=torch.float32,
+                              device=f"cuda:{self.plan.device}")
+        n = C.c_int(0)
+        _check(lib().crlot_stream_drain(self._h, C.c_void_p(out.data_ptr()), C.c_longlong(out.stride(0)), C.byref(n),
+                                        _stream_ptr(self.plan.device)))
+        return out[:, :n.value]
+
+    def last_spectra(self):
+        torch = _torch()
+        ptr, nf = C.c_void_p(), C.c_int(0)
+        _check(lib().crlot_stream_last_spectra(self._h, C.byref(ptr), C.byref(nf)))
+        return ptr.value, nf.value
+
+    def samples_ingested(self):
+        return int(lib().crlot_stream_get(self._h, 0))
+
+    def frames_processed(self):
+        return int(lib().crlot_stream_get(self._h, 1))
+
+    def ring_capacity(self):
+        return int(lib().crlot_stream_get(self._h, 2))

@@ -737,3 +737,252 @@ size_t crlot_ola_get(crlot_ola_t o, int what) {
 float crlot_ola_meter_peak(crlot_ola_t o) { return o ? o->peak : 0.0f; }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// streaming state (config 5): device rings + counters, host mirror of the bookkeeping
+// ---------------------------------------------------------------------------------------------
+struct crlot_stream_s {
+  crlot_plan_t plan = nullptr;
+  int S = 0, max_chunk = 0, rcap = 0, max_nf = 0;
+  long long w = 0, k = 0;            // host mirror of the device counters
+  int last_nf = 0;
+  DevArr<StreamCounters> ctr;
+  DevArr<float> ring, acc, frames;
+  DevArr<cpx> spec;
+  DevArr<float> h2d, d2h;            // staging of crlot_stream_tick_host
+  cudaStream_t host_stream = nullptr;
+};
+
+namespace {
+
+int stream_nf(const crlot_stream_s* s, long long w_new) {
+  const int N = s->plan->d.nfft, H = s->plan->d.hop;
+  const long long total = w_new >= N ? (w_new - N) / H + 1 : 0;   // Framer DROP count, framer.cc:106-115
+  return static_cast<int>(total - s->k);
+}
+
+// the launches of one tick; every argument is tick-independent given (w0, k_base, nf)
+cudaError_t stream_tick_launches(crlot_stream_s* s, const float* d_in, long long in_stride, int chunk_len, long long w0,
+                                 float* d_out, long long out_stride, long long k_base, int nf, cudaStream_t st) {
+  crlot_plan_s* p = s->plan;
+  const int N = p->d.nfft, H = p->d.hop;
+  cudaError_t e = launch_stream_ingest(s->ctr.p, d_in, in_stride, chunk_len, s->ring.p, s->rcap, s->S, w0, st);
+  if (e != cudaSuccess) return e;
+  if (nf > 0) {
+    StreamFwdParams f{};
+    f.ctr = s->ctr.p; f.ring = s->ring.p; f.rcap = s->rcap; f.n_streams = s->S; f.nf = nf; f.nfft = N; f.hop = H;
+    f.spec = s->spec.p; f.window = p->win_a.p; f.tw1 = p->tw1.p; f.sa = p->sa.p; f.scrub = p->d.scrub;
+    e = launch_stream_fwd(f, st);
+    if (e != cudaSuccess) return e;
+    K2Params k2{};
+    k2.spec = s->spec.p; k2.rows = static_cast<long long>(s->S) * nf; k2.nfft = N; k2.frames = s->frames.p;
+    k2.window = p->syn_active ? p->win_s.p : nullptr; k2.tw1 = p->tw1.p; k2.sa = p->sa.p; k2.pre = p->pre.p;
+    k2.scrub = p->d.scrub;
+    e = launch_istft_inv(k2, st);
+    if (e != cudaSuccess) return e;
+    StreamOlaParams o{};
+    o.ctr = s->ctr.p; o.frames = s->frames.p; o.n_streams = s->S; o.nf = nf; o.nfft = N; o.hop = H;
+    o.span = N + (nf - 1) * H; o.n_prod = nf * H; o.window = nullptr; o.gain = p->d.gain; o.eps = p->d.eps;
+    o.norm = p->env.p; o.ring_len = static_cast<long long>(p->ring_len); o.acc = s->acc.p; o.out = d_out;
+    o.out_stride = out_stride; o.k_base = k_base;
+    e = launch_stream_ola(o, st);
+    if (e != cudaSuccess) return e;
+  }
+  return launch_stream_advance(s->ctr.p, chunk_len, nf, st);
+}
+
+int stream_check_io(const crlot_stream_s* s, const void* d_in, long long in_stride, int chunk_len, const void* d_out,
+                    long long out_stride) {
+  if (!s || !d_in || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (chunk_len < 0 || chunk_len > s->max_chunk) return fail(CRLOT_ERR_INVALID_ARGUMENT, "chunk_len exceeds max_chunk");
+  if (out_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_out) % 16 != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "output must be 16-byte aligned with out_stride a multiple of 4 floats");
+  (void)in_stride;
+  return CRLOT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int crlot_stream_create(crlot_plan_t plan, int n_streams, int max_chunk, crlot_stream_t* out) {
+  if (!plan || !out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (n_streams <= 0 || max_chunk <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "n_streams and max_chunk must be positive");
+  if (plan->d.boundary_mode != CRLOT_DROP)
+    return fail(CRLOT_ERR_UNSUPPORTED, "streaming needs BoundaryMode::DROP (chunked ZERO_PAD emits premature frames)");
+  if (plan->d.nfft > 2048) return fail(CRLOT_ERR_UNSUPPORTED, "streaming supports nfft <= 2048");
+  const int N = plan->d.nfft, H = plan->d.hop;
+  std::unique_ptr<crlot_stream_s> s(new (std::nothrow) crlot_stream_s);
+  if (!s) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
+  s->plan = plan; s->S = n_streams; s->max_chunk = max_chunk;
+  int rc = 4;
+  while (rc < N + max_chunk) rc <<= 1;
+  s->rcap = rc;
+  s->max_nf = max_chunk / H + 1;
+  // the accumulate span of one tick must fit the accumulator ring without lapping itself
+  if (static_cast<size_t>(N) + static_cast<size_t>(s->max_nf - 1) * H > plan->ring_len)
+    return fail(CRLOT_ERR_UNSUPPORTED, "max_chunk too large for the OLA ring (more than 20 hops per tick)");
+  DeviceGuard g(plan->d.device);
+  CU(s->ctr.alloc(1));
+  CU(s->ring.alloc(static_cast<size_t>(n_streams) * rc));
+  CU(s->acc.alloc(static_cast<size_t>(n_streams) * plan->ring_len));
+  CU(s->spec.alloc(static_cast<size_t>(n_streams) * s->max_nf * plan->bins));
+  CU(s->frames.alloc(static_cast<size_t>(n_streams) * s->max_nf * N));
+  CU(cudaMemset(s->ctr.p, 0, sizeof(StreamCounters)));
+  CU(cudaMemset(s->ring.p, 0, sizeof(float) * n_streams * rc));
+  CU(cudaMemset(s->acc.p, 0, sizeof(float) * n_streams * plan->ring_len));
+  *out = s.release();
+  return CRLOT_OK;
+}
+
+int crlot_stream_destroy(crlot_stream_t s) {
+  if (!s) return CRLOT_OK;
+  { DeviceGuard g(s->plan->d.device); if (s->host_stream) cudaStreamDestroy(s->host_stream); delete s; }
+  return CRLOT_OK;
+}
+
+int crlot_stream_reset(crlot_stream_t s, void* stream) {
+  if (!s) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  DeviceGuard g(s->plan->d.device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU(cudaMemsetAsync(s->ctr.p, 0, sizeof(StreamCounters), st));
+  CU(cudaMemsetAsync(s->ring.p, 0, sizeof(float) * s->S * s->rcap, st));
+  CU(cudaMemsetAsync(s->acc.p, 0, sizeof(float) * s->S * s->plan->ring_len, st));
+  s->w = s->k = 0; s->last_nf = 0;
+  return CRLOT_OK;
+}
+
+int crlot_stream_frames_ready(crlot_stream_t s, int chunk_len) {
+  if (!s || chunk_len < 0) return 0;
+  return stream_nf(s, s->w + chunk_len);
+}
+
+int crlot_stream_tick(crlot_stream_t s, const float* d_chunk, long long chunk_stride, int chunk_len, float* d_out,
+                      long long out_stride, int* n_out, void* stream) {
+  if (n_out) *n_out = 0;
+  int rc = stream_check_io(s, d_chunk, chunk_stride, chunk_len, d_out, out_stride);
+  if (rc) return rc;
+  DeviceGuard g(s->plan->d.device);
+  const int nf = stream_nf(s, s->w + chunk_len);
+  CU(stream_tick_launches(s, d_chunk, chunk_stride, chunk_len, s->w, d_out, out_stride, s->k, nf,
+                          static_cast<cudaStream_t>(stream)));
+  s->w += chunk_len; s->k += nf; s->last_nf = nf;
+  if (n_out) *n_out = nf * s->plan->d.hop;
+  return CRLOT_OK;
+}
+
+int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, int chunk_len, long long n_ticks,
+                     float* d_out, long long out_stride, long long* n_out, void* stream) {
+  if (n_out) *n_out = 0;
+  int rc = stream_check_io(s, d_in, in_stride, chunk_len, d_out, out_stride);
+  if (rc) return rc;
+  if (n_ticks < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  DeviceGuard g(s->plan->d.device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long w0 = s->w, k_base = s->k;
+  // One instantiated graph per distinct frames-per-tick value seen in this run (the launches of
+  // a tick depend on the tick only through the device counters).
+  struct Cached { int nf; cudaGraphExec_t exec; };
+  std::vector<Cached> cache;
+  const bool use_graph = n_ticks >= 16;
+  int status = CRLOT_OK;
+  for (long long t = 0; t < n_ticks && status == CRLOT_OK; ++t) {
+    const int nf = stream_nf(s, s->w + chunk_len);
+    cudaError_t e = cudaSuccess;
+    if (!use_graph) {
+      e = stream_tick_launches(s, d_in, in_stride, chunk_len, w0, d_out, out_stride, k_base, nf, st);
+    } else {
+      cudaGraphExec_t exec = nullptr;
+      for (auto& c : cache) if (c.nf == nf) exec = c.exec;
+      if (!exec) {
+        // captured on a private stream (the caller's may be the legacy default stream, which
+        // cannot capture); capturing only records the launches, the replay goes to `st`
+        cudaGraph_t graph = nullptr;
+        if (!s->host_stream) e = cudaStreamCreateWithFlags(&s->host_stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamBeginCapture(s->host_stream, cudaStreamCaptureModeRelaxed);
+        if (e == cudaSuccess) {
+          cudaError_t e1 = stream_tick_launches(s, d_in, in_stride, chunk_len, w0, d_out, out_stride, k_base, nf,
+                                                s->host_stream);
+          e = cudaStreamEndCapture(s->host_stream, &graph);
+          if (e1 != cudaSuccess) e = e1;
+        }
+        if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+        if (e == cudaSuccess) cache.push_back({nf, exec});
+      }
+      if (e == cudaSuccess) e = cudaGraphLaunch(exec, st);
+    }
+    if (e != cudaSuccess) { status = fail_cuda(e, "crlot_stream_run"); break; }
+    s->w += chunk_len; s->k += nf; s->last_nf = nf;
+  }
+  if (!cache.empty()) {
+    cudaStreamSynchronize(st);            // the executables must outlive their launches
+    for (auto& c : cache) cudaGraphExecDestroy(c.exec);
+  }
+  if (n_out) *n_out = (s->k - k_base) * s->plan->d.hop;
+  return status;
+}
+
+int crlot_stream_tick_host(crlot_stream_t s, const float* h_chunk, long long chunk_stride, int chunk_len, float* h_out,
+                           long long out_stride, int* n_out) {
+  if (n_out) *n_out = 0;
+  if (!s || !h_chunk || !h_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (chunk_len < 0 || chunk_len > s->max_chunk) return fail(CRLOT_ERR_INVALID_ARGUMENT, "chunk_len exceeds max_chunk");
+  DeviceGuard g(s->plan->d.device);
+  const int H = s->plan->d.hop;
+  const long long in_pitch = (s->max_chunk + 3) / 4 * 4, out_pitch = static_cast<long long>(s->max_nf) * H;
+  if (!s->host_stream) CU(cudaStreamCreateWithFlags(&s->host_stream, cudaStreamNonBlocking));
+  if (!s->h2d.p) {
+    CU(s->h2d.alloc(static_cast<size_t>(s->S) * in_pitch));
+    CU(s->d2h.alloc(static_cast<size_t>(s->S) * out_pitch));
+  }
+  cudaStream_t st = s->host_stream;
+  CU(cudaMemcpy2DAsync(s->h2d.p, in_pitch * sizeof(float), h_chunk, chunk_stride * sizeof(float),
+                       static_cast<size_t>(chunk_len) * sizeof(float), s->S, cudaMemcpyHostToDevice, st));
+  const int nf = stream_nf(s, s->w + chunk_len);
+  CU(stream_tick_launches(s, s->h2d.p, in_pitch, chunk_len, s->w, s->d2h.p, out_pitch, s->k, nf, st));
+  s->w += chunk_len; s->k += nf; s->last_nf = nf;
+  if (nf > 0)
+    CU(cudaMemcpy2DAsync(h_out, out_stride * sizeof(float), s->d2h.p, out_pitch * sizeof(float),
+                         static_cast<size_t>(nf) * H * sizeof(float), s->S, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (n_out) *n_out = nf * H;
+  return CRLOT_OK;
+}
+
+int crlot_stream_drain(crlot_stream_t s, float* d_out, long long out_stride, int* n_out, void* stream) {
+  if (n_out) *n_out = 0;
+  if (!s || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  const int N = s->plan->d.nfft, H = s->plan->d.hop;
+  if (s->k == 0 || N == H) return CRLOT_OK;
+  if (out_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_out) % 16 != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "output must be 16-byte aligned with out_stride a multiple of 4 floats");
+  DeviceGuard g(s->plan->d.device);
+  StreamOlaParams o{};
+  o.ctr = s->ctr.p; o.frames = s->frames.p; o.n_streams = s->S; o.nf = 0; o.nfft = N; o.hop = H;
+  o.span = N - H; o.n_prod = N - H; o.window = nullptr; o.gain = s->plan->d.gain; o.eps = s->plan->d.eps;
+  o.norm = s->plan->env.p; o.ring_len = static_cast<long long>(s->plan->ring_len); o.acc = s->acc.p; o.out = d_out;
+  o.out_stride = out_stride; o.k_base = s->k;
+  CU(launch_stream_ola(o, static_cast<cudaStream_t>(stream)));
+  if (n_out) *n_out = N - H;
+  return CRLOT_OK;
+}
+
+int crlot_stream_last_spectra(crlot_stream_t s, void** d_spec, int* frames_per_stream) {
+  if (!s || !d_spec || !frames_per_stream) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  *d_spec = s->spec.p;
+  *frames_per_stream = s->last_nf;
+  return CRLOT_OK;
+}
+
+long long crlot_stream_get(crlot_stream_t s, int what) {
+  if (!s) return 0;
+  switch (what) {
+    case 0: return s->w;
+    case 1: return s->k;
+    case 2: return s->rcap;
+    default: return 0;
+  }
+}
+
+}  // extern "C"

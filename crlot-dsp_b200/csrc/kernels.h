@@ -81,6 +81,43 @@ cudaError_t launch_ring_produce(float* ring, long long ring_len, int channels, c
                                 float eps, long long read_pos, int n, float* out,
                                 long long out_chan_stride, cudaStream_t st);
 
+// ---- streaming (config 5): device-resident per-stream state, one tick = 4 launches --------------
+struct StreamCounters {
+  long long w;   // samples ingested per stream so far
+  long long k;   // next frame index (== frames processed); read position of the OLA ring = k*hop
+};
+cudaError_t launch_stream_ingest(const StreamCounters* ctr, const float* chunk, long long chunk_stride, int chunk_len,
+                                 float* ring, int rcap, int n_streams, long long w0, cudaStream_t st);
+struct StreamFwdParams {
+  const StreamCounters* ctr;
+  const float* ring;         // [n_streams][rcap] ingest rings (rcap a power of two)
+  int rcap, n_streams, nf;   // nf = frames per stream this tick
+  int nfft, hop;
+  cpx* spec;                 // [n_streams][nf][nfft/2+1]
+  const float* window;
+  const cpx* tw1;
+  const cpx* sa;
+  int scrub;
+};
+cudaError_t launch_stream_fwd(const StreamFwdParams& p, cudaStream_t st);
+struct StreamOlaParams {
+  const StreamCounters* ctr;
+  const float* frames;       // [n_streams][nf][nfft]
+  int n_streams, nf, nfft, hop;
+  int span;                  // ring positions touched per stream: nfft + (nf-1)*hop, or n_prod when nf == 0
+  int n_prod;                // samples produced per stream (nf*hop, or nfft-hop for the final drain)
+  const float* window;       // nullptr: frames already carry the synthesis window
+  float gain, eps;
+  const float* norm;
+  long long ring_len;
+  float* acc;                // [n_streams][ring_len] accumulator rings
+  float* out;                // [n_streams][out_stride]; this tick writes at offset (k - k_base)*hop
+  long long out_stride;
+  long long k_base;          // frame counter value that maps to out[.][0]
+};
+cudaError_t launch_stream_ola(const StreamOlaParams& p, cudaStream_t st);
+cudaError_t launch_stream_advance(StreamCounters* ctr, int chunk_len, int nf, cudaStream_t st);
+
 int device_sm_count();
 
 }  // namespace crlot

@@ -154,6 +154,44 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
 int crlot_synth_uniform(float* d_out, long long chan_stride, int channels, long long n, unsigned long long seed,
                         unsigned long long channel0, unsigned long long i0, int device, void* stream);
 
+/* ---- streaming state: many concurrent streams, chunked ring-buffer ingest (config 5) ------------ */
+/* Device-resident analogue, per stream, of a Framer in DROP mode fed in chunks
+ *   (ref: dsp/frame/framer.cc:37-59,88-118,128-182) followed by the window / forward / inverse
+ *   / OLAAccumulator::push_frame_AoS(k*hop) / produce(hop) drive of
+ *   bench/ola_benchmark.cc:150-157, with the accumulator in a RingBuffer of
+ *   crlot_ola_ring_len() cells (ref: dsp/ring/ring_buffer.cc:44-85, OLAAccumulator.cc:249-258).
+ * All streams of one state advance in lock step (same chunk length per tick).  The plan must use
+ * CRLOT_DROP (chunked ZERO_PAD emits premature frames in the reference, framer.cc:98-103) and
+ * nfft <= 2048.  Outputs are bit-identical to crlot_roundtrip_execute on the concatenated input. */
+typedef struct crlot_stream_s* crlot_stream_t;
+int crlot_stream_create(crlot_plan_t plan, int n_streams, int max_chunk, crlot_stream_t* out);
+int crlot_stream_destroy(crlot_stream_t st);
+int crlot_stream_reset(crlot_stream_t st, void* stream);
+/* frames a tick of chunk_len samples would complete, given the samples ingested so far */
+int crlot_stream_frames_ready(crlot_stream_t st, int chunk_len);
+/* One tick.  d_chunk: [n_streams][chunk_stride] device floats, chunk_len new samples per stream.
+ * Every frame completed by them is transformed, inverse-transformed, accumulated and produced:
+ * d_out [n_streams][out_stride] receives *n_out = new_frames*hop samples per stream. */
+int crlot_stream_tick(crlot_stream_t st, const float* d_chunk, long long chunk_stride, int chunk_len,
+                      float* d_out, long long out_stride, int* n_out, void* stream);
+/* n_ticks ticks over consecutive chunks of d_in [n_streams][in_stride] (tick i reads samples
+ * [i*chunk_len, (i+1)*chunk_len)); outputs are appended per stream in d_out; *n_out = total samples
+ * written per stream.  The tick loop runs inside the library (CUDA graph replay in steady state). */
+int crlot_stream_run(crlot_stream_t st, const float* d_in, long long in_stride, int chunk_len, long long n_ticks,
+                     float* d_out, long long out_stride, long long* n_out, void* stream);
+/* One tick with HOST buffers (ideally page-locked): h_chunk [n_streams][chunk_stride] is copied to
+ * the device, the tick runs, *n_out samples per stream are copied back into h_out
+ * [n_streams][out_stride], and the call returns when h_out is complete (the low-latency use). */
+int crlot_stream_tick_host(crlot_stream_t st, const float* h_chunk, long long chunk_stride, int chunk_len,
+                           float* h_out, long long out_stride, int* n_out);
+/* final produce(nfft - hop) of the drive; *n_out = nfft - hop (0 if no frame was ever pushed) */
+int crlot_stream_drain(crlot_stream_t st, float* d_out, long long out_stride, int* n_out, void* stream);
+/* spectra of the most recent tick, device pointer to [n_streams][frames][nfft/2+1] complex, and
+ * the frame count per stream: the reference's "processing goes here" gap (e2e_benchmark.cc:161-162) */
+int crlot_stream_last_spectra(crlot_stream_t st, void** d_spec, int* frames_per_stream);
+/* what = 0 samples ingested per stream, 1 frames processed per stream, 2 ingest ring capacity */
+long long crlot_stream_get(crlot_stream_t st, int what);
+
 /* ---- drop-in FFT plan (host pointers, reference batch/stride layout) --------------------------- */
 /* replaces dsp::fft::MakeFftPlan / IFftPlan::{forward,inverse} for FftDomain::Real
  *   ref: dsp/fft/api/fft_api.h:16-51; dsp/fft/backends/kissfft_adapter.cc:13-63,83-168
