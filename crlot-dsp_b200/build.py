@@ -19,7 +19,7 @@ LIB = os.path.join(HERE, "libcrlot_cuda.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
-SOURCES = ["k1_stft.cu", "k2_istft.cu", "k3_ola.cu", "aux_kernels.cu", "stream_kernels.cu", "capi.cu"]
+SOURCES = ["k1_stft.cu", "k2_istft.cu", "k3_ola.cu", "aux_kernels.cu", "stream_kernels.cu", "framer.cu", "capi.cu"]
 
 
 def _newer(target, deps):
@@ -56,5 +56,12 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def build_host():
+    """C++ facades (host/crlot_dsp.h) + their test driver, with g++ against the in-tree .so."""
+    subprocess.check_call(["make", "-C", os.path.join(HERE, "host"), "facade_test"], stdout=subprocess.DEVNULL)
+    return os.path.join(HERE, "host", "facade_test")
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    print(build_host())

@@ -163,6 +163,8 @@ static cudaError_t upload_cpx(DevArr<cpx>& dst, const std::vector<float>& v) {
 extern "C" {
 
 int crlot_cuda_abi_version(void) { return CRLOT_ABI_VERSION; }
+// internal: lets the other translation units of the library (framer.cu) set the last-error text
+void crlot_cuda_set_error_(const char* msg) { g_err = msg ? msg : ""; }
 const char* crlot_cuda_last_error(void) { return g_err.c_str(); }
 
 int crlot_cuda_device_count(int* count) {

@@ -1,0 +1,334 @@
+// crlot_dsp.h -- the reference's C++ class surface for the STFT -> iSTFT path, re-hosted on the
+// B200 C-ABI (include/crlot_cuda.h).  Header-only; link with -lcrlot_cuda.
+//
+// Same namespaces, class names, method names, argument meaning and exception types as
+//   dsp::BoundaryMode / dsp::Framer                 ref: dsp/frame/framer.h:11-131
+//   dsp::WindowType / NormalizationType / WindowLUT ref: dsp/window/WindowLUT.h:13-190
+//   dsp::fft::FftDomain / FftPlanDesc / IFftPlan / MakeFftPlan
+//                                                   ref: dsp/fft/api/fft_api.h:9-51
+//   dsp::OLAConfig / dsp::OLAAccumulator            ref: dsp/ola/OLAAccumulator.h:15-164
+// so that code written against the reference (bench/e2e_benchmark.cc:138-186, tests/*.cc) compiles
+// against this header unchanged.  Nothing here computes on the CPU: every method forwards to the
+// C-ABI, whose compute entry points launch sm_100a kernels or fail (no fallback).
+//
+// Extensions that the reference does not have are grouped under "B200 extension" comments; they
+// are what makes the path fast (whole-signal calls instead of one frame per call).
+#ifndef CRLOT_DSP_HOST_FACADES_H_
+#define CRLOT_DSP_HOST_FACADES_H_
+
+#include <complex>
+#include <cstddef>
+#include <cstdint>
+#include <memory>
+#include <new>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/crlot_cuda.h"
+
+namespace dsp {
+
+namespace detail {
+// status code -> the exception type the reference throws at the corresponding site
+inline void check(int rc) {
+  if (rc == CRLOT_OK) return;
+  const std::string msg = crlot_cuda_last_error();
+  switch (rc) {
+    case CRLOT_ERR_INVALID_ARGUMENT: throw std::invalid_argument(msg);
+    case CRLOT_ERR_ALLOC: throw std::bad_alloc();
+    default: throw std::runtime_error(msg);   // RUNTIME, UNSUPPORTED, CUDA
+  }
+}
+inline int& default_device() {
+  static int dev = 0;
+  return dev;
+}
+}  // namespace detail
+
+// B200 extension: device ordinal used by objects constructed afterwards (one process per GPU)
+inline void set_default_device(int device) { detail::default_device() = device; }
+
+// ------------------------------------------------------------------------------------------------
+// Framer
+// ------------------------------------------------------------------------------------------------
+enum class BoundaryMode { ZERO_PAD, DROP };
+
+class Framer {
+ public:
+  Framer() = default;
+  ~Framer() { crlot_framer_destroy(h_); }
+  Framer(const Framer&) = delete;
+  Framer& operator=(const Framer&) = delete;
+
+  void set_params(size_t frame_size, size_t hop_size, size_t channels = 1,
+                  BoundaryMode boundary_mode = BoundaryMode::ZERO_PAD) {
+    crlot_framer_t nh = nullptr;
+    detail::check(crlot_framer_create(frame_size, hop_size, channels,
+                                      boundary_mode == BoundaryMode::DROP ? CRLOT_DROP : CRLOT_ZERO_PAD,
+                                      detail::default_device(), &nh));
+    crlot_framer_destroy(h_);
+    h_ = nh;
+    frame_size_ = frame_size; hop_size_ = hop_size; channels_ = channels; boundary_mode_ = boundary_mode;
+  }
+  bool push(const float* interleaved, size_t frames) {
+    if (!h_) return false;
+    if (interleaved == nullptr && frames > 0) return false;
+    detail::check(crlot_framer_push(h_, interleaved, frames));
+    return true;
+  }
+  bool pop(float* out_frame) {
+    if (!h_ || out_frame == nullptr) return false;
+    int popped = 0;
+    detail::check(crlot_framer_pop(h_, out_frame, &popped));
+    return popped != 0;
+  }
+  size_t available_frames() const { return h_ ? crlot_framer_available(h_) : 0; }
+  void reset() { if (h_) detail::check(crlot_framer_reset(h_)); }
+  size_t frame_size() const { return frame_size_; }
+  size_t hop_size() const { return hop_size_; }
+  size_t channels() const { return channels_; }
+  BoundaryMode boundary_mode() const { return boundary_mode_; }
+  size_t buffer_size() const { return h_ ? crlot_framer_get(h_, 4) : 0; }
+
+  // ---- B200 extension --------------------------------------------------------------------------
+  crlot_framer_t handle() const { return h_; }
+  size_t drainable_frames() const { return h_ ? crlot_framer_get(h_, 8) : 0; }
+
+ private:
+  crlot_framer_t h_ = nullptr;
+  size_t frame_size_ = 0, hop_size_ = 0, channels_ = 1;
+  BoundaryMode boundary_mode_ = BoundaryMode::ZERO_PAD;
+};
+
+// ------------------------------------------------------------------------------------------------
+// WindowLUT
+// ------------------------------------------------------------------------------------------------
+enum class WindowType { HANN, HAMMING, BLACKMAN, RECT, BLACKMAN_HARRIS };
+enum class NormalizationType { NONE, SUM_TO_ONE, L2_NORM, OLA_UNITY_GAIN, OLA_SUM_WSQ };
+
+class WindowLUT {
+ public:
+  WindowLUT(size_t nfft, WindowType type, bool periodic = false, NormalizationType norm = NormalizationType::NONE)
+      : size_(nfft), type_(type), periodic_(periodic), norm_(norm) {
+    data_ = make(type, nfft, periodic, norm);
+  }
+  WindowLUT() = default;
+
+  const float* data() const { return data_.get(); }
+  size_t size() const { return data_ ? size_ : 0; }
+  WindowType type() const { return data_ ? type_ : WindowType::HANN; }
+  bool periodic() const { return data_ ? periodic_ : false; }
+  NormalizationType normalization() const { return data_ ? norm_ : NormalizationType::NONE; }
+
+  // The reference memoises tables process-wide behind a mutex and a generation counter
+  // (WindowLUT.cc:60-165).  A table here is a few KB built once per plan and then resident on the
+  // device, so GetWindowSafe simply builds and hands out ownership.
+  std::shared_ptr<const float> GetWindowSafe(WindowType type, size_t N, bool periodic = false,
+                                             NormalizationType norm = NormalizationType::NONE) {
+    return make(type, N, periodic, norm);
+  }
+  static WindowLUT& getInstance() {
+    static WindowLUT inst;
+    return inst;
+  }
+  static double calculateSum(const float* window, size_t N) {
+    double s = 0.0;
+    for (size_t i = 0; i < N; ++i) s += static_cast<double>(window[i]);
+    return s;
+  }
+  static double calculateSumOfSquares(const float* window, size_t N) {
+    double s = 0.0;
+    for (size_t i = 0; i < N; ++i) s += static_cast<double>(window[i]) * static_cast<double>(window[i]);
+    return s;
+  }
+
+ private:
+  static std::shared_ptr<const float> make(WindowType type, size_t N, bool periodic, NormalizationType norm) {
+    std::shared_ptr<float> p(new float[N ? N : 1], std::default_delete<float[]>());
+    detail::check(crlot_window_make(static_cast<int>(type), N, periodic ? 1 : 0, static_cast<int>(norm), p.get()));
+    return p;
+  }
+  std::shared_ptr<const float> data_;
+  size_t size_ = 0;
+  WindowType type_ = WindowType::HANN;
+  bool periodic_ = false;
+  NormalizationType norm_ = NormalizationType::NONE;
+};
+
+// ------------------------------------------------------------------------------------------------
+// OLAAccumulator
+// ------------------------------------------------------------------------------------------------
+struct OLAConfig {
+  int sample_rate;
+  size_t frame_size;
+  size_t hop_size;
+  size_t channels;
+  float eps = 1e-8f;
+  bool apply_window_inside;
+  bool shadow_ring = false;
+  bool isValid() const {
+    return sample_rate > 0 && frame_size > 0 && hop_size > 0 && channels > 0 && eps > 0.0f;
+  }
+};
+
+class OLAAccumulator {
+ public:
+  explicit OLAAccumulator(const OLAConfig& cfg) : cfg_(cfg) {
+    detail::check(crlot_ola_create(cfg.sample_rate, cfg.frame_size, cfg.hop_size, cfg.channels, cfg.eps,
+                                   cfg.apply_window_inside ? 1 : 0, cfg.shadow_ring ? 1 : 0,
+                                   detail::default_device(), &h_));
+  }
+  ~OLAAccumulator() { crlot_ola_destroy(h_); }
+  OLAAccumulator(const OLAAccumulator&) = delete;
+  OLAAccumulator& operator=(const OLAAccumulator&) = delete;
+  OLAAccumulator(OLAAccumulator&&) = delete;
+  OLAAccumulator& operator=(OLAAccumulator&&) = delete;
+
+  void set_window(const float* w, int wlen) { detail::check(crlot_ola_set_window(h_, w, wlen)); }
+  void add_frame_SoA(const float* const* ch_frames, const float* window, size_t start_sample, size_t start_off,
+                     size_t size, float gain) {
+    detail::check(crlot_ola_add_frame_soa(h_, ch_frames, window, start_sample, start_off, size, gain));
+  }
+  void push_frame_AoS(const float* interleaved, const float* window, size_t start_sample, size_t start_off,
+                      size_t size, float gain) {
+    detail::check(crlot_ola_push_frame_aos(h_, interleaved, window, start_sample, start_off, size, gain));
+  }
+  size_t produce(float* const* ch_out, size_t n) {
+    size_t produced = 0;
+    detail::check(crlot_ola_produce(h_, ch_out, n, &produced));
+    return produced;
+  }
+  void flush() { detail::check(crlot_ola_flush(h_)); }
+  void reset() { detail::check(crlot_ola_reset(h_)); }
+  size_t produced_samples() const { return crlot_ola_get(h_, 0); }
+  size_t read_pos() const { return crlot_ola_get(h_, 1); }
+  float meter_peak() const { return crlot_ola_meter_peak(h_); }
+  const OLAConfig& config() const { return cfg_; }
+  bool has_window() const { return crlot_ola_get(h_, 3) != 0; }
+  size_t ring_size() const { return crlot_ola_get(h_, 2); }
+
+  // ---- B200 extension --------------------------------------------------------------------------
+  crlot_ola_t handle() const { return h_; }
+
+ private:
+  OLAConfig cfg_;
+  crlot_ola_t h_ = nullptr;
+};
+
+// ------------------------------------------------------------------------------------------------
+// FFT plan API
+// ------------------------------------------------------------------------------------------------
+namespace fft {
+
+enum class FftDomain { Real, Complex };
+
+struct FftPlanDesc {
+  FftDomain domain;
+  int nfft;
+  bool in_place;
+  int batch;
+  int stride_in;
+  int stride_out;
+};
+
+class IFftPlan {
+ public:
+  virtual ~IFftPlan() = default;
+  virtual void forward(const float* in, std::complex<float>* out, int batch = 1) = 0;
+  virtual void inverse(const std::complex<float>* in, float* out, int batch = 1) = 0;
+  virtual void forward_complex(const std::complex<float>* in, std::complex<float>* out, int batch = 1) = 0;
+  virtual void inverse_complex(const std::complex<float>* in, std::complex<float>* out, int batch = 1) = 0;
+  virtual FftDomain domain() const = 0;
+  virtual int size() const = 0;
+  virtual bool supports_batch() const { return true; }
+  virtual int max_batch_size() const { return 16; }
+};
+
+// IFftPlan over crlot_fft_* (the register-FFT kernels of K1/K2 run without window or framing)
+class CudaFftPlan final : public IFftPlan {
+ public:
+  explicit CudaFftPlan(const FftPlanDesc& d) : desc_(d) {
+    if (d.domain != FftDomain::Real)      // the hot path is the real transform; ref: kissfft_adapter.cc:170-239
+      throw std::runtime_error("Complex-domain plans are not provided by the B200 path (Real only)");
+    dsp::detail::check(crlot_fft_plan_create(d.nfft, d.in_place ? 1 : 0, d.batch, d.stride_in, d.stride_out,
+                                             dsp::detail::default_device(), &h_));
+  }
+  ~CudaFftPlan() override { crlot_fft_plan_destroy(h_); }
+  void forward(const float* in, std::complex<float>* out, int batch = 1) override {
+    dsp::detail::check(crlot_fft_forward(h_, in, reinterpret_cast<float*>(out), batch));
+  }
+  void inverse(const std::complex<float>* in, float* out, int batch = 1) override {
+    dsp::detail::check(crlot_fft_inverse(h_, reinterpret_cast<const float*>(in), out, batch));
+  }
+  void forward_complex(const std::complex<float>*, std::complex<float>*, int = 1) override {
+    throw std::runtime_error("Plan is not configured for complex FFT");   // ref: kissfft_adapter.cc:171-173
+  }
+  void inverse_complex(const std::complex<float>*, std::complex<float>*, int = 1) override {
+    throw std::runtime_error("Plan is not configured for complex FFT");   // ref: kissfft_adapter.cc:207-209
+  }
+  FftDomain domain() const override { return desc_.domain; }
+  int size() const override { return desc_.nfft; }
+
+ private:
+  FftPlanDesc desc_;
+  crlot_fft_t h_ = nullptr;
+};
+
+inline std::unique_ptr<IFftPlan> MakeFftPlan(const FftPlanDesc& desc) {
+  return std::unique_ptr<IFftPlan>(new CudaFftPlan(desc));
+}
+
+}  // namespace fft
+
+// ------------------------------------------------------------------------------------------------
+// B200 extension: the whole round trip as one object (what a maintainer would switch the loop of
+// bench/e2e_benchmark.cc:149-176 to).  Host pointers in, host pointers out; device-resident
+// variants through plan() and the C-ABI.
+// ------------------------------------------------------------------------------------------------
+class StftRoundTrip {
+ public:
+  StftRoundTrip(size_t frame_size, size_t hop_size, const float* analysis_window, const float* ola_window,
+                BoundaryMode mode = BoundaryMode::DROP, bool apply_window_inside = true, float gain = 1.0f,
+                float eps = 1e-8f) {
+    crlot_stft_desc d{};
+    d.nfft = static_cast<int>(frame_size);
+    d.hop = static_cast<int>(hop_size);
+    d.boundary_mode = mode == BoundaryMode::DROP ? CRLOT_DROP : CRLOT_ZERO_PAD;
+    d.analysis_window = analysis_window;
+    d.ola_window = ola_window;
+    d.push_window = nullptr;
+    d.apply_window_inside = apply_window_inside ? 1 : 0;
+    d.gain = gain;
+    d.eps = eps;
+    d.scrub = 1;
+    d.device = detail::default_device();
+    detail::check(crlot_stft_plan_create(&d, &plan_));
+    n_ = d.nfft; h_ = d.hop; mode_ = d.boundary_mode;
+  }
+  ~StftRoundTrip() { crlot_stft_plan_destroy(plan_); }
+  StftRoundTrip(const StftRoundTrip&) = delete;
+  StftRoundTrip& operator=(const StftRoundTrip&) = delete;
+
+  size_t frames_for(size_t len) const { return static_cast<size_t>(crlot_frame_count((long long)len, n_, h_, mode_)); }
+  size_t output_len_for(size_t len) const {
+    const size_t f = frames_for(len);
+    return f ? (f - 1) * static_cast<size_t>(h_) + static_cast<size_t>(n_) : 0;
+  }
+  // planar channels: in[c*chan_stride + i]; returns samples written per channel
+  size_t process(const float* in, size_t chan_stride, size_t len, size_t channels, float* out, size_t out_chan_stride) {
+    long long n_out = 0;
+    detail::check(crlot_roundtrip_host(plan_, in, (long long)chan_stride, (long long)len, (int)channels, out,
+                                       (long long)out_chan_stride, &n_out));
+    return static_cast<size_t>(n_out);
+  }
+  crlot_plan_t plan() const { return plan_; }
+
+ private:
+  crlot_plan_t plan_ = nullptr;
+  int n_ = 0, h_ = 0, mode_ = CRLOT_DROP;
+};
+
+}  // namespace dsp
+
+#endif  // CRLOT_DSP_HOST_FACADES_H_

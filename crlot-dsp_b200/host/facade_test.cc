@@ -1,0 +1,416 @@
+// facade_test.cc -- exercises the reference-named C++ classes of crlot_dsp.h on a B200, in the
+// shape of the reference's own gtest cases (gtest is not in this image, so plain CHECKs):
+//   tests/framer_test.cc:100-322, tests/window_lut_test.cc:85-215, tests/fft_test.cc:57-250,
+//   tests/ola_accumulator_test.cc:143-330, and the loop of bench/e2e_benchmark.cc:138-186.
+// It does not link the oracle.  Arrays it produces are written to <outdir>/*.f32 so that
+// tests/test_gpu_facades_cpp.py can compare them with the oracle on the same inputs.
+//
+//   usage: facade_test <outdir>
+#include <cmath>
+#include <complex>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "crlot_dsp.h"
+
+using namespace dsp;
+using namespace dsp::fft;
+
+static int g_fail = 0, g_checks = 0;
+#define CHECK(cond)                                                               \
+  do {                                                                            \
+    ++g_checks;                                                                   \
+    if (!(cond)) { ++g_fail; std::printf("FAIL %s:%d  %s\n", __FILE__, __LINE__, #cond); } \
+  } while (0)
+#define CHECK_THROWS(expr, extype)                          \
+  do {                                                      \
+    ++g_checks;                                             \
+    bool ok__ = false;                                      \
+    try { expr; } catch (const extype&) { ok__ = true; } catch (...) {} \
+    if (!ok__) { ++g_fail; std::printf("FAIL %s:%d  %s should throw %s\n", __FILE__, __LINE__, #expr, #extype); } \
+  } while (0)
+
+static std::string g_out;
+static void dump(const char* name, const float* p, size_t n) {
+  const std::string path = g_out + "/" + name + ".f32";
+  FILE* f = std::fopen(path.c_str(), "wb");
+  if (!f) { std::printf("cannot write %s\n", path.c_str()); ++g_fail; return; }
+  std::fwrite(p, sizeof(float), n, f);
+  std::fclose(f);
+}
+
+// deterministic test signal (an LCG; the Python side regenerates it from the dumped copy)
+static std::vector<float> noise(size_t n, uint32_t seed) {
+  std::vector<float> v(n);
+  uint32_t s = seed;
+  for (size_t i = 0; i < n; ++i) {
+    s = s * 1664525u + 1013904223u;
+    v[i] = static_cast<float>(static_cast<int32_t>(s >> 8) - (1 << 23)) / static_cast<float>(1 << 23);
+  }
+  return v;
+}
+
+// ---- Framer (tests/framer_test.cc) --------------------------------------------------------------
+static void test_framer() {
+  std::vector<float> sine(4800);
+  for (size_t i = 0; i < sine.size(); ++i) sine[i] = std::sin(2.0 * M_PI * 440.0 * i / 48000.0);
+  {  // BasicPushPop :100-112
+    Framer f;
+    std::vector<float> fr(64);
+    CHECK(!f.push(sine.data(), 10));                 // params not set -> false (framer.cc:38-40)
+    CHECK(!f.pop(fr.data()));
+    f.set_params(64, 16, 1);
+    CHECK(f.push(sine.data(), sine.size()));
+    CHECK(f.available_frames() > 0);
+    CHECK(f.pop(fr.data()));
+    bool same = true;
+    for (int i = 0; i < 64; ++i) same = same && fr[i] == sine[i];
+    CHECK(same);
+    CHECK(f.pop(fr.data()));
+    same = true;
+    for (int i = 0; i < 64; ++i) same = same && fr[i] == sine[16 + i];
+    CHECK(same);
+  }
+  {  // InterleavedChannels :114-134 -- stereo frames stay interleaved [L0,R0,L1,R1,...]
+    std::vector<float> st(200);
+    for (int i = 0; i < 100; ++i) { st[2 * i] = (float)i; st[2 * i + 1] = -(float)i; }
+    Framer f;
+    f.set_params(32, 8, 2);
+    CHECK(f.push(st.data(), 100));
+    std::vector<float> fr(64);
+    CHECK(f.pop(fr.data()));
+    CHECK(f.pop(fr.data()));
+    bool ok = true;
+    for (int i = 0; i < 32; ++i) ok = ok && fr[2 * i] == (float)(8 + i) && fr[2 * i + 1] == -(float)(8 + i);
+    CHECK(ok);
+    CHECK(f.channels() == 2);
+  }
+  {  // EvenOddLengths :227-241, VeryShortLengths :244-259
+    Framer f;
+    f.set_params(64, 16, 1);
+    CHECK(f.push(sine.data(), 100));
+    CHECK(f.available_frames() > 0);
+    f.set_params(63, 15, 1);
+    f.reset();
+    CHECK(f.push(sine.data(), 100));
+    CHECK(f.available_frames() == (100 - 63) / 15 + 1);
+    f.set_params(32, 8, 1);
+    CHECK(f.push(nullptr, 0));
+    CHECK(f.available_frames() == 0);
+    float one = 1.0f;
+    CHECK(f.push(&one, 1));
+    CHECK(f.available_frames() == 1);                // ZERO_PAD: a partial frame is available
+    std::vector<float> sh(7, 0.5f);
+    CHECK(f.push(sh.data(), sh.size()));
+    CHECK(!f.push(nullptr, 3));
+  }
+  {  // BoundaryConditions :262-296
+    std::vector<float> sh(20, 1.0f), fr(32, 7.0f);
+    Framer pad, drop;
+    pad.set_params(32, 16, 1, BoundaryMode::ZERO_PAD);
+    drop.set_params(32, 16, 1, BoundaryMode::DROP);
+    CHECK(pad.push(sh.data(), 20));
+    CHECK(drop.push(sh.data(), 20));
+    CHECK(pad.pop(fr.data()));
+    bool ok = true;
+    for (int i = 0; i < 32; ++i) ok = ok && fr[i] == (i < 20 ? 1.0f : 0.0f);
+    CHECK(ok);
+    CHECK(pad.available_frames() == 1);              // 4 samples left -> one more padded frame
+    CHECK(pad.pop(fr.data()));
+    CHECK(fr[3] == 1.0f && fr[4] == 0.0f);
+    CHECK(pad.available_frames() == 0);              // cursor clamped at the write position
+    CHECK(!pad.pop(fr.data()));
+    CHECK(!drop.pop(fr.data()));
+    CHECK(drop.available_frames() == 0);
+    CHECK_THROWS(pad.set_params(0, 16), std::invalid_argument);
+    CHECK_THROWS(pad.set_params(32, 0), std::invalid_argument);
+    CHECK_THROWS(pad.set_params(32, 16, 0), std::invalid_argument);
+  }
+  {  // FramingCompatibilityFormula :299-322 and MemoryEfficiency-style long streaming
+    Framer f;
+    f.set_params(64, 16, 1);
+    std::vector<float> ones(200, 1.0f);
+    CHECK(f.push(ones.data(), 200));
+    CHECK(f.available_frames() == (200 - 64) / 16 + 1);
+    CHECK(f.buffer_size() == 256);                   // max(required 200, 2 * initial 128), framer.cc:120-126
+  }
+  {  // chunked streaming across compaction/growth: every frame equals the slice of the input
+    const size_t N = 256, H = 64, total = 40000;
+    std::vector<float> x = noise(total, 7);
+    Framer f;
+    f.set_params(N, H, 1, BoundaryMode::DROP);
+    std::vector<float> fr(N);
+    size_t pushed = 0, k = 0;
+    bool ok = true;
+    const size_t chunks[] = {1, 63, 64, 65, 300, 1024, 17, 4096};
+    for (size_t it = 0; pushed < total; ++it) {
+      const size_t c = std::min(chunks[it % 8], total - pushed);
+      f.push(x.data() + pushed, c);
+      pushed += c;
+      while (f.pop(fr.data())) {
+        for (size_t i = 0; i < N; ++i) ok = ok && fr[i] == x[k * H + i];
+        ++k;
+      }
+    }
+    CHECK(ok);
+    CHECK(k == (total - N) / H + 1);
+  }
+}
+
+// ---- WindowLUT (tests/window_lut_test.cc) --------------------------------------------------------
+static void test_window() {
+  WindowLUT hann(1024, WindowType::HANN);
+  CHECK(hann.size() == 1024 && hann.type() == WindowType::HANN && !hann.periodic());
+  CHECK(hann.data() != nullptr);
+  CHECK(std::fabs(hann.data()[0]) < 1e-7f && std::fabs(hann.data()[1023]) < 1e-6f);
+  CHECK(std::fabs(hann.data()[512] - 0.5f * (1.0f - std::cos(2.0 * M_PI * 512 / 1023.0))) < 1e-6f);
+  WindowLUT ham(512, WindowType::HAMMING, true);
+  CHECK(std::fabs(ham.data()[0] - 0.08f) < 1e-6f);
+  WindowLUT bl(512, WindowType::BLACKMAN);
+  CHECK(std::fabs(bl.data()[0]) < 1e-6f);
+  WindowLUT rect(64, WindowType::RECT);
+  CHECK(rect.data()[0] == 1.0f && rect.data()[63] == 1.0f);
+  WindowLUT s1(256, WindowType::HANN, false, NormalizationType::SUM_TO_ONE);
+  CHECK(std::fabs(WindowLUT::calculateSum(s1.data(), 256) - 1.0) < 1e-5);
+  WindowLUT l2(256, WindowType::HANN, false, NormalizationType::L2_NORM);
+  CHECK(std::fabs(WindowLUT::calculateSumOfSquares(l2.data(), 256) - 1.0) < 1e-5);
+  CHECK_THROWS(WindowLUT(0, WindowType::HANN), std::invalid_argument);
+  CHECK_THROWS(WindowLUT(16, WindowType::BLACKMAN_HARRIS), std::invalid_argument);
+  auto sp = WindowLUT::getInstance().GetWindowSafe(WindowType::HANN, 2048, true);
+  CHECK(sp && sp.get()[1024] == 1.0f);
+  dump("win_hann_2048_periodic", sp.get(), 2048);
+  dump("win_blackman_512", bl.data(), 512);
+}
+
+// ---- IFftPlan (tests/fft_test.cc) -----------------------------------------------------------------
+static void test_fft() {
+  for (int n : {512, 1024, 2048}) {
+    auto plan = MakeFftPlan({FftDomain::Real, n, false, 1, 1, 1});
+    CHECK(plan->size() == n && plan->domain() == FftDomain::Real && plan->max_batch_size() == 16);
+    std::vector<float> x = noise(n, 100 + n), y(n);
+    std::vector<std::complex<float>> X(n / 2 + 1);
+    plan->forward(x.data(), X.data());
+    plan->inverse(X.data(), y.data());
+    double e = 0;
+    for (int i = 0; i < n; ++i) e += (double)(y[i] - x[i]) * (y[i] - x[i]);
+    CHECK(std::sqrt(e / n) < 1e-5);                                  // :57-129
+    CHECK(X[0].imag() == 0.0f && X[n / 2].imag() == 0.0f);           // :344-382
+    std::vector<float> tone(n);
+    for (int i = 0; i < n; ++i) tone[i] = 2.0f * std::cos(2.0 * M_PI * 10 * i / n);
+    plan->forward(tone.data(), X.data());
+    CHECK(std::fabs(std::abs(X[10]) - n) < 1e-2 * n / 512);          // :131-197
+    if (n == 1024) {
+      dump("fft_x_1024", x.data(), n);
+      plan->forward(x.data(), X.data());
+      dump("fft_X_1024", reinterpret_cast<float*>(X.data()), 2 * (n / 2 + 1));
+    }
+  }
+  {  // NaNAndDenormalHandling :199-221
+    auto plan = MakeFftPlan({FftDomain::Real, 512, false, 1, 1, 1});
+    std::vector<float> x(512, 0.25f);
+    x[3] = NAN; x[9] = INFINITY; x[11] = 1e-38f;
+    std::vector<std::complex<float>> X(257);
+    plan->forward(x.data(), X.data());
+    bool fin = true;
+    for (auto& v : X) fin = fin && std::isfinite(v.real()) && std::isfinite(v.imag());
+    CHECK(fin);
+  }
+  // InvalidConfiguration :223-249 (std::runtime_error from the adapter)
+  CHECK_THROWS(MakeFftPlan({FftDomain::Real, 511, false, 1, 1, 1}), std::runtime_error);
+  CHECK_THROWS(MakeFftPlan({FftDomain::Real, 512, true, 1, 1, 1}), std::runtime_error);
+  CHECK_THROWS(MakeFftPlan({FftDomain::Real, 512, false, 0, 1, 1}), std::runtime_error);
+  CHECK_THROWS(MakeFftPlan({FftDomain::Real, 512, false, 17, 1, 1}), std::runtime_error);
+  CHECK_THROWS(MakeFftPlan({FftDomain::Real, 512, false, 1, 0, 1}), std::runtime_error);
+  {  // BatchProcessingReal :384-448
+    auto plan = MakeFftPlan({FftDomain::Real, 512, false, 4, 1, 1});
+    std::vector<float> x = noise(4 * 512, 5), y(4 * 512);
+    std::vector<std::complex<float>> X(4 * 257), X1(257);
+    plan->forward(x.data(), X.data(), 4);
+    auto one = MakeFftPlan({FftDomain::Real, 512, false, 1, 1, 1});
+    bool same = true;
+    for (int b = 0; b < 4; ++b) {
+      one->forward(x.data() + b * 512, X1.data());
+      for (int k = 0; k < 257; ++k) same = same && X1[k] == X[b * 257 + k];
+    }
+    CHECK(same);
+    CHECK_THROWS(plan->forward(x.data(), X.data(), 5), std::runtime_error);
+  }
+}
+
+// ---- OLAAccumulator (tests/ola_accumulator_test.cc) -----------------------------------------------
+static void test_ola() {
+  OLAConfig cfg{48000, 256, 64, 1, 1e-8f, true};
+  {
+    OLAAccumulator ola(cfg);
+    CHECK(ola.config().frame_size == 256 && ola.ring_size() == (256 / 64 + 20) * 64);     // :143-153
+    CHECK(!ola.has_window() && ola.produced_samples() == 0 && ola.read_pos() == 0);
+    WindowLUT w(256, WindowType::HANN);
+    ola.set_window(w.data(), 256);
+    CHECK(ola.has_window());
+    CHECK_THROWS(ola.set_window(w.data(), 128), std::invalid_argument);                    // :178-192
+    CHECK_THROWS(ola.set_window(nullptr, 256), std::invalid_argument);
+    std::vector<float> out(64);
+    float* outs[1] = {out.data()};
+    CHECK(ola.produce(outs, 0) == 0);                                                      // :279-292
+    CHECK(ola.produce(outs, 64) == 0);                                                     // nothing pushed yet
+  }
+  {
+    OLAConfig bad = cfg;
+    bad.frame_size = 0;
+    CHECK_THROWS(OLAAccumulator o(bad), std::invalid_argument);                            // :155-176
+    bad = cfg; bad.hop_size = 0;
+    CHECK_THROWS(OLAAccumulator o(bad), std::invalid_argument);
+    bad = cfg; bad.channels = 0;
+    CHECK_THROWS(OLAAccumulator o(bad), std::invalid_argument);
+    bad = cfg; bad.eps = 0.0f;
+    CHECK_THROWS(OLAAccumulator o(bad), std::invalid_argument);
+  }
+  {  // AoS == SoA :392-437, two channels, streaming drive
+    OLAConfig c2{48000, 512, 128, 2, 1e-8f, true};
+    OLAAccumulator a(c2), b(c2);
+    WindowLUT w(512, WindowType::HANN);
+    a.set_window(w.data(), 512);
+    b.set_window(w.data(), 512);
+    const int F = 20;                                             // stays below ring_size: read_pos does not wrap
+    std::vector<float> fr = noise((size_t)F * 2 * 512, 11);       // [frame][channel][sample]
+    std::vector<float> inter(1024), oa0(128), oa1(128), ob0(128), ob1(128), all_a, all_b;
+    bool same = true;
+    for (int k = 0; k < F; ++k) {
+      const float* p0 = fr.data() + (size_t)k * 1024;
+      const float* p1 = p0 + 512;
+      const float* chs[2] = {p0, p1};
+      for (int i = 0; i < 512; ++i) { inter[2 * i] = p0[i]; inter[2 * i + 1] = p1[i]; }
+      a.add_frame_SoA(chs, nullptr, (size_t)k * 128, 0, 512, 0.75f);
+      b.push_frame_AoS(inter.data(), nullptr, (size_t)k * 128, 0, 512, 0.75f);
+      float* oa[2] = {oa0.data(), oa1.data()};
+      float* ob[2] = {ob0.data(), ob1.data()};
+      const size_t na = a.produce(oa, 128), nb = b.produce(ob, 128);
+      same = same && na == nb && na == 128;
+      for (size_t i = 0; i < na; ++i) same = same && oa0[i] == ob0[i] && oa1[i] == ob1[i];
+      all_a.insert(all_a.end(), oa0.begin(), oa0.begin() + na);
+      all_b.insert(all_b.end(), oa1.begin(), oa1.begin() + na);
+    }
+    CHECK(same);
+    CHECK(a.produced_samples() == (size_t)(F - 1) * 128 + 512 && a.read_pos() == (size_t)F * 128);   // OLAAccumulator.cc:114,215
+    dump("ola_frames", fr.data(), fr.size());
+    dump("ola_out_ch0", all_a.data(), all_a.size());
+    dump("ola_out_ch1", all_b.data(), all_b.size());
+    a.reset();
+    CHECK(a.produced_samples() == 0 && a.read_pos() == 0);                                  // :307-332
+  }
+}
+
+// ---- the reference's FullPipeline loop, verbatim shape (bench/e2e_benchmark.cc:138-186) ------------
+static void test_e2e_loop() {
+  const size_t N = 1024, H = 256, L = 48000;
+  std::vector<float> in = noise(L, 2024);
+  WindowLUT lut(N, WindowType::HANN);
+  const float* window = lut.data();
+  Framer framer;
+  framer.set_params(N, H, 1, BoundaryMode::DROP);
+  OLAConfig cfg{48000, N, H, 1, 1e-8f, true};
+  OLAAccumulator ola(cfg);
+  ola.set_window(window, (int)N);
+  auto plan = MakeFftPlan({FftDomain::Real, (int)N, false, 1, 1, 1});
+
+  framer.push(in.data(), L);
+  std::vector<float> frame(N), proc(N), out_loop;
+  std::vector<std::complex<float>> spec(N / 2 + 1);
+  std::vector<float> hopbuf(H);
+  size_t k = 0;
+  while (framer.pop(frame.data())) {
+    for (size_t i = 0; i < N; ++i) proc[i] = frame[i] * window[i];
+    plan->forward(proc.data(), spec.data());
+    plan->inverse(spec.data(), proc.data());
+    ola.push_frame_AoS(proc.data(), nullptr, k * H, 0, N, 1.0f);
+    float* ch[1] = {hopbuf.data()};
+    const size_t n = ola.produce(ch, H);
+    out_loop.insert(out_loop.end(), hopbuf.begin(), hopbuf.begin() + n);
+    ++k;
+  }
+  CHECK(k == (L - N) / H + 1);
+  CHECK(out_loop.size() == k * H);
+
+  // the same signal through the whole-signal call
+  StftRoundTrip rt(N, H, window, window, BoundaryMode::DROP);
+  CHECK(rt.frames_for(L) == k);
+  std::vector<float> out_batch(rt.output_len_for(L));
+  const size_t n_out = rt.process(in.data(), L, L, 1, out_batch.data(), out_batch.size());
+  CHECK(n_out == (k - 1) * H + N);
+  size_t diff = 0;
+  double num = 0, den = 0;
+  for (size_t i = 0; i < out_loop.size(); ++i) {
+    if (out_loop[i] != out_batch[i]) ++diff;
+    num += (double)(out_loop[i] - out_batch[i]) * (out_loop[i] - out_batch[i]);
+    den += (double)out_batch[i] * out_batch[i];
+  }
+  std::printf("e2e loop vs whole-signal call: %zu of %zu samples differ in bits, rel-L2 %.3g\n", diff, out_loop.size(),
+              std::sqrt(num / den));
+  CHECK(std::sqrt(num / den) < 1e-6);
+  dump("e2e_in", in.data(), in.size());
+  dump("e2e_out_loop", out_loop.data(), out_loop.size());
+  dump("e2e_out_batch", out_batch.data(), n_out);
+}
+
+// ---- Framer -> kernel 1 without a host hop (B200 extension) -----------------------------------------
+static void test_framer_stft() {
+  const size_t N = 512, H = 128, C = 2, L = 10000;
+  std::vector<float> inter = noise(L * C, 99);
+  WindowLUT lut(N, WindowType::HAMMING);
+  Framer fr;
+  fr.set_params(N, H, C, BoundaryMode::DROP);
+  StftRoundTrip rt(N, H, lut.data(), lut.data(), BoundaryMode::DROP);
+  fr.push(inter.data(), L / 2);
+  fr.push(inter.data() + (L / 2) * C, L - L / 2);
+  const size_t F = fr.drainable_frames();
+  CHECK(F == (L - N) / H + 1);
+  const size_t bins = N / 2 + 1;
+  crlot_buf_t spec = nullptr;
+  detail::check(crlot_buf_create(C * F * bins * 2 * sizeof(float), 0, &spec));
+  long long got = 0;
+  detail::check(crlot_framer_stft(fr.handle(), rt.plan(), -1, crlot_buf_device_ptr(spec), &got, nullptr));
+  CHECK((size_t)got == F);
+  CHECK(fr.available_frames() == 0);
+  std::vector<float> S(C * F * bins * 2);
+  detail::check(crlot_buf_download(spec, 0, S.data(), S.size() * sizeof(float), nullptr));
+  detail::check(crlot_cuda_stream_sync(0, nullptr));
+  crlot_buf_destroy(spec);
+  dump("fstft_in_interleaved", inter.data(), inter.size());
+  dump("fstft_spec", S.data(), S.size());
+  // channel 1, frame 3 against the per-frame plan on the de-interleaved, windowed slice
+  std::vector<float> x(N);
+  for (size_t i = 0; i < N; ++i) x[i] = inter[(3 * H + i) * C + 1] * lut.data()[i];
+  auto plan = MakeFftPlan({FftDomain::Real, (int)N, false, 1, 1, 1});
+  std::vector<std::complex<float>> X(bins);
+  plan->forward(x.data(), X.data());
+  bool same = true;
+  for (size_t k = 0; k < bins; ++k) {
+    const float* s = &S[((1 * F + 3) * bins + k) * 2];
+    same = same && s[0] == X[k].real() && s[1] == X[k].imag();
+  }
+  CHECK(same);
+}
+
+int main(int argc, char** argv) {
+  g_out = argc > 1 ? argv[1] : ".";
+  int ndev = 0;
+  if (crlot_cuda_device_count(&ndev) != CRLOT_OK || ndev == 0) {
+    std::printf("no CUDA device: %s\n", crlot_cuda_last_error());
+    return 2;
+  }
+  try {
+    test_window();
+    test_framer();
+    test_fft();
+    test_ola();
+    test_e2e_loop();
+    test_framer_stft();
+  } catch (const std::exception& e) {
+    std::printf("unexpected exception: %s\n", e.what());
+    return 1;
+  }
+  std::printf("%d checks, %d failed\n", g_checks, g_fail);
+  return g_fail ? 1 : 0;
+}

@@ -192,6 +192,39 @@ int crlot_stream_last_spectra(crlot_stream_t st, void** d_spec, int* frames_per_
 /* what = 0 samples ingested per stream, 1 frames processed per stream, 2 ingest ring capacity */
 long long crlot_stream_get(crlot_stream_t st, int what);
 
+/* ---- drop-in Framer state (device-resident sample store) --------------------------------------- */
+/* replaces dsp::Framer   ref: dsp/frame/framer.h:25-131, dsp/frame/framer.cc:15-182
+ * Samples are de-interleaved once on push into a planar [channel][capacity] device buffer; frame
+ * extraction is then pure addressing inside kernel 1 (crlot_framer_stft).  pop() to a host pointer
+ * is kept for source compatibility.  available/advance/clamp/ZERO_PAD/DROP rules are the
+ * reference's (framer.cc:88-118,162-165). */
+typedef struct crlot_framer_s* crlot_framer_t;
+int crlot_framer_create(size_t frame_size, size_t hop_size, size_t channels, int boundary_mode, int device,
+                        crlot_framer_t* out);                                   /* Framer() + set_params */
+int crlot_framer_destroy(crlot_framer_t f);
+int crlot_framer_reset(crlot_framer_t f);                                       /* Framer::reset         */
+/* Framer::push: h_interleaved holds frames*channels floats ([frame][channel]) */
+int crlot_framer_push(crlot_framer_t f, const float* h_interleaved, size_t frames);
+/* same from device memory that is already planar: d_planar[c*chan_stride + (0..frames)) */
+int crlot_framer_push_device(crlot_framer_t f, const float* d_planar, long long chan_stride, size_t frames,
+                             void* stream);
+size_t crlot_framer_available(crlot_framer_t f);                                /* available_frames()    */
+/* Framer::pop: *popped = 1 and channels*frame_size interleaved floats in h_out_frame, or *popped = 0 */
+int crlot_framer_pop(crlot_framer_t f, float* h_out_frame, int* popped);
+/* Every frame that repeated pop() would deliver (at most max_frames; < 0 = all) goes through kernel
+ * 1 of `plan` straight from the device store: d_spec [channels][*n_frames][nfft/2+1] complex.
+ * The read cursor advances exactly as *n_frames pops would.
+ * replaces the pop / window / forward loop of bench/e2e_benchmark.cc:152-158 */
+int crlot_framer_stft(crlot_framer_t f, crlot_plan_t plan, long long max_frames, void* d_spec, long long* n_frames,
+                      void* stream);
+/* what = 0 frame_size, 1 hop_size, 2 channels, 3 boundary_mode, 4 buffer_size() as the reference
+ * would report it, 5 read cursor, 6 write cursor (per-channel samples), 7 device capacity per
+ * channel, 8 frames repeated pop() would deliver */
+size_t crlot_framer_get(crlot_framer_t f, int what);
+/* device view of the unread samples: returns &buf[0][read], *chan_stride floats between channels,
+ * *valid samples per channel */
+const float* crlot_framer_device_ptr(crlot_framer_t f, long long* chan_stride, long long* valid);
+
 /* ---- drop-in FFT plan (host pointers, reference batch/stride layout) --------------------------- */
 /* replaces dsp::fft::MakeFftPlan / IFftPlan::{forward,inverse} for FftDomain::Real
  *   ref: dsp/fft/api/fft_api.h:16-51; dsp/fft/backends/kissfft_adapter.cc:13-63,83-168
