@@ -236,6 +236,48 @@ class Plan:
                                           C.c_longlong(n_out), _stream_ptr(self.device)))
         return out
 
+    def istft_ola_supported(self, t_offset=0, frame_t0=0, out=None):
+        ptr = C.c_void_p(out.data_ptr() if out is not None else 0)
+        stride = out.stride(0) if out is not None and out.dim() == 2 and out.shape[0] > 1 else 0
+        return bool(lib().crlot_istft_ola_supported(self._h, C.c_longlong(t_offset), C.c_longlong(frame_t0), ptr,
+                                                    C.c_longlong(stride)))
+
+    def istft_ola(self, spec, t_offset=0, frame_t0=0, n_out=None, out=None, frames_per_chan=None):
+        """Kernels 2+3 fused.  spec: complex64 [channels, F, bins] -> float32 [channels, n_out];
+        bit-identical to ola(istft_frames(spec, True), prewindowed=True, ...)."""
+        torch = _torch()
+        if spec.dim() == 2:
+            spec = spec.unsqueeze(0)
+        ch, rows = spec.shape[0], spec.shape[1]
+        F = rows if frames_per_chan is None else frames_per_chan
+        if n_out is None:
+            n_out = (F - 1) * self.hop + self.nfft if F > 0 else 0
+        if out is None:
+            out = torch.empty((ch, n_out), dtype=torch.float32, device=spec.device)
+        _check(lib().crlot_istft_ola_execute(self._h, C.c_void_p(spec.data_ptr()), C.c_longlong(rows), C.c_longlong(F),
+                                             C.c_int(ch), C.c_longlong(t_offset), C.c_longlong(frame_t0),
+                                             C.c_void_p(out.data_ptr()), C.c_longlong(out.stride(0) if ch > 1 else 0),
+                                             C.c_longlong(n_out), _stream_ptr(self.device)))
+        return out
+
+    def roundtrip_fused(self, signal, spec=None, out=None, length=None):
+        """K1 -> fused K2+K3 (iFFT frames never materialised); returns (out, spec)."""
+        torch = _torch()
+        if signal.dim() == 1:
+            signal = signal.unsqueeze(0)
+        ch = signal.shape[0]
+        length = signal.shape[1] if length is None else length
+        F = self.n_frames(length)
+        if spec is None:
+            spec = torch.empty((ch, F, self.bins), dtype=torch.complex64, device=signal.device)
+        if out is None:
+            out = torch.empty((ch, self.out_len(length)), dtype=torch.float32, device=signal.device)
+        _check(lib().crlot_roundtrip_execute(self._h, C.c_void_p(signal.data_ptr()), C.c_longlong(signal.stride(0) if ch > 1 else 0),
+                                             C.c_longlong(length), C.c_int(ch), C.c_void_p(spec.data_ptr()),
+                                             C.c_void_p(0), C.c_void_p(out.data_ptr()),
+                                             C.c_longlong(out.stride(0) if ch > 1 else 0), _stream_ptr(self.device)))
+        return out, spec
+
     def roundtrip(self, signal, spec=None, frames=None, out=None, length=None):
         """K1 -> K2 (synthesis window fused) -> K3 on device tensors; returns (out, spec, frames)."""
         torch = _torch()

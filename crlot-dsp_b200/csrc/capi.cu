@@ -146,7 +146,7 @@ struct crlot_plan_s {
   int bins = 0;
   size_t ring_len = 0;
   bool syn_active = false;
-  DevArr<float> win_a, win_s, env;
+  DevArr<float> win_a, win_s, win_ones, env;
   DevArr<cpx> tw1, sa, pre;
   DevArr<unsigned int> counter;
   int k1_scrub = 0;            // kernel-1 clean-up mode (kernels.h)
@@ -315,6 +315,10 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
   const float* ws = desc->apply_window_inside ? desc->ola_window : desc->push_window;
   p->syn_active = ws != nullptr;
   if (ws) CU(p->win_s.upload(ws, N));
+  {
+    const std::vector<float> ones(N, 1.0f);          // the fused kernel always multiplies: y * 1.0f == y
+    CU(p->win_ones.upload(ones.data(), N));
+  }
   // envelope
   if (desc->envelope) {
     if (desc->envelope_len == 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "envelope_len is 0");
@@ -403,6 +407,41 @@ int crlot_ola_accumulate(crlot_plan_t plan, const float* d_frames, long long fra
   return CRLOT_OK;
 }
 
+static void fill_k23(K23Params& k, crlot_plan_t plan, int counter_word) {
+  k.nfft = plan->d.nfft; k.hop = plan->d.hop;
+  k.window = plan->syn_active ? plan->win_s.p : plan->win_ones.p;
+  k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.scrub = plan->d.scrub;
+  k.gain = plan->d.gain; k.eps = plan->d.eps; k.norm = plan->env.p; k.ring_len = static_cast<long long>(plan->ring_len);
+  k.counter = plan->counter.p + counter_word; k.chunk_blocks = 0;
+}
+
+int crlot_istft_ola_supported(crlot_plan_t plan, long long t_offset, long long frame_t0, const float* d_out,
+                              long long out_chan_stride) {
+  if (!plan) return 0;
+  return istft_ola_supported(plan->d.nfft, plan->d.hop, static_cast<long long>(plan->ring_len), t_offset, frame_t0,
+                             out_chan_stride, d_out, plan->env.p) ? 1 : 0;
+}
+
+int crlot_istft_ola_execute(crlot_plan_t plan, const void* d_spec, long long spec_chan_rows, long long frames_per_chan,
+                            int channels, long long t_offset, long long frame_t0, float* d_out,
+                            long long out_chan_stride, long long n_out, void* stream) {
+  if (!plan || !d_spec || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || frames_per_chan < 0 || n_out < 0 || t_offset < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (reinterpret_cast<uintptr_t>(d_spec) % 8 != 0) return fail(CRLOT_ERR_UNSUPPORTED, "buffers must be 8-byte aligned");
+  if (!crlot_istft_ola_supported(plan, t_offset, frame_t0, d_out, out_chan_stride))
+    return fail(CRLOT_ERR_UNSUPPORTED,
+                "fused inverse+overlap-add needs nfft <= 2048, hop a multiple of 64 (16 for nfft 256, 32 for 512/1024), "
+                "even offsets/strides; use crlot_istft_execute + crlot_ola_accumulate");
+  DeviceGuard g(plan->d.device);
+  K23Params k{};
+  fill_k23(k, plan, 2);
+  k.spec = static_cast<const cpx*>(d_spec); k.spec_chan_rows = spec_chan_rows; k.frames_per_chan = frames_per_chan;
+  k.channels = channels; k.t_offset = t_offset; k.frame_t0 = frame_t0; k.out = d_out; k.out_chan_stride = out_chan_stride;
+  k.n_out = n_out;
+  CU(launch_istft_ola(k, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
 int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
                             void* d_spec, float* d_frames, float* d_out, long long out_chan_stride, void* stream) {
   if (!plan) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
@@ -410,6 +449,9 @@ int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long 
   if (F == 0) return CRLOT_OK;
   int rc = crlot_stft_execute(plan, d_signal, chan_stride, len, channels, F, d_spec, stream);
   if (rc) return rc;
+  if (!d_frames)   // no materialisation of the iFFT frames requested: kernels 2+3 fused
+    return crlot_istft_ola_execute(plan, d_spec, F, F, channels, 0, 0, d_out, out_chan_stride,
+                                   (F - 1) * plan->d.hop + plan->d.nfft, stream);
   rc = crlot_istft_execute(plan, d_spec, F * channels, d_frames, 1, stream);
   if (rc) return rc;
   const long long n_out = (F - 1) * plan->d.hop + plan->d.nfft;
@@ -432,12 +474,14 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
   const long long overlap = (N + H - 1) / H - 1;
   const long long slab_hops = std::min<long long>(std::max<long long>((1ll << 24) / H, 4 * (overlap + 1)), F + overlap);
   const long long slab_frames = slab_hops + overlap;
+  // slab offsets are multiples of the hop, so one eligibility test covers every slab
+  const bool fused = istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, 0, nullptr, plan->env.p);
   if (plan->slot_frames < slab_frames) {
     for (auto& s : plan->slot) {
       if (!s.stream) CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
       CU(s.in.alloc(static_cast<size_t>((slab_frames - 1) * H + N)));
       CU(s.spec.alloc(static_cast<size_t>(slab_frames) * plan->bins));
-      CU(s.frames.alloc(static_cast<size_t>(slab_frames) * N));
+      if (!fused) CU(s.frames.alloc(static_cast<size_t>(slab_frames) * N));
       CU(s.out.alloc(static_cast<size_t>(slab_hops) * H + N));
     }
     plan->slot_frames = slab_frames;
@@ -462,6 +506,15 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
       k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p;
       k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2;
       CU(launch_stft_fwd(k1, s.stream));
+      if (fused) {
+        K23Params k{};
+        fill_k23(k, plan, 2 + (it & 1));
+        k.spec = s.spec.p; k.spec_chan_rows = nf; k.frames_per_chan = nf; k.channels = 1; k.t_offset = t0;
+        k.frame_t0 = s0 - t0; k.out = s.out.p; k.out_chan_stride = 0; k.n_out = t1 - t0;
+        CU(launch_istft_ola(k, s.stream));
+        CU(cudaMemcpyAsync(yout + t0, s.out.p, static_cast<size_t>(t1 - t0) * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        continue;
+      }
       K2Params k2{};
       k2.spec = s.spec.p; k2.rows = nf; k2.nfft = N; k2.frames = s.frames.p;
       k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.sa = plan->sa.p; k2.pre = plan->pre.p;

@@ -68,6 +68,34 @@ struct K3Params {
 };
 cudaError_t launch_ola_gather(const K3Params& p, cudaStream_t st);
 
+// ---- kernels 2+3 fused: inverse real FFT + synthesis window + overlap-add + normalise ------------
+// Same inputs as kernel 2 (spectra) and same outputs as kernel 3 (see K3Params for the meaning of
+// t_offset / frame_t0 / n_out); the iFFT frames stay in shared memory.  Bit-identical to K2 -> K3.
+struct K23Params {
+  const cpx* spec;              // [channels][spec_chan_rows][nfft/2+1]
+  long long spec_chan_rows;
+  long long frames_per_chan;
+  int channels;
+  int nfft, hop;
+  const float* window;          // device synthesis window or nullptr
+  const cpx* tw1;
+  const cpx* sa;
+  int scrub;
+  float gain, eps;
+  const float* norm;
+  long long ring_len;
+  long long t_offset, frame_t0;
+  float* out;
+  long long out_chan_stride;
+  long long n_out;
+  unsigned int* counter;        // zeroed work counter
+  int chunk_blocks;             // output hop blocks per scheduled chunk (0 = choose)
+  long long m_begin, m_end;     // filled by the launcher: hop blocks [m_begin, m_end) cover [0, n_out)
+};
+bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offset, long long frame_t0,
+                         long long out_chan_stride, const void* out, const void* norm);
+cudaError_t launch_istft_ola(K23Params p, cudaStream_t st);
+
 // ---- helpers ----------------------------------------------------------------------------------
 // x[c][i] = uniform[-1,1) from hash(seed, channel0 + c, i0 + i); same function as oracle/crlot_oracle.c
 cudaError_t launch_synth_uniform(float* out, long long chan_stride, int channels, long long n,

@@ -132,7 +132,23 @@ int crlot_ola_accumulate(crlot_plan_t plan, const float* d_frames, long long fra
                          long long frames_per_chan, int channels, int frames_prewindowed, long long t_offset,
                          long long frame_t0, float* d_out, long long out_chan_stride, long long n_out, void* stream);
 
-/* The composed round trip on device buffers (K1 -> K2 -> K3 on `stream`).  d_spec and d_frames
+/* Kernels 2+3 fused.  Same inputs as crlot_istft_execute (spectra [channels][spec_chan_rows][bins],
+ * frames_per_chan of them used per channel) and same outputs / t_offset / frame_t0 / n_out meaning
+ * as crlot_ola_accumulate, bit-identical to calling the two in sequence with the synthesis window
+ * fused -- but the iFFT frames stay in shared memory: per frame 8*bins bytes are read and 4*hop
+ * written, instead of 8*bins + 4*nfft + 4*nfft + 4*hop.  Returns CRLOT_ERR_UNSUPPORTED outside its
+ * shapes (crlot_istft_ola_supported() == 0): nfft <= 2048, hop a multiple of 64 (16 for nfft 256,
+ * 32 for 512/1024), even t_offset / frame_t0 / out_chan_stride, 8-byte aligned d_out.
+ * replaces: IFftPlan::inverse + OLAAccumulator::push_frame_AoS + produce
+ *   ref: kissfft_adapter.cc:124-168; OLAAccumulator.cc:54-122,162-221; dsp/ola/kernels.cc:18-36 */
+int crlot_istft_ola_supported(crlot_plan_t plan, long long t_offset, long long frame_t0, const float* d_out,
+                              long long out_chan_stride);
+int crlot_istft_ola_execute(crlot_plan_t plan, const void* d_spec, long long spec_chan_rows, long long frames_per_chan,
+                            int channels, long long t_offset, long long frame_t0, float* d_out,
+                            long long out_chan_stride, long long n_out, void* stream);
+
+/* The composed round trip on device buffers (K1 -> K2 -> K3 on `stream`, or K1 -> fused K2+K3 when
+ * d_frames is NULL).  d_spec and d_frames
  * are caller-provided materialisation buffers ([channels][n_frames][bins] complex and
  * [channels][n_frames][nfft] fp32).  n_frames = crlot_frame_count(len,...); output length per
  * channel = (n_frames-1)*hop + nfft.
