@@ -236,6 +236,12 @@ class Plan:
                                           C.c_longlong(n_out), _stream_ptr(self.device)))
         return out
 
+    def selftest_division(self, n=1 << 28, seed=1):
+        """Mismatches between the fused kernel's table-driven division and __fdiv_rn over n operand pairs."""
+        bad = C.c_ulonglong(0)
+        _check(lib().crlot_selftest_division(self._h, C.c_ulonglong(n), C.c_ulonglong(seed), C.byref(bad)))
+        return bad.value
+
     def istft_ola_supported(self, t_offset=0, frame_t0=0, out=None):
         ptr = C.c_void_p(out.data_ptr() if out is not None else 0)
         stride = out.stride(0) if out is not None and out.dim() == 2 and out.shape[0] > 1 else 0

@@ -53,7 +53,62 @@ __global__ void ring_produce_kernel(float* ring, long long ring_len, const float
   *acc = 0.0f;
 }
 
+__global__ void build_den_rcp_kernel(const float* __restrict__ norm, float eps, long long n, float2* __restrict__ out) {
+  const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i < n) {
+    const float b = fmaxf(norm[i], eps);
+    out[i] = make_float2(b, div_refined_rcp(b));
+  }
+}
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+// operand pairs: numerator = random sign/mantissa with exponent in [-60, 60] (or exactly 0 once in
+// 1024), denominator alternately a table entry and a random value with exponent in [-40, 40]
+__global__ void division_selftest_kernel(const float2* __restrict__ den_rcp, long long ring_len, unsigned long long n,
+                                         unsigned long long seed, unsigned long long* mismatches) {
+  unsigned long long bad = 0;
+  const unsigned long long stride = static_cast<unsigned long long>(gridDim.x) * blockDim.x;
+  for (unsigned long long i = blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x; i < n; i += stride) {
+    const unsigned long long h = mix64(seed ^ (i * 0xD6E8FEB86659FD93ull));
+    const unsigned long long h2 = mix64(h);
+    const unsigned int ea = 127u - 60u + static_cast<unsigned int>((h >> 32) % 120u);
+    float a = __uint_as_float((static_cast<unsigned int>(h) & 0x807fffffu) | (ea << 23));
+    if (((h >> 40) & 1023u) == 0u) a = 0.0f;
+    float b, r;
+    if (ring_len > 0 && (h2 & 1ull)) {
+      const float2 t = den_rcp[(h2 >> 8) % static_cast<unsigned long long>(ring_len)];
+      b = t.x; r = t.y;
+    } else {
+      const unsigned int eb = 127u - 40u + static_cast<unsigned int>((h2 >> 32) % 81u);
+      b = __uint_as_float((static_cast<unsigned int>(h2 >> 1) & 0x007fffffu) | (eb << 23));
+      r = div_refined_rcp(b);
+    }
+    if (!div_tail_ok(a)) { ++bad; continue; }
+    const float want = __fdiv_rn(a, b), got = div_tail(a, b, r);
+    if (__float_as_uint(want) != __float_as_uint(got)) ++bad;
+  }
+  if (bad) atomicAdd(mismatches, bad);
+}
+
 }  // namespace
+
+cudaError_t launch_build_den_rcp(const float* norm, float eps, long long n, float2* den_rcp, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  build_den_rcp_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(norm, eps, n, den_rcp);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_division_selftest(const float2* den_rcp, long long ring_len, unsigned long long n,
+                                     unsigned long long seed, unsigned long long* mismatches, cudaStream_t st) {
+  division_selftest_kernel<<<device_sm_count() * 8, 256, 0, st>>>(den_rcp, ring_len, n, seed, mismatches);
+  return cudaGetLastError();
+}
 
 cudaError_t launch_synth_uniform(float* out, long long chan_stride, int channels, long long n, unsigned long long seed,
                                  unsigned long long channel0, unsigned long long i0, cudaStream_t st) {

@@ -149,7 +149,9 @@ struct crlot_plan_s {
   DevArr<float> win_a, win_s, win_ones, env;
   DevArr<cpx> tw1, sa, pre;
   DevArr<unsigned int> counter;
+  DevArr<float2> den_rcp;      // {max(env, eps), refined reciprocal}: division table of the fused kernel 2+3
   int k1_scrub = 0;            // kernel-1 clean-up mode (kernels.h)
+  bool k23_win_ok = true;      // synthesis window can be pre-scaled by 2/N exactly (fused kernel 2+3)
   unsigned int tiny2 = 0;
   std::vector<float> env_host;
   HostSlot slot[2];
@@ -315,6 +317,9 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
   const float* ws = desc->apply_window_inside ? desc->ola_window : desc->push_window;
   p->syn_active = ws != nullptr;
   if (ws) CU(p->win_s.upload(ws, N));
+  if (ws)
+    for (int i = 0; i < N; ++i)
+      if (!std::isfinite(ws[i]) || (ws[i] != 0.0f && std::fabs(ws[i]) < 1e-25f)) p->k23_win_ok = false;
   {
     const std::vector<float> ones(N, 1.0f);          // the fused kernel always multiplies: y * 1.0f == y
     CU(p->win_ones.upload(ones.data(), N));
@@ -330,6 +335,19 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
     envelope_impl(p->env_host.data(), desc->ola_window, p->ring_len, N, desc->hop, desc->apply_window_inside, desc->eps);
   }
   CU(p->env.upload(p->env_host.data(), p->env_host.size()));
+  {
+    // the fused kernel's table-driven division needs every denominator well inside the normal range
+    bool ok = true;
+    for (float v : p->env_host) {
+      const float b = std::max(v, desc->eps);
+      if (!(b >= 9.094947017729282e-13f && b <= 1.099511627776e12f)) ok = false;   // [2^-40, 2^40]; NaN fails
+    }
+    if (ok) {
+      CU(p->den_rcp.alloc(p->env_host.size()));
+      CU(launch_build_den_rcp(p->env.p, desc->eps, static_cast<long long>(p->env_host.size()), p->den_rcp.p, nullptr));
+      CU(cudaStreamSynchronize(nullptr));
+    }
+  }
   const FftTables T = make_fft_tables(N);
   CU(upload_cpx(p->tw1, T.tw1));
   CU(upload_cpx(p->sa, T.sa));
@@ -412,12 +430,24 @@ static void fill_k23(K23Params& k, crlot_plan_t plan, int counter_word) {
   k.window = plan->syn_active ? plan->win_s.p : plan->win_ones.p;
   k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.scrub = plan->d.scrub;
   k.gain = plan->d.gain; k.eps = plan->d.eps; k.norm = plan->env.p; k.ring_len = static_cast<long long>(plan->ring_len);
+  k.den_rcp = plan->den_rcp.p;
   k.counter = plan->counter.p + counter_word; k.chunk_blocks = 0;
+}
+
+int crlot_selftest_division(crlot_plan_t plan, unsigned long long n, unsigned long long seed, unsigned long long* mismatches) {
+  if (!plan || !mismatches) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  DeviceGuard g(plan->d.device);
+  DevArr<unsigned long long> d;
+  CU(d.alloc(1));
+  CU(cudaMemset(d.p, 0, sizeof(unsigned long long)));
+  CU(launch_division_selftest(plan->den_rcp.p, plan->den_rcp.p ? static_cast<long long>(plan->ring_len) : 0, n, seed, d.p, nullptr));
+  CU(cudaMemcpy(mismatches, d.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return CRLOT_OK;
 }
 
 int crlot_istft_ola_supported(crlot_plan_t plan, long long t_offset, long long frame_t0, const float* d_out,
                               long long out_chan_stride) {
-  if (!plan) return 0;
+  if (!plan || !plan->k23_win_ok) return 0;
   return istft_ola_supported(plan->d.nfft, plan->d.hop, static_cast<long long>(plan->ring_len), t_offset, frame_t0,
                              out_chan_stride, d_out, plan->env.p) ? 1 : 0;
 }
@@ -475,7 +505,7 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
   const long long slab_hops = std::min<long long>(std::max<long long>((1ll << 24) / H, 4 * (overlap + 1)), F + overlap);
   const long long slab_frames = slab_hops + overlap;
   // slab offsets are multiples of the hop, so one eligibility test covers every slab
-  const bool fused = istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, 0, nullptr, plan->env.p);
+  const bool fused = plan->k23_win_ok && istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, 0, nullptr, plan->env.p);
   if (plan->slot_frames < slab_frames) {
     for (auto& s : plan->slot) {
       if (!s.stream) CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));

@@ -37,11 +37,23 @@ __host__ __device__ inline int k23_next_pow2(int v) {
   return r;
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 // RDIV = nfft / hop when that is 1, 2, 4 or 8 (hop known at compile time: the three register
-// classes above are compile-time ranges and the ring loads of a frame issue back to back), else 0
-// (any eligible hop; per-register tests at run time).  The synthesis window is always multiplied
-// in; "no window" is served by a table of ones (y * 1.0f == y exactly).
-template <int NFFT, int RDIV, bool SCRUB>
+// classes above are compile-time ranges, the ring loads of a frame issue back to back and all
+// addresses are base + immediate), else 0 (any eligible hop: every frame takes the rolled path).
+//
+// Shared-memory window table: ws[i] = (2/N) * w[i] (exact: a power-of-two scale; the host refuses
+// windows with non-zero values so small that the product would be subnormal).  "No window" is a
+// table of ones.  Fast path per frame: f = fl(v * ws) -- equal to fl(scrub(fl(v*2/N)) * w) whenever
+// the clean-up rule leaves every sample alone, which a screening pass over the registers decides
+// (non-finite, or 0 < |v*2/N| < 1e-30; zeros are fine: their sign cannot reach the output because
+// every sum starts from +0).  Frames that fail the screen, warm-up frames and ragged blocks take
+// the rolled path, which stages the raw iFFT output in the exchange buffer and applies the
+// reference formula sample by sample.
+template <int NFFT, int RDIV>
 __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23Params p, const int acap) {
   using X = GeoX<NFFT>;
   constexpr int C = X::C, G = X::G, A = X::A, B = X::B;
@@ -54,8 +66,9 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + acap);
   const int mask = acap - 1;
+  const float scale = 2.0f / static_cast<float>(NFFT);             // inv_split hands over halved values
 
-  for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+  for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i] * scale;
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     s_tw1[i] = p.tw1[i];
     s_sa[i] = p.sa[i];
@@ -70,9 +83,13 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
   const long long total_chunks = chunks_per_chan * p.channels;
   const long long u_cov = F > 0 ? (F - 1) * H + NFFT : 0;          // u >= u_cov: no frame contributes
   const int lp = mirror_lane<A>(lane);
-  const float scale = 2.0f / static_cast<float>(NFFT);             // inv_split hands over halved values
   const int ring_len = static_cast<int>(p.ring_len);
   const float gain = p.gain, eps = p.eps;
+  const cpx gain2 = mk(gain, gain);
+  // screen threshold on the raw registers: |v * 2/N| < 1e-30  <=>  |v| < 1e-30 * N/2 (exact scaling);
+  // compared as 2*bits - 2 so that +-0 wraps to the top (K1 uses the same trick)
+  const unsigned int tiny2 = 2u * __float_as_uint(1e-30f * (0.5f * NFFT)) - 2u;
+  const float unscale = 0.5f * NFFT;                                // ws * N/2 == w exactly
 
   for (;;) {
     unsigned long long q = 0;
@@ -91,27 +108,42 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
     for (int i = lane * 4; i < acap; i += 128) *reinterpret_cast<float4*>(ring + i) = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
 
-    // envelope phase of sample 0 of frame k0, advanced by hop per frame (no 64-bit modulo per frame)
-    int e_frame = 0;
+    // envelope phase of sample 0 of frame kbase, advanced per step (no 64-bit modulo per frame)
+    int e_base = 0;
     {
       long long e = (p.t_offset + p.frame_t0 + k0 * H) % ring_len;
       if (e < 0) e += ring_len;
-      e_frame = static_cast<int>(e);
+      e_base = static_cast<int>(e);
     }
-    const int e_step = H % ring_len;
+    const int e_hop = H % ring_len;
+
+    // spectrum rows of a step, straight into registers (8 bytes per lane, contiguous across the warp)
+    auto load_rows = [&](cpx (&dst)[32], cpx (&dnyq)[X::M1], long long kb) {
+      const long long lft = k1 - kb;
+#pragma unroll
+      for (int j = 0; j < X::M1; ++j) {
+        const int i1 = lane + 32 * j, g = i1 / A, a = i1 % A;
+        const bool ok = g < lft;
+        const cpx* row = spec + (kb + g) * (C + 1);
+#pragma unroll
+        for (int b = 0; b < B; ++b) dst[j * B + b] = ok ? ldg_stream(row + a + A * b) : mk(0.f, 0.f);
+        dnyq[j] = (ok && a == 0) ? ldg_stream(row + C) : mk(0.f, 0.f);
+      }
+    };
 
     for (long long kbase = k0; kbase < k1; kbase += G) {
       const long long left = k1 - kbase;
       cpx v[32];
       cpx nyq[X::M1];
+      load_rows(v, nyq, kbase);
+      // pull the next step's rows into L2 while this one is transformed (12 warps per SM cannot
+      // cover a DRAM round trip by themselves)
+      if (kbase + G < k1) {
+        const char* nxt = reinterpret_cast<const char*>(spec + (kbase + G) * (C + 1));
+        constexpr int kBytes = G * (C + 1) * 8;
 #pragma unroll
-      for (int j = 0; j < X::M1; ++j) {
-        const int i1 = lane + 32 * j, g = i1 / A, a = i1 % A;
-        const bool ok = g < left;
-        const cpx* row = spec + (kbase + g) * (C + 1);
-#pragma unroll
-        for (int b = 0; b < B; ++b) v[j * B + b] = ok ? ldg_stream(row + a + A * b) : mk(0.f, 0.f);
-        nyq[j] = (ok && a == 0) ? ldg_stream(row + C) : mk(0.f, 0.f);
+        for (int o = 0; o < (kBytes + 4095) / 4096; ++o)
+          if (o * 4096 + lane * 128 < kBytes) prefetch_l2(nxt + o * 4096 + lane * 128);
       }
       inv_split<X>(v, lane, s_sa,
                    [&](int r) {
@@ -126,102 +158,140 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
       __syncwarp();
       pass2<X, true>(v);
 
-      // f = fl( scrub(fl(y * 2/N)) * w ), in place, every frame of the step at once
+      // is every frame of this step a plain interior frame of the chunk?
+      const long long j_first = p.frame_t0 + kbase * H;               // output index of sample 0 of frame kbase
+      bool fast = RDIV > 0 && p.den_rcp != nullptr && left >= G && kbase >= m0 && j_first >= 0 && j_first + static_cast<long long>(G) * H <= p.n_out;
+      if (fast) {
+        unsigned int wm[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+        cpx nfs[4] = {mk(0.f, 0.f), mk(0.f, 0.f), mk(0.f, 0.f), mk(0.f, 0.f)};
 #pragma unroll
-      for (int j = 0; j < X::M2; ++j) {
-        const int ob = (lane + 32 * j) % B;
-#pragma unroll
-        for (int oa = 0; oa < A; ++oa) {
-          float y0 = v[j * A + oa].x * scale, y1 = v[j * A + oa].y * scale;
-          if (SCRUB) {
-            y0 = scrub(y0);
-            y1 = scrub(y1);
-          }
-          const float2 w = *reinterpret_cast<const float2*>(s_win + 2 * (ob + B * oa));
-          v[j * A + oa] = mk(__fmul_rn(y0, w.x), __fmul_rn(y1, w.y));
+        for (int r = 0; r < 32; ++r) {       // four independent chains
+          const unsigned int u0 = __float_as_uint(v[r].x), u1 = __float_as_uint(v[r].y);
+          wm[r & 3] = min(wm[r & 3], min(u0 + u0 - 2u, u1 + u1 - 2u));
+          nfs[r & 3] = fma2(v[r], mk(0.f, 0.f), nfs[r & 3]);
         }
+        const unsigned int wmin = min(min(wm[0], wm[1]), min(wm[2], wm[3]));
+        const cpx nf = (nfs[0] + nfs[1]) + (nfs[2] + nfs[3]);
+        const bool suspect = (wmin < tiny2) || (nf.x != 0.0f) || (nf.y != 0.0f);
+        fast = !__any_sync(0xffffffffu, suspect);
       }
 
-      // overlap-add, one frame at a time so that every ring cell sees its frames in ascending order
+      if (fast) {
+        constexpr int AE = RDIV > 0 ? A / RDIV : A;     // registers per hop
+        // {denominator, reciprocal} pairs of this lane's emit registers, requested before the ring work
+        float4 nm[X::M2][AE];
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
-        if (g < left) {
-          const long long k = kbase + g;
-          const long long u0 = k * H;
+        for (int j = 0; j < X::M2; ++j) {
+          const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
+          int e0 = e_base + g * e_hop;
+          e0 %= ring_len;
+#pragma unroll
+          for (int oa = 0; oa < AE; ++oa) {
+            int e = e0 + 2 * (ob + B * oa);
+            if (e >= ring_len) e -= ring_len;
+            nm[j][oa] = __ldg(reinterpret_cast<const float4*>(p.den_rcp + e));
+          }
+        }
+        // f = fl(v * ws), every frame of the step at once
+#pragma unroll
+        for (int j = 0; j < X::M2; ++j) {
+          const int ob = (lane + 32 * j) % B;
+#pragma unroll
+          for (int oa = 0; oa < A; ++oa)
+            v[j * A + oa] = mul2(v[j * A + oa], *reinterpret_cast<const cpx*>(s_win + 2 * (ob + B * oa)));
+        }
+        // overlap-add, one frame at a time so that every ring cell sees its frames in ascending order
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const long long u0 = (kbase + g) * H;
           const int r0 = static_cast<int>(u0 & mask);
-          const long long j0 = p.frame_t0 + u0;                           // output index of sample 0
-          const int e0 = e_frame;
-          e_frame += e_step;
-          if (e_frame >= ring_len) e_frame -= ring_len;
-          const bool fast = RDIV > 0 && k >= m0 && j0 >= 0 && j0 + H <= p.n_out;
-          if (fast) {
-            constexpr int AE = RDIV > 0 ? A / RDIV : A;     // registers per hop
 #pragma unroll
-            for (int j = 0; j < X::M2; ++j) {
-              const int i2 = lane + 32 * j, ob = i2 % B;
-              if (i2 / B == g) {
-                const int rb = r0 + 2 * ob;
+          for (int j = 0; j < X::M2; ++j) {
+            const int i2 = lane + 32 * j, ob = i2 % B;
+            if (i2 / B == g) {
+              const int rb = r0 + 2 * ob;
 #pragma unroll
-                for (int oa = 0; oa < A; ++oa) {            // all ring reads of the frame, back to back
-                  float2 a = make_float2(0.f, 0.f);
-                  if (oa < A - AE) a = *reinterpret_cast<const float2*>(ring + ((rb + 2 * B * oa) & mask));
-                  v[j * A + oa] = mk(__fmaf_rn(v[j * A + oa].x, gain, a.x), __fmaf_rn(v[j * A + oa].y, gain, a.y));
-                }
+              for (int oa = 0; oa < A; ++oa) {            // all ring reads of the frame, back to back
+                cpx a = mk(0.f, 0.f);
+                if (oa < A - AE) a = *reinterpret_cast<const cpx*>(ring + ((rb + 2 * B * oa) & mask));
+                v[j * A + oa] = fma2(v[j * A + oa], gain2, a);
+              }
 #pragma unroll
-                for (int oa = AE; oa < A; ++oa)
-                  *reinterpret_cast<float2*>(ring + ((rb + 2 * B * oa) & mask)) = make_float2(v[j * A + oa].x, v[j * A + oa].y);
-                float2 nm[AE];
+              for (int oa = AE; oa < A; ++oa) *reinterpret_cast<cpx*>(ring + ((rb + 2 * B * oa) & mask)) = v[j * A + oa];
+              float* dst = out + (p.frame_t0 + u0) + 2 * ob;
+              bool all_ok = true;
+#pragma unroll
+              for (int oa = 0; oa < AE; ++oa) {
+                const cpx a = v[j * A + oa];
+                const float4 t = nm[j][oa];
+                all_ok = all_ok && div_tail_ok(a.x) && div_tail_ok(a.y);
+                stg_stream(reinterpret_cast<cpx*>(dst + 2 * B * oa), mk(div_tail(a.x, t.x, t.y), div_tail(a.y, t.z, t.w)));
+              }
+              if (!all_ok) {                             // operands outside the tail's range: the full division
 #pragma unroll
                 for (int oa = 0; oa < AE; ++oa) {
-                  int e = e0 + 2 * (ob + B * oa);
-                  if (e >= ring_len) e -= ring_len;
-                  nm[oa] = __ldg(reinterpret_cast<const float2*>(p.norm + e));
+                  const cpx a = v[j * A + oa];
+                  const float4 t = nm[j][oa];
+                  stg_stream(reinterpret_cast<cpx*>(dst + 2 * B * oa), mk(__fdiv_rn(a.x, t.x), __fdiv_rn(a.y, t.z)));
                 }
-                float* dst = out + j0 + 2 * ob;
-#pragma unroll
-                for (int oa = 0; oa < AE; ++oa)
-                  stg_stream(reinterpret_cast<cpx*>(dst + 2 * B * oa),
-                             mk(__fdiv_rn(v[j * A + oa].x, fmaxf(nm[oa].x, eps)), __fdiv_rn(v[j * A + oa].y, fmaxf(nm[oa].y, eps))));
               }
             }
-          } else {
-            const int thr = k < m0 ? static_cast<int>((m0 - k) * H) : 0;   // warm-up: keep u >= m0*H only
-            const bool emit = k >= m0;
+          }
+          if (G > 1) __syncwarp();
+        }
+      } else {
+        // rolled path: raw iFFT output -> exchange buffer (natural order), then the reference formula
 #pragma unroll
-            for (int j = 0; j < X::M2; ++j) {
-              const int i2 = lane + 32 * j, ob = i2 % B;
-              if (i2 / B == g) {
+        for (int j = 0; j < X::M2; ++j) {
+          const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
 #pragma unroll
-                for (int oa = 0; oa < A; ++oa) {
-                  const int ib = 2 * B * oa;                 // warp-uniform part of the sample index
-                  if (ib < thr) continue;
-                  const int i = ib + 2 * ob;
-                  float* cell = ring + ((r0 + i) & mask);
-                  float2 a = make_float2(0.f, 0.f);
-                  if (ib < NFFT - H) a = *reinterpret_cast<const float2*>(cell);   // else: first touch
-                  a.x = __fmaf_rn(v[j * A + oa].x, gain, a.x);
-                  a.y = __fmaf_rn(v[j * A + oa].y, gain, a.y);
-                  if (emit && ib < H) {
-                    const long long jo = j0 + i;
-                    if (jo >= 0 && jo < p.n_out) {
-                      int e = e0 + i;
-                      if (e >= ring_len) e -= ring_len;
-                      const float2 nm = __ldg(reinterpret_cast<const float2*>(p.norm + e));
-                      const float o0 = __fdiv_rn(a.x, fmaxf(nm.x, eps));
-                      const float o1 = __fdiv_rn(a.y, fmaxf(nm.y, eps));
-                      if (jo + 1 < p.n_out) stg_stream(reinterpret_cast<cpx*>(out + jo), mk(o0, o1));
-                      else out[jo] = o0;
-                    }
-                  } else {
-                    *reinterpret_cast<float2*>(cell) = a;
-                  }
-                }
+          for (int oa = 0; oa < A; ++oa) ex[g * C + ob + B * oa] = v[j * A + oa];
+        }
+        __syncwarp();
+        for (int g = 0; g < G && g < left; ++g) {
+          const long long k = kbase + g;
+          const int thr = k < m0 ? static_cast<int>((m0 - k) * H) : 0;   // warm-up: keep u >= m0*H only
+          const bool emit = k >= m0;
+          const long long u0 = k * H;
+          const int r0 = static_cast<int>(u0 & mask);
+          const long long j0 = p.frame_t0 + u0;
+          const int e0 = (e_base + g * e_hop) % ring_len;
+          for (int o = lane; o < C; o += 32) {
+            const int i = 2 * o;
+            if (i < thr) continue;                        // thr is a multiple of 64: warp-uniform
+            const cpx raw = ex[g * C + o];
+            float y0 = raw.x * scale, y1 = raw.y * scale;
+            if (p.scrub) {
+              y0 = scrub(y0);
+              y1 = scrub(y1);
+            }
+            const float2 w = *reinterpret_cast<const float2*>(s_win + i);
+            y0 = __fmul_rn(y0, w.x * unscale);
+            y1 = __fmul_rn(y1, w.y * unscale);
+            float* cell = ring + ((r0 + i) & mask);
+            float2 a = make_float2(0.f, 0.f);
+            if (i < NFFT - H) a = *reinterpret_cast<const float2*>(cell);     // else: first touch
+            a.x = __fmaf_rn(y0, gain, a.x);
+            a.y = __fmaf_rn(y1, gain, a.y);
+            if (emit && i < H) {
+              const long long jo = j0 + i;
+              if (jo >= 0 && jo < p.n_out) {
+                int e = e0 + i;
+                if (e >= ring_len) e -= ring_len;
+                const float2 nm = __ldg(reinterpret_cast<const float2*>(p.norm + e));
+                const float o0 = __fdiv_rn(a.x, fmaxf(nm.x, eps));
+                const float o1 = __fdiv_rn(a.y, fmaxf(nm.y, eps));
+                if (jo + 1 < p.n_out) stg_stream(reinterpret_cast<cpx*>(out + jo), mk(o0, o1));
+                else out[jo] = o0;
               }
+            } else {
+              *reinterpret_cast<float2*>(cell) = a;
             }
           }
           __syncwarp();
         }
       }
+      e_base = (e_base + G * e_hop) % ring_len;
     }
 
     // blocks of this chunk that have no frame of their own: before frame 0 (zeros) and the
@@ -255,7 +325,7 @@ cudaError_t launch_k23(const K23Params& p, cudaStream_t st) {
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
   const int rdiv = (NFFT % p.hop == 0) ? NFFT / p.hop : 0;
   void (*kern)(const K23Params, const int) = nullptr;
-#define CRLOT_K23_PICK(RD) kern = p.scrub ? istft_ola_kernel<NFFT, RD, true> : istft_ola_kernel<NFFT, RD, false>
+#define CRLOT_K23_PICK(RD) kern = istft_ola_kernel<NFFT, RD>
   switch (rdiv) {
     case 1: CRLOT_K23_PICK(1); break;
     case 2: CRLOT_K23_PICK(2); break;

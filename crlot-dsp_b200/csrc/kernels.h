@@ -83,6 +83,7 @@ struct K23Params {
   int scrub;
   float gain, eps;
   const float* norm;
+  const float2* den_rcp;        // [ring_len] {max(norm, eps), refined reciprocal} or nullptr (common.cuh)
   long long ring_len;
   long long t_offset, frame_t0;
   float* out;
@@ -95,6 +96,13 @@ struct K23Params {
 bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offset, long long frame_t0,
                          long long out_chan_stride, const void* out, const void* norm);
 cudaError_t launch_istft_ola(K23Params p, cudaStream_t st);
+
+// den_rcp[i] = {max(norm[i], eps), div_refined_rcp(max(norm[i], eps))}
+cudaError_t launch_build_den_rcp(const float* norm, float eps, long long n, float2* den_rcp, cudaStream_t st);
+// compares div_tail with __fdiv_rn on `n` hashed operand pairs inside the tail's operand range plus
+// the plan's own denominators; *mismatches (device) is incremented per differing result
+cudaError_t launch_division_selftest(const float2* den_rcp, long long ring_len, unsigned long long n,
+                                     unsigned long long seed, unsigned long long* mismatches, cudaStream_t st);
 
 // ---- helpers ----------------------------------------------------------------------------------
 // x[c][i] = uniform[-1,1) from hash(seed, channel0 + c, i0 + i); same function as oracle/crlot_oracle.c

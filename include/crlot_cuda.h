@@ -147,6 +147,12 @@ int crlot_istft_ola_execute(crlot_plan_t plan, const void* d_spec, long long spe
                             int channels, long long t_offset, long long frame_t0, float* d_out,
                             long long out_chan_stride, long long n_out, void* stream);
 
+/* Self-test of the fused kernel's table-driven IEEE division (csrc/common.cuh div_tail): n hashed
+ * operand pairs, including the plan's own envelope denominators, compared bit for bit with the
+ * hardware-correct __fdiv_rn on the device; *mismatches receives the number that differ (must be 0). */
+int crlot_selftest_division(crlot_plan_t plan, unsigned long long n, unsigned long long seed,
+                            unsigned long long* mismatches);
+
 /* The composed round trip on device buffers (K1 -> K2 -> K3 on `stream`, or K1 -> fused K2+K3 when
  * d_frames is NULL).  d_spec and d_frames
  * are caller-provided materialisation buffers ([channels][n_frames][bins] complex and

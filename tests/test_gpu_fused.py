@@ -128,3 +128,30 @@ def test_roundtrip_host_uses_fused_path_same_bits(cuda, dsp, oracle):
     got = plan.roundtrip_host(x)
     want, _, _ = plan.roundtrip(dev(cuda, x))
     assert np.array_equal(bits(got), bits(want.cpu().numpy()))
+
+
+def test_table_division_equals_fdiv_rn(cuda, dsp, oracle):
+    """The fused kernel divides by tabulated envelope values with the 3-FFMA tail of __fdiv_rn
+    (csrc/common.cuh); 2^30 hashed operand pairs per plan must agree bit for bit with __fdiv_rn."""
+    for N, H, wt, eps in ((2048, 512, po.HANN, 1e-8), (1024, 256, po.HAMMING, 1e-3), (256, 64, po.BLACKMAN, 1e-8)):
+        w = oracle.window(wt, N)
+        plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, eps=eps)
+        assert plan.selftest_division(1 << 30, seed=N + 1) == 0
+
+
+def test_fused_extreme_amplitudes_take_exact_division(cuda, dsp, oracle):
+    """Accumulator values outside the table division's operand range (huge, tiny, zero) must still be
+    bit-identical to kernel 3's __fdiv_rn."""
+    N, H, F = 2048, 512, 40
+    rng = np.random.default_rng(11)
+    w = oracle.window(po.HANN, N)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, scrub=False)
+    Xh = rand_spec(rng, 1, F, N)
+    Xh[0, 5:9] *= 1e25            # |acc| ~ 1e24 > 2^60
+    Xh[0, 15:19] *= 1e-27         # |acc| ~ 1e-26 < 2^-60 (kept: scrub is off)
+    Xh[0, 25:30] = 0
+    X = dev(cuda, Xh)
+    want = plan.ola(plan.istft_frames(X, True), prewindowed=True)
+    got = plan.istft_ola(X)
+    cuda.cuda.synchronize()
+    assert np.array_equal(bits(got.cpu().numpy()), bits(want.cpu().numpy()))
