@@ -481,6 +481,59 @@ def main():
                 "path": {"bytes_per_sample": dsp.bytes_per_sample(N, H), "achieved_GBps_per_gpu": path_gbps,
                          "frac_of_measured": path_gbps / peak, "frac_of_8TBps_nominal": path_gbps / 8000.0}}
 
+    # measured DRAM traffic of the dominant kernel, from the committed ncu --set full capture
+    # (profiles/traffic.json: bytes per frame, read+write, per kernel and frame size)
+    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_path):
+        tj = json.load(open(traffic_path))
+        ent = tj.get("kernels", {}).get(f"{dom}_n{N}_h{H}")
+        if ent:
+            roofline["traffic"] = ent["dram_bytes_per_frame"] * frames_per_launch
+            roofline["traffic_source"] = f"profiles/traffic.json ({ent['source']}), bytes/frame x frames per launch"
+
+    # ---- the same round trip with kernels 2+3 fused (iFFT frames never materialised) --------------
+    fused = None
+    if args.workload != "c4" and plan.istft_ola_supported():
+        def fstep(record=None):
+            for c0 in range(0, chans, batch):
+                xb = x[c0:c0 + batch]
+                if record is not None:
+                    e = [ev() for _ in range(3)]
+                    e[0].record()
+                plan.stft(xb, out=spec)
+                if record is not None:
+                    e[1].record()
+                plan.istft_ola(spec, out=out[c0:c0 + batch])
+                if record is not None:
+                    e[2].record()
+                    record.append(e)
+        for _ in range(args.warmup):
+            fstep()
+        sync_all()
+        rec = []
+        f_beg, f_end = ev(), ev()
+        f_beg.record()
+        for _ in range(args.steps):
+            fstep(rec)
+        f_end.record()
+        sync_all()
+        fms = torch.tensor([f_beg.elapsed_time(f_end)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(fms, op=dist.ReduceOp.MAX)
+        fms = float(fms.item())
+        fk1 = float(np.mean([e[0].elapsed_time(e[1]) for e in rec]))
+        fk23 = float(np.mean([e[1].elapsed_time(e[2]) for e in rec]))
+        alg23 = (8.0 * bins + 4.0 * H) * frames_per_launch
+        fbps = 8.0 + 16.0 * bins / H
+        fval = total_samples * args.steps / (fms * 1e-3)
+        fused = {"value": fval / 1e6, "unit": "Msamples/s", "ms_per_step": fms / args.steps,
+                 "kernels": "stft_fwd_kernel (K1) + istft_ola_kernel (K2+K3 fused, bit-identical output)",
+                 "k1_ms": fk1, "k23_ms": fk23, "k23_alg_GB": alg23 / 1e9, "k23_GBps": alg23 / (fk23 * 1e-3) / 1e9,
+                 "k23_frac": alg23 / (fk23 * 1e-3) / 1e9 / peak, "bytes_per_sample": fbps,
+                 "path_GBps_per_gpu": fbps * (fval / world) / 1e9, "path_frac_of_measured": fbps * (fval / world) / 1e9 / peak,
+                 "note": "the fused path moves 8+16*bins/hop bytes per sample instead of 8+16*bins/hop+8*N/hop; `value` "
+                         "above stays on the three-kernel path that BASELINE.json's north_star names"}
+
     # ---- e2e: host buffers through the C-ABI host entry point, copies inside the timed region -----
     e2e = None
     if not args.no_e2e:
@@ -504,8 +557,9 @@ def main():
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": ce * Le * world * n_e2e / float(dt.item()) / 1e6, "unit": "Msamples/s",
                "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": ce * n_out_e * 4, "steps": n_e2e,
-               "api": "crlot_roundtrip_host (pinned host buffers, slabbed H2D/compute/D2H pipeline)",
-               "workload": f"{ce}ch x 2^{int(np.log2(Le))} samples per rank"}
+               "api": "crlot_roundtrip_host (pinned host buffers, slabbed H2D/compute/D2H pipeline; K1 + fused K2+K3 per slab)",
+               "workload": f"{ce}ch x 2^{int(np.log2(Le))} samples per rank",
+               "ceiling": "PCIe: 45.8 GB/s per direction with H2D and D2H running together (tools/pcie_probe.py) = 11.4 Gsamples/s per GPU"}
         del hin, hout
 
     cpu = None
@@ -526,7 +580,7 @@ def main():
                        "samples_per_rank": local_samples, "frames_per_launch": frames_per_launch,
                        "cache": "inputs larger than L2 (every buffer >> 126 MB), no flush needed",
                        "generator": "counter hash uniform[-1,1), seed 0xC0FFEE"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
+            "roofline": roofline, "fused_k23": fused, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

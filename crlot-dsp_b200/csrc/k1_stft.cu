@@ -35,7 +35,7 @@ __host__ __device__ inline int next_pow2(int v) {
 template <int NFFT>
 struct K1Smem {
   using X = GeoX<NFFT>;
-  static constexpr int kTableBytes = NFFT * 4 + X::C * 8 + X::C * 8;
+  static constexpr int kTableBytes = NFFT * 4 + X::C * 8;
   __host__ __device__ static int per_warp_bytes(int rcap) { return rcap * 4 + X::XCPX * 8 + 16; }
   __host__ __device__ static int total(int rcap, int nwarps) { return kTableBytes + nwarps * per_warp_bytes(rcap); }
 };
@@ -83,19 +83,16 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
-  cpx* s_sa = s_tw1 + C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wb = reinterpret_cast<unsigned char*>(s_sa + C) + warp * K1Smem<NFFT>::per_warp_bytes(rcap);
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_tw1 + C) + warp * K1Smem<NFFT>::per_warp_bytes(rcap);
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + rcap);
   const uint32_t bar = smem_u32(ex + X::XCPX);
   const int mask = rcap - 1;
 
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    s_tw1[i] = p.tw1[i];
-    s_sa[i] = p.sa[i];
-  }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  const SplitLane<X::M2> SL = make_split_fwd<X>(lane);   // lane factors of the real split (no table)
   if (lane == 0) {
     mbar_init(bar, 1);
     fence_mbar_init();
@@ -184,12 +181,10 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
       xchg_read<X>(v, lane, ex);
       __syncwarp();
       pass2<X, false>(v);
-      cpx nyq[X::M2];
-      fwd_split<X>(v, lane, s_sa,
-                   [&](int r) {
-                     return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
-                   },
-                   nyq);
+      cpx nyq[X::M2], mid[X::M2];
+      auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp)); };
+      fwd_split_pairs<X>(v, lane, SL, mirror, nyq, mid);
+      fwd_split_finish<X>(v, lane, mirror, mid);
 
       const long long left = nfr - static_cast<long long>(s) * G;
 #pragma unroll

@@ -60,19 +60,16 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
-  cpx* s_sa = s_tw1 + C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wb = reinterpret_cast<unsigned char*>(s_sa + C) + warp * (acap * 4 + X::XCPX * 8);
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_tw1 + C) + warp * (acap * 4 + X::XCPX * 8);
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + acap);
   const int mask = acap - 1;
   const float scale = 2.0f / static_cast<float>(NFFT);             // inv_split hands over halved values
 
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i] * scale;
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    s_tw1[i] = p.tw1[i];
-    s_sa[i] = p.sa[i];
-  }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  const SplitLane<X::M1> SL = make_split_inv<X>(lane);   // lane factors of the real split (no table)
   __syncthreads();
 
   const int H = RDIV > 0 ? NFFT / (RDIV > 0 ? RDIV : 1) : p.hop;
@@ -145,11 +142,12 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
         for (int o = 0; o < (kBytes + 4095) / 4096; ++o)
           if (o * 4096 + lane * 128 < kBytes) prefetch_l2(nxt + o * 4096 + lane * 128);
       }
-      inv_split<X>(v, lane, s_sa,
-                   [&](int r) {
-                     return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
-                   },
-                   nyq);
+      {
+        cpx mid[X::M1];
+        auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp)); };
+        inv_split_pairs<X>(v, lane, SL, mirror, nyq, mid);
+        inv_split_finish<X>(v, lane, mirror, mid);
+      }
       pass1<X, true>(v);
       twiddle1<X, true>(v, lane, s_tw1);
       xchg_write<X>(v, lane, ex);
@@ -321,7 +319,7 @@ cudaError_t launch_k23(const K23Params& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
   const int S = (X::G - 1) * p.hop + NFFT;
   const int acap = k23_next_pow2(S);
-  const int smem = NFFT * 4 + X::C * 16 + kK23Warps * (acap * 4 + X::XCPX * 8);
+  const int smem = NFFT * 4 + X::C * 8 + kK23Warps * (acap * 4 + X::XCPX * 8);
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
   const int rdiv = (NFFT % p.hop == 0) ? NFFT / p.hop : 0;
   void (*kern)(const K23Params, const int) = nullptr;

@@ -28,16 +28,13 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
-  cpx* s_sa = s_tw1 + C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  cpx* ex = s_sa + C + warp * X::XCPX;
+  cpx* ex = s_tw1 + C + warp * X::XCPX;
 
   if (WIN)
     for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    s_tw1[i] = p.tw1[i];
-    s_sa[i] = p.sa[i];
-  }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  const SplitLane<X::M1> SL = make_split_inv<X>(lane);   // lane factors of the real split (no table)
   __syncthreads();
 
   const long long total_steps = (p.rows + G - 1) / G;
@@ -59,11 +56,10 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
       for (int b = 0; b < B; ++b) v[j * B + b] = ok ? ldg_stream(row + a + A * b) : mk(0.f, 0.f);
       nyq[j] = (ok && a == 0) ? ldg_stream(row + C) : mk(0.f, 0.f);
     }
-    inv_split<X>(v, lane, s_sa,
-                 [&](int r) {
-                   return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
-                 },
-                 nyq);
+    cpx mid[X::M1];
+    auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp)); };
+    inv_split_pairs<X>(v, lane, SL, mirror, nyq, mid);
+    inv_split_finish<X>(v, lane, mirror, mid);
     pass1<X, true>(v);
     twiddle1<X, true>(v, lane, s_tw1);
     __syncwarp();                 // previous step's exchange reads are complete
@@ -182,7 +178,7 @@ template <int NFFT>
 cudaError_t launch_k2(const K2Params& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
   const bool win = p.window != nullptr;
-  const int smem = (win ? NFFT * 4 : 0) + X::C * 16 + kK2Warps * X::XCPX * 8;
+  const int smem = (win ? NFFT * 4 : 0) + X::C * 8 + kK2Warps * X::XCPX * 8;
   void (*kern)(const K2Params) = nullptr;
   if (win) kern = p.scrub ? istft_inv_kernel<NFFT, true, true> : istft_inv_kernel<NFFT, true, false>;
   else     kern = p.scrub ? istft_inv_kernel<NFFT, false, true> : istft_inv_kernel<NFFT, false, false>;

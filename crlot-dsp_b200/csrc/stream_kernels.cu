@@ -64,14 +64,11 @@ __global__ void __launch_bounds__(kSWarps * 32) stream_fwd_kernel(const StreamFw
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
-  cpx* s_sa = s_tw1 + C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  cpx* ex = s_sa + C + warp * X::XCPX;
+  cpx* ex = s_tw1 + C + warp * X::XCPX;
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    s_tw1[i] = p.tw1[i];
-    s_sa[i] = p.sa[i];
-  }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  const SplitLane<X::M2> SL = make_split_fwd<X>(lane);
   __syncthreads();
 
   const long long k0 = p.ctr->k;
@@ -108,12 +105,10 @@ __global__ void __launch_bounds__(kSWarps * 32) stream_fwd_kernel(const StreamFw
     __syncwarp();
     xchg_read<X>(v, lane, ex);
     pass2<X, false>(v);
-    cpx nyq[X::M2];
-    fwd_split<X>(v, lane, s_sa,
-                 [&](int r) {
-                   return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
-                 },
-                 nyq);
+    cpx nyq[X::M2], mid[X::M2];
+    auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp)); };
+    fwd_split_pairs<X>(v, lane, SL, mirror, nyq, mid);
+    fwd_split_finish<X>(v, lane, mirror, mid);
 #pragma unroll
     for (int j = 0; j < X::M2; ++j) {
       const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
@@ -187,7 +182,7 @@ __global__ void stream_advance_kernel(StreamCounters* ctr, int chunk_len, int nf
 template <int NFFT>
 cudaError_t launch_fwd_t(const StreamFwdParams& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
-  const int smem = NFFT * 4 + X::C * 16 + kSWarps * X::XCPX * 8;
+  const int smem = NFFT * 4 + X::C * 8 + kSWarps * X::XCPX * 8;
   auto kern = p.scrub ? stream_fwd_kernel<NFFT, true> : stream_fwd_kernel<NFFT, false>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;

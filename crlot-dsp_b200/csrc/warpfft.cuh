@@ -18,6 +18,8 @@
 // Everything here is a function of (lane, registers) so that tests/cpu_emu can run the same
 // code lane by lane on the CPU (index algebra check without a GPU).
 #pragma once
+#include <math.h>
+
 #include "regfft.cuh"
 
 namespace crlot {
@@ -102,69 +104,147 @@ template <class X> CRLOT_HD void out_coord(int lane, int r, int& g, int& o) {
 // A-1-oa, except for ob == 0 where it is the lane's own register (A-oa)%A.  Same algebra
 // with (A,a,b) for the pass-1 view.
 //
-// Forward (after pass 2), k = o, M = Z[C-k]:
-//   X[k] = 0.5*(Z + conj M) + 0.5*t_k*(Z - conj M),  t_k = exp(-i pi (k/C + 1/2))
-//        = conj(M) + A_k*(Z - conj M),               A_k = 0.5*(1 + t_k)
-//   (kiss_fftr.c:53-59,101-116 of the reference, restated; 5 packed instructions per bin)
+// Forward (after pass 2).  For the PAIR k, C-k with z = Z[k], m = Z[C-k], w_k = exp(-i pi k/C):
+//   s = z + conj m,  d = z - conj m,  f = (-i/2) w_k d
+//   X[k] = s/2 + f            X[C-k] = conj(s/2 - f)
+//   (kiss_fftr.c:53-59,101-116 of the reference, restated)
+// One lane computes BOTH bins of a pair -- those of its registers oa < A/2 -- and hands X[C-k] to
+// the lane that stores it, so the pair costs 9 packed instructions instead of 2 x 5, and no table
+// is read: with k = ob + B*oa,  w_k = exp(-i pi ob/C) * exp(-i pi oa/A)  = (lane constant) x
+// (compile-time constant).  The lane constants (SplitLane) are computed once per kernel in double.
 //   k = 0 gives X[0] = Re+Im, X[C] = Re-Im with exactly zero imaginary parts.
-// sa[] is the table sa[k] = A_k, k in [0,C).
-// `peer(r)` returns register r of the partner lane (a warp shuffle on the device).
-template <class X, class Peer>
-CRLOT_HD void fwd_split(cpx (&v)[32], int lane, const cpx* sa, Peer peer, cpx (&nyq)[X::M2]) {
-  cpx out[32];
-#pragma unroll
-  for (int j = 0; j < X::M2; ++j) {
-    const int ob = (lane + 32 * j) % X::B;
-#pragma unroll
-    for (int oa = 0; oa < X::A; ++oa) {
-      const cpx z = v[j * X::A + oa];
-      const cpx far = peer(j * X::A + (X::A - 1 - oa));
-      const cpx own = v[j * X::A + (X::A - oa) % X::A];
-      const cpx m = (ob == 0) ? own : far;                   // Z[C-k]
-      const cpx ds = fma2(m, mk(-1.f, 1.f), z);              // Z - conj(M)
-      const cpx mc = mul2(m, mk(1.f, -1.f));                 // conj(M)
-      out[j * X::A + oa] = cfma(ds, sa[ob + X::B * oa], mc);
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < X::M2; ++j) {
-    const int ob = (lane + 32 * j) % X::B;
-    if (ob == 0) {   // k = 0 of frame g: exact DC and Nyquist (ob = lane % B for every j)
-      const cpx z = v[j * X::A];
-      out[j * X::A] = mk(z.x + z.y, 0.0f);
-      nyq[j] = mk(z.x - z.y, 0.0f);
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < 32; ++r) v[r] = out[r];
+// The split runs in two phases because values travel between lanes twice:
+//   phase A (split_pairs):  needs peer(r) = register r of the mirror lane BEFORE the phase
+//   phase B (split_finish): needs peer(r) = register r of the mirror lane AFTER phase A
+// (on the device both are warp shuffles of the live registers; the CPU emulator snapshots).
+
+// cos(2 pi n/64), n = 0..16
+CRLOT_HD constexpr float c64(int n) {
+  return n == 0 ? 1.0f : n == 1 ? 0.99518472667219688624f : n == 2 ? 0.98078528040323044913f
+       : n == 3 ? 0.95694033573220886494f : n == 4 ? 0.92387953251128675613f : n == 5 ? 0.88192126434835502971f
+       : n == 6 ? 0.83146961230254523708f : n == 7 ? 0.77301045336273696081f : n == 8 ? 0.70710678118654752440f
+       : n == 9 ? 0.63439328416364549822f : n == 10 ? 0.55557023301960222474f : n == 11 ? 0.47139673682599764856f
+       : n == 12 ? 0.38268343236508977173f : n == 13 ? 0.29028467725446236764f : n == 14 ? 0.19509032201612826785f
+       : n == 15 ? 0.09801714032956060199f : 0.0f;
+}
+// exp(-/+ i pi n/D) for 0 <= n <= D/2 (first quadrant), D in {8,16,32}: the compile-time factor
+template <int D, int n, bool CONJ> CRLOT_HD cpx wq() {
+  static_assert(D == 8 || D == 16 || D == 32, "split constants: 2D in {16,32,64}");
+  static_assert(n >= 0 && 2 * n <= D, "first quadrant only");
+  constexpr int m = n * (32 / D);                       // angle = 2 pi m/64
+  return mk(c64(m), CONJ ? c64(16 - m) : -c64(16 - m));
 }
 
-// Inverse (before pass 1), k = i, M = X[C-k]:
-//   Z'[k] = (X + conj M) + u_k*(X - conj M),  u_k = exp(+i pi (k/C + 1/2)) = conj(t_k)
-//   Z'[k]/2 = conj(M) + conj(A_k)*(X - conj M)
-//   (kiss_fftr.c:119-155 restated).  The HALVED values are produced (exact power-of-two
-//   scaling) and the caller folds the 2 into its final 1/N scale.  k = 0 uses only the real
-//   parts of X[0] and X[C]:  Z'[0]/2 = ((X0.r + XC.r)/2, (X0.r - XC.r)/2).
-template <class X, class Peer>
-CRLOT_HD void inv_split(cpx (&v)[32], int lane, const cpx* sa, Peer peer, const cpx (&nyq)[X::M1]) {
-  cpx out[32];
+// Per-lane constants of the split, one pair per register group j: (q, rot(q)) with
+//   forward: q = (-i/2) exp(-i pi ob/C)      inverse: q = (+i/2) exp(+i pi a/C)
+template <int M> struct SplitLane {
+  cpx q[M], qr[M];          // qr = (-q.y, q.x) = i*q, so that e*q = e.x*q + e.y*qr
+};
+template <class X> CRLOT_HD SplitLane<X::M2> make_split_fwd(int lane) {
+  SplitLane<X::M2> L;
+#pragma unroll
+  for (int j = 0; j < X::M2; ++j) {
+    const int ob = (lane + 32 * j) % X::B;
+    const double th = 3.14159265358979323846 * (double)ob / (double)X::C;
+    L.q[j] = mk((float)(-0.5 * sin(th)), (float)(-0.5 * cos(th)));
+    L.qr[j] = mk(-L.q[j].y, L.q[j].x);
+  }
+  return L;
+}
+template <class X> CRLOT_HD SplitLane<X::M1> make_split_inv(int lane) {
+  SplitLane<X::M1> L;
 #pragma unroll
   for (int j = 0; j < X::M1; ++j) {
     const int a = (lane + 32 * j) % X::A;
-#pragma unroll
-    for (int b = 0; b < X::B; ++b) {
-      const cpx x = v[j * X::B + b];
-      const cpx far = peer(j * X::B + (X::B - 1 - b));
-      const cpx own = v[j * X::B + (X::B - b) % X::B];
-      const cpx m = (a == 0) ? own : far;                    // X[C-k]
-      const cpx ds = fma2(m, mk(-1.f, 1.f), x);
-      const cpx mc = mul2(m, mk(1.f, -1.f));
-      out[j * X::B + b] = cfmac(ds, sa[a + X::A * b], mc);
-    }
-    if (a == 0) out[j * X::B] = mk(0.5f * (v[j * X::B].x + nyq[j].x), 0.5f * (v[j * X::B].x - nyq[j].x));
+    const double th = 3.14159265358979323846 * (double)a / (double)X::C;
+    L.q[j] = mk((float)(-0.5 * sin(th)), (float)(0.5 * cos(th)));
+    L.qr[j] = mk(-L.q[j].y, L.q[j].x);
   }
+  return L;
+}
+
+// One pair: from z, m and the two factors produce x1 = s/2 + f, x2 = conj(s/2 - f).
+template <int D, int n, bool CONJ> CRLOT_HD void split_pair(cpx z, cpx m, cpx q, cpx qr, cpx& x1, cpx& x2) {
+  const cpx s = fma2(m, mk(1.f, -1.f), z);               // z + conj(m)
+  const cpx d = fma2(m, mk(-1.f, 1.f), z);               // z - conj(m)
+  cpx e = d;
+  if (n != 0) e = cmul(d, wq<D, n, CONJ>());             // compile-time factor
+  const cpx f = fma2(splat(e.y), qr, mul2(splat(e.x), q));   // lane factor
+  x1 = fma2(s, mk(0.5f, 0.5f), f);
+  x2 = fma2(s, mk(0.5f, -0.5f), mul2(f, mk(-1.f, 1.f)));
+}
+
+// Phase A over the registers of group j laid out as v[j*R + r], r < R (R = A forward, B inverse),
+// with `self` = this lane's index digit is 0 (mirror inside the lane).  x2 of pair r is parked in
+// slot R-1-r.  Descending r, so that the self lane still finds its own partner register R-r intact.
+template <int R, int D, bool CONJ, int r, class Peer>
+CRLOT_HD void split_pairs_rec(cpx (&v)[32], int base, bool self, cpx q, cpx qr, Peer& peer) {
+  const cpx far = peer(base + R - 1 - r);
+  const cpx own = v[base + (R - r) % R];
+  const cpx m = self ? own : far;
+  cpx x1, x2;
+  split_pair<D, r, CONJ>(v[base + r], m, q, qr, x1, x2);
+  v[base + r] = x1;
+  v[base + R - 1 - r] = x2;
+  if constexpr (r > 0) split_pairs_rec<R, D, CONJ, r - 1>(v, base, self, q, qr, peer);
+}
+// Phase B: bins R/2..R-1 of the group come from the mirror lane's parked x2 (self lane: its own,
+// one slot lower; its middle bin R/2 is the self-mirrored conj(z) saved before phase A).
+template <int R, class Peer> CRLOT_HD void split_finish_group(cpx (&v)[32], int base, bool self, cpx mid, Peer& peer) {
 #pragma unroll
-  for (int r = 0; r < 32; ++r) v[r] = out[r];
+  for (int r = R - 1; r > R / 2; --r) {
+    const cpx far = peer(base + r);
+    const cpx own = v[base + r - 1];
+    v[base + r] = self ? own : far;
+  }
+  const cpx far = peer(base + R / 2);
+  v[base + R / 2] = self ? mid : far;
+}
+
+// Forward split, pass-2 view.  peer_a / peer_b as described above.
+template <class X, class PeerA>
+CRLOT_HD void fwd_split_pairs(cpx (&v)[32], int lane, const SplitLane<X::M2>& L, PeerA peer_a, cpx (&nyq)[X::M2],
+                              cpx (&mid)[X::M2]) {
+#pragma unroll
+  for (int j = 0; j < X::M2; ++j) {
+    const bool self = (lane + 32 * j) % X::B == 0;
+    const cpx z0 = v[j * X::A];
+    mid[j] = mul2(v[j * X::A + X::A / 2], mk(1.f, -1.f));          // X[C/2] = conj(Z[C/2]) (self lane only)
+    split_pairs_rec<X::A, X::A, false, X::A / 2 - 1>(v, j * X::A, self, L.q[j], L.qr[j], peer_a);
+    if (self) {                                                    // k = 0: exact DC and Nyquist
+      v[j * X::A] = mk(z0.x + z0.y, 0.0f);
+      nyq[j] = mk(z0.x - z0.y, 0.0f);
+    }
+  }
+}
+template <class X, class PeerB>
+CRLOT_HD void fwd_split_finish(cpx (&v)[32], int lane, PeerB peer_b, const cpx (&mid)[X::M2]) {
+#pragma unroll
+  for (int j = 0; j < X::M2; ++j) split_finish_group<X::A>(v, j * X::A, (lane + 32 * j) % X::B == 0, mid[j], peer_b);
+}
+
+// Inverse (before pass 1), pass-1 view, k = a + A*b.  For the pair k, C-k with x = X[k], m = X[C-k]:
+//   s = x + conj m,  d = x - conj m,  f = (+i/2) conj(w_k) d
+//   Z'[k]/2 = s/2 + f         Z'[C-k]/2 = conj(s/2 - f)
+//   (kiss_fftr.c:119-155 restated).  The HALVED values are produced (exact power-of-two
+//   scaling) and the caller folds the 2 into its final 1/N scale.  k = 0 uses only the real
+//   parts of X[0] and X[C]:  Z'[0]/2 = ((X0.r + XC.r)/2, (X0.r - XC.r)/2).
+template <class X, class PeerA>
+CRLOT_HD void inv_split_pairs(cpx (&v)[32], int lane, const SplitLane<X::M1>& L, PeerA peer_a, const cpx (&nyq)[X::M1],
+                              cpx (&mid)[X::M1]) {
+#pragma unroll
+  for (int j = 0; j < X::M1; ++j) {
+    const bool self = (lane + 32 * j) % X::A == 0;
+    const cpx x0 = v[j * X::B];
+    mid[j] = mul2(v[j * X::B + X::B / 2], mk(1.f, -1.f));
+    split_pairs_rec<X::B, X::B, true, X::B / 2 - 1>(v, j * X::B, self, L.q[j], L.qr[j], peer_a);
+    if (self) v[j * X::B] = mk(0.5f * (x0.x + nyq[j].x), 0.5f * (x0.x - nyq[j].x));
+  }
+}
+template <class X, class PeerB>
+CRLOT_HD void inv_split_finish(cpx (&v)[32], int lane, PeerB peer_b, const cpx (&mid)[X::M1]) {
+#pragma unroll
+  for (int j = 0; j < X::M1; ++j) split_finish_group<X::B>(v, j * X::B, (lane + 32 * j) % X::A == 0, mid[j], peer_b);
 }
 
 // ---- N = 4096: two warps per frame ------------------------------------------------------------

@@ -22,8 +22,6 @@ template <int NFFT> static int run() {
   const int C = X::C, G = X::G, N = NFFT;
   FftTables T = make_fft_tables(N);
   const cpx* tw1 = reinterpret_cast<const cpx*>(T.tw1.data());
-  const cpx* st = reinterpret_cast<const cpx*>(T.sa.data());
-  const cpx* su = st;
   std::vector<std::vector<float>> x(G, std::vector<float>(N));
   for (auto& f : x) for (auto& s : f) s = (float)frand();
   // reference spectra in double
@@ -61,9 +59,15 @@ template <int NFFT> static int run() {
   cpx snap[32][32];
   for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
   cpx nyq[32][X::M2];
-  for (int l = 0; l < 32; ++l) {
+  cpx mid[32][X::M2];
+  for (int l = 0; l < 32; ++l) {                       // phase A: mirror lane's registers before the phase
     const int lp = mirror_lane<X::B>(l);
-    fwd_split<X>(v[l], l, st, [&](int r) { return snap[lp][r]; }, nyq[l]);
+    fwd_split_pairs<X>(v[l], l, make_split_fwd<X>(l), [&](int r) { return snap[lp][r]; }, nyq[l], mid[l]);
+  }
+  for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
+  for (int l = 0; l < 32; ++l) {                       // phase B: mirror lane's registers after phase A
+    const int lp = mirror_lane<X::B>(l);
+    fwd_split_finish<X>(v[l], l, [&](int r) { return snap[lp][r]; }, mid[l]);
   }
   double err = 0, nrm = 0;
   std::vector<std::vector<cd>> Xg(G, std::vector<cd>(C + 1));
@@ -86,9 +90,15 @@ template <int NFFT> static int run() {
       if (i == 0) { v[l][r].y = 123.0f; nq[l][r / X::B] = mk((float)Xr[g][C].real(), -77.0f); }  // imag of DC/Nyquist must be ignored
     }
   for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
+  cpx midi[32][X::M1];
   for (int l = 0; l < 32; ++l) {
     const int lp = mirror_lane<X::A>(l);
-    inv_split<X>(v[l], l, su, [&](int r) { return snap[lp][r]; }, nq[l]);
+    inv_split_pairs<X>(v[l], l, make_split_inv<X>(l), [&](int r) { return snap[lp][r]; }, nq[l], midi[l]);
+  }
+  for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
+  for (int l = 0; l < 32; ++l) {
+    const int lp = mirror_lane<X::A>(l);
+    inv_split_finish<X>(v[l], l, [&](int r) { return snap[lp][r]; }, midi[l]);
   }
   for (int l = 0; l < 32; ++l) { pass1<X, true>(v[l]); twiddle1<X, true>(v[l], l, tw1); }
   for (int l = 0; l < 32; ++l) xchg_write<X>(v[l], l, ex.data());
