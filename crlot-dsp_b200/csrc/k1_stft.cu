@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "warpfft.cuh"
+#include "warpfft4096.cuh"
 
 namespace crlot {
 
@@ -203,43 +204,29 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
   }
 }
 
-// ---- N = 4096: two warps per frame (warpfft.cuh "N = 4096") ------------------------------------
-// A warp pair shares one ring (the frame's 4096 samples) and one mbarrier; parity 0 transforms
-// z[n]+z[n+1024] into the even bins, parity 1 transforms (z[n]-z[n+1024])*W_2048^n into the odd
-// bins.  The only coupling between the two warps is a 64-thread named barrier per step ("both
-// have read the ring") and the shared chunk index.
-constexpr int kK1Warps4096 = 10;
+// ---- N = 4096: one warp per frame, 64 complex registers per lane (warpfft4096.cuh) --------------
+// Same pipeline as above with G = 1: private 4096-float ring (the frame itself; the hop that has
+// just been read into registers is the one the next bulk copy overwrites), two-round exchange so
+// that eight warps fit the 227 KB of shared memory, in-lane real split (no shuffles, no table).
+constexpr int kK1Warps4096 = 8;
 
-__device__ __forceinline__ void pair_sync(int pair) {
-  asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
-}
-
-template <bool SCRUB>
+template <int SCRUB>
 __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(const K1Params p) {
-  using X = GeoX<2048>;                      // the 1024-point machinery
-  constexpr int NFFT = 4096, CB = 2048, RCAP = 4096, NPAIR = kK1Warps4096 / 2;
+  constexpr int NFFT = 4096, C = 2048, RCAP = 4096, mask = RCAP - 1;
+  constexpr int kPerWarp = RCAP * 4 + Geo4096::FX_ROUND_CPX * 8 + 16;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
-  cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
-  cpx* s_sa = s_tw1 + 1024;
-  cpx* s_pre = s_sa + CB;
-  float* rings = reinterpret_cast<float*>(s_pre + 1024);
-  cpx* exs = reinterpret_cast<cpx*>(rings + NPAIR * RCAP);
-  unsigned long long* bars = reinterpret_cast<unsigned long long*>(exs + kK1Warps4096 * X::XCPX);
-  unsigned int* pair_q = reinterpret_cast<unsigned int*>(bars + NPAIR);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, pair = warp >> 1, parity = warp & 1;
-  float* ring = rings + pair * RCAP;
-  cpx* ex = exs + warp * X::XCPX;
-  const uint32_t bar = smem_u32(bars + pair);
-  constexpr int mask = RCAP - 1;
+  cpx* s_tw = reinterpret_cast<cpx*>(s_win + NFFT);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_tw + C) + warp * kPerWarp;
+  float* ring = reinterpret_cast<float*>(wb);
+  cpx* ex = reinterpret_cast<cpx*>(ring + RCAP);
+  const uint32_t bar = smem_u32(ex + Geo4096::FX_ROUND_CPX);
 
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < CB; i += blockDim.x) s_sa[i] = p.sa[i];
-  for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
-    s_tw1[i] = p.tw1[i];
-    s_pre[i] = p.pre[i];
-  }
-  if (parity == 0 && lane == 0) {
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw[i] = p.tw1[i];
+  const SplitLane4096 SL = make_split_4096<false>(lane);
+  if (lane == 0) {
     mbar_init(bar, 1);
     fence_mbar_init();
   }
@@ -249,76 +236,93 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
   const long long frames_per_chunk = p.chunk_steps;
   const long long chunks_per_chan = (p.frames + frames_per_chunk - 1) / frames_per_chunk;
   const long long total_chunks = chunks_per_chan * p.channels;
-  const int lp = parity == 0 ? mirror_lane<32>(lane) : 31 - lane;
-  uint32_t phase = 0;
+  const int ob1 = Geo4096::row1(lane);
+  uint32_t parity = 0;
 
   for (;;) {
-    if (parity == 0 && lane == 0) pair_q[pair] = atomicAdd(p.counter, 1u);
-    pair_sync(pair);                         // chunk index published; previous chunk's ring reads done
-    const long long q = *reinterpret_cast<volatile unsigned int*>(pair_q + pair);
-    if (q >= total_chunks) break;
+    unsigned long long q = 0;
+    if (lane == 0) q = atomicAdd(p.counter, 1u);
+    q = __shfl_sync(0xffffffffu, q, 0);
+    if (static_cast<long long>(q) >= total_chunks) break;
     const long long c = q / chunks_per_chan;
     const long long first = (q % chunks_per_chan) * frames_per_chunk;
     const int nsteps = static_cast<int>(min(frames_per_chunk, p.frames - first));
     const float* sig = p.sig + c * p.chan_stride;
-    cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (CB + 1);
+    cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (C + 1);
     long long pos = first * H;
-    if (parity == 0) ring_fill(ring, mask, sig, p.len, pos, NFFT, bar, lane);
+
+    int dirty = 0;
+    __syncwarp();
+    ring_fill(ring, mask, sig, p.len, pos, NFFT, bar, lane);
 
     for (int s = 0; s < nsteps; ++s) {
-      mbar_wait(bar, phase);
-      phase ^= 1u;
+      mbar_wait(bar, parity);
+      parity ^= 1u;
       __syncwarp();
-      cpx v[32];
-#pragma unroll
-      for (int b = 0; b < 32; ++b) {
-        const int n = lane + 32 * b;
-        const cpx x0 = *reinterpret_cast<const cpx*>(ring + ((pos + 2 * n) & mask));
-        const cpx x1 = *reinterpret_cast<const cpx*>(ring + ((pos + 2 * n + 2048) & mask));
-        cpx p0 = mul2(x0, *reinterpret_cast<const cpx*>(s_win + 2 * n));
-        cpx p1 = mul2(x1, *reinterpret_cast<const cpx*>(s_win + 2 * n + 2048));
-        if (SCRUB) {
-          p0 = mk(scrub(p0.x), scrub(p0.y));
-          p1 = mk(scrub(p1.x), scrub(p1.y));
-        }
-        v[b] = parity == 0 ? p0 + p1 : cmul(p0 - p1, s_pre[n]);
-      }
-      pair_sync(pair);                       // both warps have read the ring
-      if (parity == 0 && s + 1 < nsteps) ring_fill(ring, mask, sig, p.len, pos + NFFT, H, bar, lane);
 
-      pass1<X, false>(v);
-      twiddle1<X, false>(v, lane, s_tw1);
-      xchg_write<X>(v, lane, ex);
-      __syncwarp();
-      xchg_read<X>(v, lane, ex);
-      __syncwarp();
-      pass2<X, false>(v);
-      cpx nyq = mk(0.f, 0.f);
-      fwd_split_4096(v, lane, parity, s_sa,
-                     [&](int r) {
-                       return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp));
-                     },
-                     nyq);
+      cpx v[64];
+      unsigned int wmin = 0xffffffffu;
+      cpx nf = mk(0.f, 0.f);
 #pragma unroll
-      for (int oa = 0; oa < 32; ++oa) stg_stream(spec + 2 * (lane + 32 * oa) + parity, v[oa]);
-      if (parity == 0 && lane == 0) stg_stream(spec + CB, nyq);
+      for (int b = 0; b < 64; ++b) {
+        const int ridx = static_cast<int>((pos + 2 * lane + 64 * b) & mask);
+        const cpx x = *reinterpret_cast<const cpx*>(ring + ridx);
+        const cpx w = *reinterpret_cast<const cpx*>(s_win + 2 * lane + 64 * b);
+        cpx pw = mul2(x, w);                   // one rounding per sample, as frame[i]*window[i]
+        if (SCRUB == 1) pw = mk(scrub(pw.x), scrub(pw.y));
+        if (SCRUB == 2 && b >= 48) {           // the newest hop (nfft == 4*hop): samples >= 3072
+          const unsigned int u0 = __float_as_uint(x.x), u1 = __float_as_uint(x.y);
+          wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));
+          nf = fma2(x, mk(0.f, 0.f), nf);
+        }
+        v[b] = pw;
+      }
+      if (SCRUB == 2) {
+        const bool suspect = (wmin < p.tiny2) || (nf.x != 0.0f) || (nf.y != 0.0f);
+        if (__any_sync(0xffffffffu, suspect)) dirty = 5;
+        if (dirty > 0 || s == 0) {             // s == 0: the whole ring is new
+#pragma unroll
+          for (int r = 0; r < 64; ++r) v[r] = mk(scrub(v[r].x), scrub(v[r].y));
+          if (dirty > 0) --dirty;
+        }
+      }
+      __syncwarp();
+      if (s + 1 < nsteps) ring_fill(ring, mask, sig, p.len, pos + NFFT, H, bar, lane);
+
+      fwd4096_pass1(v);
+      fwd4096_twiddle(v, lane, s_tw);
+      fwd4096_xwrite<0>(v, lane, ex);
+      __syncwarp();
+      fwd4096_xread<0>(v, lane, ex);
+      __syncwarp();
+      fwd4096_xwrite<1>(v, lane, ex);
+      __syncwarp();
+      fwd4096_xread<1>(v, lane, ex);
+      __syncwarp();
+      fwd4096_pass2(v);
+      cpx nyq = mk(0.f, 0.f);
+      fwd4096_split(v, lane, SL, nyq);
+#pragma unroll
+      for (int oa = 0; oa < 32; ++oa) stg_stream(spec + lane + 64 * oa, v[oa]);
+#pragma unroll
+      for (int oa = 0; oa < 32; ++oa) stg_stream(spec + ob1 + 64 * oa, v[32 + oa]);
+      if (lane == 0) stg_stream(spec + C, nyq);
       pos += H;
-      spec += CB + 1;
+      spec += C + 1;
     }
   }
 }
 
 static cudaError_t launch_k1_4096(const K1Params& p, cudaStream_t st) {
-  using X = GeoX<2048>;
-  constexpr int NPAIR = kK1Warps4096 / 2;
-  const int smem = 4096 * 4 + 1024 * 8 + 2048 * 8 + 1024 * 8 + NPAIR * 4096 * 4 + kK1Warps4096 * X::XCPX * 8 + NPAIR * 8 + NPAIR * 4 + 16;
-  auto kern = p.scrub ? stft_fwd_kernel_4096<true> : stft_fwd_kernel_4096<false>;
+  const int smem = 4096 * 4 + 2048 * 8 + kK1Warps4096 * (4096 * 4 + Geo4096::FX_ROUND_CPX * 8 + 16);
+  const int mode = !p.scrub ? 0 : (p.scrub == 2 && 4096 == 4 * p.hop) ? 2 : 1;
+  auto kern = mode == 0 ? stft_fwd_kernel_4096<0> : mode == 1 ? stft_fwd_kernel_4096<1> : stft_fwd_kernel_4096<2>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
   if (e != cudaSuccess) return e;
   const long long total_chunks = ((p.frames + p.chunk_steps - 1) / p.chunk_steps) * p.channels;
-  const long long want_blocks = (total_chunks + NPAIR - 1) / NPAIR;
+  const long long want_blocks = (total_chunks + kK1Warps4096 - 1) / kK1Warps4096;
   const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
   kern<<<grid > 0 ? grid : 1, kK1Warps4096 * 32, smem, st>>>(p);
   return cudaGetLastError();

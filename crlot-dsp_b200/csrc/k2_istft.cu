@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "warpfft.cuh"
+#include "warpfft4096.cuh"
 
 namespace crlot {
 
@@ -92,57 +93,48 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
   }
 }
 
-// ---- N = 4096: two independent warps per frame (warpfft.cuh "N = 4096") -------------------------
-// Work item = (row, parity).  Each warp reads X[k], X[k+1024] and the mirrors X[2048-k], X[1024-k]
-// straight from global memory (both orders are contiguous across the lanes; the second touch of a
-// line hits L1/L2), builds its half of the radix-2 pre-stage, runs the 1024-point inverse and
-// writes samples 4n+2*parity, 4n+2*parity+1.  No communication between the two warps.
+// ---- N = 4096: one warp per frame, 64 complex registers per lane (warpfft4096.cuh) --------------
+// A lane loads the spectrum columns a0 = lane and a1 = 64 - lane (32 for lane 0): bin a + 64*b, so
+// every load instruction covers one contiguous 256-byte segment and the mirror bin 2048 - k of
+// each of its values sits in the lane's own registers (no shuffles, no split table).
+constexpr int kK2Warps4096 = 8;
+
 template <bool WIN, bool SCRUB>
-__global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel_4096(const K2Params p) {
-  using X = GeoX<2048>;
-  constexpr int NFFT = 4096, CB = 2048;
+__global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(const K2Params p) {
+  constexpr int NFFT = 4096, C = 2048;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* s_win = reinterpret_cast<float*>(smem_raw);
-  cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
-  cpx* s_sa = s_tw1 + 1024;
-  cpx* s_pre = s_sa + CB;
+  cpx* s_twi = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  cpx* ex = s_pre + 1024 + warp * X::XCPX;
+  cpx* ex = s_twi + C + warp * Geo4096::IX_CPX;
   if (WIN)
     for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < CB; i += blockDim.x) s_sa[i] = p.sa[i];
-  for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
-    s_tw1[i] = p.tw1[i];
-    s_pre[i] = p.pre[i];
-  }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_twi[i] = p.pre[i];
+  const SplitLane4096 SL = make_split_4096<true>(lane);
   __syncthreads();
-  const long long total_items = p.rows * 2;
-  const long long stride = static_cast<long long>(gridDim.x) * kK2Warps;
-  const float scale = 2.0f / static_cast<float>(NFFT);
-  for (long long item = static_cast<long long>(blockIdx.x) * kK2Warps + warp; item < total_items; item += stride) {
-    const long long rowi = item >> 1;
-    const int parity = static_cast<int>(item & 1);
-    const cpx* row = p.spec + rowi * (CB + 1);
-    cpx v[32];
+  const long long stride = static_cast<long long>(gridDim.x) * kK2Warps4096;
+  const float scale = 2.0f / static_cast<float>(NFFT);    // the split hands over halved values
+  const int a1 = Geo4096::row1(lane);
+  for (long long rowi = static_cast<long long>(blockIdx.x) * kK2Warps4096 + warp; rowi < p.rows; rowi += stride) {
+    const cpx* row = p.spec + rowi * (C + 1);
+    cpx v[64];
 #pragma unroll
-    for (int b = 0; b < 32; ++b) {
-      const int k = lane + 32 * b;
-      const cpx xlo = row[k];
-      const cpx mlo = row[2048 - k];
-      const cpx xhi = row[k + 1024];
-      const cpx mhi = row[1024 - k];
-      v[b] = inv_pre_4096(k, parity, xlo, mlo, xhi, mhi, s_sa[k], s_sa[k + 1024], s_pre[k]);
-    }
-    pass1<X, true>(v);
-    twiddle1<X, true>(v, lane, s_tw1);
-    __syncwarp();
-    xchg_write<X>(v, lane, ex);
-    __syncwarp();
-    xchg_read<X>(v, lane, ex);
-    pass2<X, true>(v);
-    float* dst = p.frames + rowi * NFFT + 2 * parity;
+    for (int b = 0; b < 32; ++b) v[b] = ldg_stream(row + lane + 64 * b);
 #pragma unroll
-    for (int oa = 0; oa < 32; ++oa) {
+    for (int b = 0; b < 32; ++b) v[32 + b] = ldg_stream(row + a1 + 64 * b);
+    cpx nyq = mk(0.f, 0.f);
+    if (lane == 0) nyq = ldg_stream(row + C);
+    inv4096_split(v, lane, SL, nyq);
+    inv4096_pass1(v);
+    inv4096_twiddle(v, lane, s_twi);
+    __syncwarp();                 // previous row's exchange reads are complete
+    inv4096_xwrite(v, lane, ex);
+    __syncwarp();
+    inv4096_xread(v, lane, ex);
+    inv4096_pass2(v);
+    float* dst = p.frames + rowi * NFFT;
+#pragma unroll
+    for (int oa = 0; oa < 64; ++oa) {
       const int n = lane + 32 * oa;
       float y0 = v[oa].x * scale, y1 = v[oa].y * scale;
       if (SCRUB) {
@@ -150,27 +142,26 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel_4096(const 
         y1 = scrub(y1);
       }
       if (WIN) {
-        const float2 w = *reinterpret_cast<const float2*>(s_win + 4 * n + 2 * parity);
+        const float2 w = *reinterpret_cast<const float2*>(s_win + 2 * n);
         y0 = __fmul_rn(y0, w.x);
         y1 = __fmul_rn(y1, w.y);
       }
-      stg_stream(reinterpret_cast<cpx*>(dst + 4 * n), mk(y0, y1));
+      stg_stream(reinterpret_cast<cpx*>(dst + 2 * n), mk(y0, y1));
     }
   }
 }
 
 static cudaError_t launch_k2_4096(const K2Params& p, cudaStream_t st) {
-  using X = GeoX<2048>;
   const bool win = p.window != nullptr;
-  const int smem = (win ? 4096 * 4 : 0) + 1024 * 8 + 2048 * 8 + 1024 * 8 + kK2Warps * X::XCPX * 8;
+  const int smem = (win ? 4096 * 4 : 0) + 2048 * 8 + kK2Warps4096 * Geo4096::IX_CPX * 8;
   void (*kern)(const K2Params) = nullptr;
   if (win) kern = p.scrub ? istft_inv_kernel_4096<true, true> : istft_inv_kernel_4096<true, false>;
   else     kern = p.scrub ? istft_inv_kernel_4096<false, true> : istft_inv_kernel_4096<false, false>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  const long long want_blocks = (p.rows * 2 + kK2Warps - 1) / kK2Warps;
+  const long long want_blocks = (p.rows + kK2Warps4096 - 1) / kK2Warps4096;
   const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
-  kern<<<grid > 0 ? grid : 1, kK2Warps * 32, smem, st>>>(p);
+  kern<<<grid > 0 ? grid : 1, kK2Warps4096 * 32, smem, st>>>(p);
   return cudaGetLastError();
 }
 

@@ -186,6 +186,58 @@ template <int R, bool INV> struct Dft {
   }
 };
 
+// ---- 64-point transform (N = 4096 kernels: one 64-point pass per lane) -------------------------
+// cos(2 pi n/64), n = 0..16
+CRLOT_HD constexpr float c64(int n) {
+  return n == 0 ? 1.0f : n == 1 ? 0.99518472667219688624f : n == 2 ? 0.98078528040323044913f
+       : n == 3 ? 0.95694033573220886494f : n == 4 ? 0.92387953251128675613f : n == 5 ? 0.88192126434835502971f
+       : n == 6 ? 0.83146961230254523708f : n == 7 ? 0.77301045336273696081f : n == 8 ? 0.70710678118654752440f
+       : n == 9 ? 0.63439328416364549822f : n == 10 ? 0.55557023301960222474f : n == 11 ? 0.47139673682599764856f
+       : n == 12 ? 0.38268343236508977173f : n == 13 ? 0.29028467725446236764f : n == 14 ? 0.19509032201612826785f
+       : n == 15 ? 0.09801714032956060199f : 0.0f;
+}
+// cos / sin of 2 pi m/64 for any m in [0, 64)
+CRLOT_HD constexpr float cos64(int m) {
+  return m <= 16 ? c64(m) : m <= 32 ? -c64(32 - m) : m <= 48 ? -c64(m - 32) : c64(64 - m);
+}
+CRLOT_HD constexpr float sin64(int m) {
+  return m <= 16 ? c64(16 - m) : m <= 32 ? c64(m - 16) : m <= 48 ? -c64(48 - m) : -c64(m - 48);
+}
+// a * exp(-/+ 2 pi i K/64), trivial cases folded
+template <int K, bool INV> CRLOT_HD cpx mulw64(cpx a) {
+  constexpr int k = ((K % 64) + 64) % 64;
+  if (k == 0) return a;
+  if (k == 16) return rot90<INV>(a);
+  if (k == 32) return mk(-a.x, -a.y);
+  if (k == 48) return rot90<!INV>(a);
+  return cmul(a, mk(cos64(k), INV ? sin64(k) : -sin64(k)));
+}
+// R = 64: four 16-point transforms of x[4j+q], twiddle W_64^(qK), 16 radix-4 butterflies.
+template <bool INV> struct Dft<64, INV> {
+  template <int K> CRLOT_HD static void col(cpx (&v)[64], const cpx (&y0)[16], const cpx (&y1)[16],
+                                            const cpx (&y2)[16], const cpx (&y3)[16]) {
+    cpx a = y0[K];
+    cpx b = mulw64<K, INV>(y1[K]);
+    cpx c = mulw64<2 * K, INV>(y2[K]);
+    cpx d = mulw64<3 * K, INV>(y3[K]);
+    bfly4<INV>(a, b, c, d);
+    v[K] = a; v[K + 16] = b; v[K + 32] = c; v[K + 48] = d;
+    if constexpr (K + 1 < 16) col<K + 1>(v, y0, y1, y2, y3);
+  }
+  CRLOT_HD static void run(cpx (&v)[64]) {
+    cpx y0[16], y1[16], y2[16], y3[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      y0[j] = v[4 * j]; y1[j] = v[4 * j + 1]; y2[j] = v[4 * j + 2]; y3[j] = v[4 * j + 3];
+    }
+    Dft<16, INV>::run(y0);
+    Dft<16, INV>::run(y1);
+    Dft<16, INV>::run(y2);
+    Dft<16, INV>::run(y3);
+    col<0>(v, y0, y1, y2, y3);
+  }
+};
+
 // DFT over a strided sub-array living inside a larger register file: v[OFF + STRIDE*i], i < R.
 template <int R, bool INV, int OFF, int STRIDE, int TOTAL> CRLOT_HD void dft_sub(cpx (&v)[TOTAL]) {
   cpx t[R];

@@ -10,18 +10,20 @@ struct FftTables {
   int nfft = 0, C = 0, A = 0, B = 0;
   std::vector<float> tw1;   // [B][A] cpx : exp(-2 pi i a*ob / C)      inter-pass twiddle (forward)
   std::vector<float> sa;    // [C]    cpx : 0.5*(1 + exp(-i pi (k/C + 1/2)))  real split (inverse uses conj)
-  std::vector<float> pre;   // [1024] cpx : exp(-2 pi i n / 2048)      N=4096 radix-2 pre-stage
+  std::vector<float> pre;   // N=4096 only: [32][64] cpx : exp(-2 pi i a*ob / 2048), the inverse kernel's
+                            // transposed inter-pass table twi[ob*64 + a] (warpfft4096.cuh)
 };
 
-// C = complex length of the real split (nfft/2); Cw = complex length one warp transforms
-// (== C except nfft=4096 where the warp transforms 1024 points after the radix-2 pre-stage).
+// C = complex length of the real split (nfft/2) = complex length one warp transforms.
+// nfft = 4096: forward uses A=32, B=64 (tw1), inverse A=64, B=32 (pre).
 inline FftTables make_fft_tables(int nfft) {
   const double pi = 3.141592653589793238462643383279502884;
   FftTables t;
   t.nfft = nfft;
   t.C = nfft / 2;
-  const int Cw = t.C > 1024 ? 1024 : t.C;
+  const int Cw = t.C;
   switch (Cw) {
+    case 2048: t.A = 32; t.B = 64; break;
     case 1024: t.A = 32; t.B = 32; break;
     case 512:  t.A = 32; t.B = 16; break;
     case 256:  t.A = 16; t.B = 16; break;
@@ -41,12 +43,13 @@ inline FftTables make_fft_tables(int nfft) {
     t.sa[2 * k + 1] = (float)(0.5 * std::sin(ph));
   }
   if (nfft == 4096) {
-    t.pre.resize(2 * 1024);
-    for (int n = 0; n < 1024; ++n) {
-      const double ph = -2.0 * pi * (double)n / 2048.0;
-      t.pre[2 * n] = (float)std::cos(ph);
-      t.pre[2 * n + 1] = (float)std::sin(ph);
-    }
+    t.pre.resize(2 * 2048);
+    for (int ob = 0; ob < 32; ++ob)
+      for (int a = 0; a < 64; ++a) {
+        const double ph = -2.0 * pi * (double)a * (double)ob / 2048.0;
+        t.pre[2 * (ob * 64 + a)] = (float)std::cos(ph);
+        t.pre[2 * (ob * 64 + a) + 1] = (float)std::sin(ph);
+      }
   }
   return t;
 }

@@ -3,7 +3,7 @@
 // One warp owns 1024 complex points per step, 32 per lane ("register file" v[32]):
 //   N=2048 -> 1 frame  (C=1024 = 32 x 32)      N=1024 -> 2 frames (C=512 = 32 x 16)
 //   N= 512 -> 4 frames (C= 256 = 16 x 16)      N= 256 -> 8 frames (C=128 = 16 x  8)
-//   N=4096 -> half a frame per warp (radix-2 decimation-in-frequency pre-stage, then C=1024)
+//   N=4096 -> one frame per warp with 64 registers per lane: warpfft4096.cuh
 // A C-point complex transform is done "four-step": with input index i = a + A*b and output
 // index o = ob + B*oa,
 //   pass 1: lane item (g,a) transforms over b (B points, in registers), times W_C^(a*ob)
@@ -118,15 +118,6 @@ template <class X> CRLOT_HD void out_coord(int lane, int r, int& g, int& o) {
 //   phase B (split_finish): needs peer(r) = register r of the mirror lane AFTER phase A
 // (on the device both are warp shuffles of the live registers; the CPU emulator snapshots).
 
-// cos(2 pi n/64), n = 0..16
-CRLOT_HD constexpr float c64(int n) {
-  return n == 0 ? 1.0f : n == 1 ? 0.99518472667219688624f : n == 2 ? 0.98078528040323044913f
-       : n == 3 ? 0.95694033573220886494f : n == 4 ? 0.92387953251128675613f : n == 5 ? 0.88192126434835502971f
-       : n == 6 ? 0.83146961230254523708f : n == 7 ? 0.77301045336273696081f : n == 8 ? 0.70710678118654752440f
-       : n == 9 ? 0.63439328416364549822f : n == 10 ? 0.55557023301960222474f : n == 11 ? 0.47139673682599764856f
-       : n == 12 ? 0.38268343236508977173f : n == 13 ? 0.29028467725446236764f : n == 14 ? 0.19509032201612826785f
-       : n == 15 ? 0.09801714032956060199f : 0.0f;
-}
 // exp(-/+ i pi n/D) for 0 <= n <= D/2 (first quadrant), D in {8,16,32}: the compile-time factor
 template <int D, int n, bool CONJ> CRLOT_HD cpx wq() {
   static_assert(D == 8 || D == 16 || D == 32, "split constants: 2D in {16,32,64}");
@@ -245,57 +236,6 @@ template <class X, class PeerB>
 CRLOT_HD void inv_split_finish(cpx (&v)[32], int lane, PeerB peer_b, const cpx (&mid)[X::M1]) {
 #pragma unroll
   for (int j = 0; j < X::M1; ++j) split_finish_group<X::B>(v, j * X::B, (lane + 32 * j) % X::A == 0, mid[j], peer_b);
-}
-
-// ---- N = 4096: two warps per frame ------------------------------------------------------------
-// The 2048-point complex transform is split by one radix-2 decimation-in-frequency stage done at
-// load time:  a[n] = z[n] + z[n+1024],  b[n] = (z[n] - z[n+1024]) * W_2048^n  (n < 1024);
-// warp parity 0 transforms a -> bins 2k', parity 1 transforms b -> bins 2k'+1, each with the
-// 1024-point machinery above (Geo<2048>).  Mirror pairs keep their parity, so the real split
-// stays inside one warp: even bins pair as in fwd_split, odd bins pair (ob,oa) <-> (31-ob,31-oa)
-// with no special lane.  sa[] has 2048 entries indexed by the true bin.
-template <class Peer>
-CRLOT_HD void fwd_split_4096(cpx (&v)[32], int lane, int parity, const cpx* sa, Peer peer, cpx& nyq) {
-  cpx out[32];
-  const int ob = lane;
-  if (parity == 0) {
-#pragma unroll
-    for (int oa = 0; oa < 32; ++oa) {
-      const cpx z = v[oa];
-      const cpx far = peer(31 - oa);
-      const cpx own = v[(32 - oa) % 32];
-      const cpx m = (ob == 0) ? own : far;
-      const cpx ds = fma2(m, mk(-1.f, 1.f), z);
-      const cpx mc = mul2(m, mk(1.f, -1.f));
-      out[oa] = cfma(ds, sa[2 * (ob + 32 * oa)], mc);
-    }
-    if (ob == 0) {
-      out[0] = mk(v[0].x + v[0].y, 0.0f);
-      nyq = mk(v[0].x - v[0].y, 0.0f);
-    }
-  } else {
-#pragma unroll
-    for (int oa = 0; oa < 32; ++oa) {
-      const cpx z = v[oa];
-      const cpx m = peer(31 - oa);
-      const cpx ds = fma2(m, mk(-1.f, 1.f), z);
-      const cpx mc = mul2(m, mk(1.f, -1.f));
-      out[oa] = cfma(ds, sa[2 * (ob + 32 * oa) + 1], mc);
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < 32; ++r) v[r] = out[r];
-}
-
-// Inverse pre-pass for N = 4096, one register: from X[k], X[k+1024] and their mirrors
-// X[2048-k], X[1024-k] (all read straight from global memory, k = a + 32 b < 1024) build the
-// halved Z'[k], Z'[k+1024] and combine them for this warp's parity:
-//   parity 0: Z'[k] + Z'[k+1024]            parity 1: (Z'[k] - Z'[k+1024]) * conj(W_2048^k)
-CRLOT_HD cpx inv_pre_4096(int k, int parity, cpx xlo, cpx mlo, cpx xhi, cpx mhi, cpx alo, cpx ahi, cpx pre) {
-  cpx zlo = cfmac(fma2(mlo, mk(-1.f, 1.f), xlo), alo, mul2(mlo, mk(1.f, -1.f)));
-  if (k == 0) zlo = mk(0.5f * (xlo.x + mlo.x), 0.5f * (xlo.x - mlo.x));   // mlo = X[2048]: real parts only
-  const cpx zhi = cfmac(fma2(mhi, mk(-1.f, 1.f), xhi), ahi, mul2(mhi, mk(1.f, -1.f)));
-  return parity == 0 ? zlo + zhi : cmulc(zlo - zhi, pre);
 }
 
 // partner lane for the mirror: pass-2 view uses B, pass-1 view uses A (lane + 32*j keeps j).

@@ -11,6 +11,7 @@
 
 #include "../../crlot-dsp_b200/csrc/tables.h"
 #include "../../crlot-dsp_b200/csrc/warpfft.cuh"
+#include "../../crlot-dsp_b200/csrc/warpfft4096.cuh"
 
 using namespace crlot;
 typedef std::complex<double> cd;
@@ -119,14 +120,12 @@ template <int NFFT> static int run() {
   return ok ? 0 : 1;
 }
 
-// N = 4096: two emulated warps per frame (parity 0 / 1), see warpfft.cuh.
+// N = 4096: one emulated warp per frame, 64 registers per lane (warpfft4096.cuh).
 static int run4096() {
-  typedef GeoX<2048> X;
   const int N = 4096, C = 2048;
   FftTables T = make_fft_tables(N);
-  const cpx* tw1 = reinterpret_cast<const cpx*>(T.tw1.data());
-  const cpx* sa = reinterpret_cast<const cpx*>(T.sa.data());
-  const cpx* pre = reinterpret_cast<const cpx*>(T.pre.data());
+  const cpx* tw = reinterpret_cast<const cpx*>(T.tw1.data());
+  const cpx* twi = reinterpret_cast<const cpx*>(T.pre.data());
   std::vector<float> x(N);
   for (auto& s : x) s = (float)frand();
   std::vector<cd> Xr(C + 1);
@@ -135,62 +134,74 @@ static int run4096() {
     for (int n = 0; n < N; ++n) s += (double)x[n] * std::polar(1.0, -2.0 * M_PI * (double)n * k / N);
     Xr[k] = s;
   }
-  std::vector<cd> Xg(C + 1);
-  std::vector<cpx> ex(X::XCPX);
-  for (int parity = 0; parity < 2; ++parity) {
-    cpx v[32][32];
-    for (int l = 0; l < 32; ++l)
-      for (int r = 0; r < 32; ++r) {
-        const int n = l + 32 * r;
-        const cpx p0 = mk(x[2 * n], x[2 * n + 1]), p1 = mk(x[2 * (n + 1024)], x[2 * (n + 1024) + 1]);
-        v[l][r] = parity == 0 ? p0 + p1 : cmul(p0 - p1, pre[n]);
-      }
-    for (int l = 0; l < 32; ++l) { pass1<X, false>(v[l]); twiddle1<X, false>(v[l], l, tw1); }
-    for (int l = 0; l < 32; ++l) xchg_write<X>(v[l], l, ex.data());
-    for (int l = 0; l < 32; ++l) xchg_read<X>(v[l], l, ex.data());
-    for (int l = 0; l < 32; ++l) pass2<X, false>(v[l]);
-    cpx snap[32][32];
-    for (int l = 0; l < 32; ++l) for (int r = 0; r < 32; ++r) snap[l][r] = v[l][r];
-    for (int l = 0; l < 32; ++l) {
-      const int lp = parity == 0 ? mirror_lane<32>(l) : 31 - l;
-      cpx nyq = mk(0, 0);
-      fwd_split_4096(v[l], l, parity, sa, [&](int r) { return snap[lp][r]; }, nyq);
-      for (int r = 0; r < 32; ++r) Xg[2 * (l + 32 * r) + parity] = cd(v[l][r].x, v[l][r].y);
-      if (parity == 0 && l == 0) Xg[C] = cd(nyq.x, nyq.y);
-    }
+  // ---- forward ----
+  static cpx v[32][64];
+  std::vector<cpx> ex(Geo4096::IX_CPX);
+  for (int l = 0; l < 32; ++l)
+    for (int b = 0; b < 64; ++b) { const int i = l + 32 * b; v[l][b] = mk(x[2 * i], x[2 * i + 1]); }
+  for (int l = 0; l < 32; ++l) { fwd4096_pass1(v[l]); fwd4096_twiddle(v[l], l, tw); }
+  int conflicts = 0;
+  for (int h = 0; h < 2; ++h) for (int a = 0; a < 32; ++a) for (int hw = 0; hw < 2; ++hw) {
+    std::set<int> banks;
+    for (int l = 16 * hw; l < 16 * hw + 16; ++l) { const int row = h == 0 ? l : (l ? 32 - l : 0); banks.insert((row * Geo4096::FXS + a) % 16); }
+    if (banks.size() != 16) ++conflicts;
   }
+  for (int l = 0; l < 32; ++l) fwd4096_xwrite<0>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) fwd4096_xread<0>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) fwd4096_xwrite<1>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) fwd4096_xread<1>(v[l], l, ex.data());
+  std::vector<cd> Xg(C + 1);
+  std::vector<int> seen(C + 1, 0);
+  for (int l = 0; l < 32; ++l) {
+    fwd4096_pass2(v[l]);
+    cpx nyq = mk(0, 0);
+    fwd4096_split(v[l], l, make_split_4096<false>(l), nyq);
+    for (int r = 0; r < 64; ++r) { const int k = fwd4096_bin(l, r); Xg[k] = cd(v[l][r].x, v[l][r].y); ++seen[k]; }
+    if (l == 0) { Xg[C] = cd(nyq.x, nyq.y); ++seen[C]; }
+  }
+  int cover = 1;
+  for (int k = 0; k <= C; ++k) if (seen[k] != 1) cover = 0;
   double err = 0, nrm = 0;
   for (int k = 0; k <= C; ++k) { err += std::norm(Xg[k] - Xr[k]); nrm += std::norm(Xr[k]); }
   const double fwd_rel = std::sqrt(err / nrm);
   const int exact0 = Xg[0].imag() == 0.0 && Xg[C].imag() == 0.0;
-  // inverse
+  // ---- inverse ----
   std::vector<cpx> Xf(C + 1);
   for (int k = 0; k <= C; ++k) Xf[k] = mk((float)Xr[k].real(), (float)Xr[k].imag());
   Xf[0].y = 55.0f; Xf[C].y = -9.0f;    // must be ignored
+  for (int l = 0; l < 32; ++l) {
+    for (int r = 0; r < 64; ++r) v[l][r] = Xf[inv4096_bin(l, r)];
+    inv4096_split(v[l], l, make_split_4096<true>(l), Xf[C]);
+    inv4096_pass1(v[l]);
+    inv4096_twiddle(v[l], l, twi);
+  }
+  for (int ob = 0; ob < 32; ++ob) for (int j = 0; j < 2; ++j) for (int hw = 0; hw < 2; ++hw) {
+    std::set<int> banks;
+    for (int l = 16 * hw; l < 16 * hw + 16; ++l) banks.insert((ob * Geo4096::IXS + (j ? Geo4096::row1(l) : l)) % 16);
+    if (banks.size() != 16) ++conflicts;
+  }
+  for (int a = 0; a < 64; ++a) for (int hw = 0; hw < 2; ++hw) {
+    std::set<int> banks;
+    for (int l = 16 * hw; l < 16 * hw + 16; ++l) banks.insert((l * Geo4096::IXS + a) % 16);
+    if (banks.size() != 16) ++conflicts;
+  }
+  for (int l = 0; l < 32; ++l) inv4096_xwrite(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) inv4096_xread(v[l], l, ex.data());
   std::vector<double> y(N);
-  for (int parity = 0; parity < 2; ++parity) {
-    cpx v[32][32];
-    for (int l = 0; l < 32; ++l)
-      for (int r = 0; r < 32; ++r) {
-        const int k = l + 32 * r;
-        v[l][r] = inv_pre_4096(k, parity, Xf[k], Xf[2048 - k], Xf[k + 1024], Xf[1024 - k], sa[k], sa[k + 1024], pre[k]);
-      }
-    for (int l = 0; l < 32; ++l) { pass1<X, true>(v[l]); twiddle1<X, true>(v[l], l, tw1); }
-    for (int l = 0; l < 32; ++l) xchg_write<X>(v[l], l, ex.data());
-    for (int l = 0; l < 32; ++l) xchg_read<X>(v[l], l, ex.data());
-    for (int l = 0; l < 32; ++l) pass2<X, true>(v[l]);
-    for (int l = 0; l < 32; ++l)
-      for (int r = 0; r < 32; ++r) {
-        const int n = l + 32 * r;            // z[2n + parity]
-        y[2 * (2 * n + parity)] = 2.0 * v[l][r].x / N;
-        y[2 * (2 * n + parity) + 1] = 2.0 * v[l][r].y / N;
-      }
+  for (int l = 0; l < 32; ++l) {
+    inv4096_pass2(v[l]);
+    for (int oa = 0; oa < 64; ++oa) {
+      const int n = l + 32 * oa;
+      y[2 * n] = 2.0 * v[l][oa].x / N;
+      y[2 * n + 1] = 2.0 * v[l][oa].y / N;
+    }
   }
   err = 0; nrm = 0;
   for (int i = 0; i < N; ++i) { err += (y[i] - x[i]) * (y[i] - x[i]); nrm += (double)x[i] * x[i]; }
   const double inv_rel = std::sqrt(err / nrm);
-  const int ok = fwd_rel < 5e-7 && inv_rel < 5e-7 && exact0;
-  printf("N=4096 (2 warps/frame)  fwd rel-L2 %.3e  inv rel-L2 %.3e  exact-zero imag %d  %s\n", fwd_rel, inv_rel, exact0, ok ? "OK" : "FAIL");
+  const int ok = fwd_rel < 5e-7 && inv_rel < 5e-7 && exact0 && cover && conflicts == 0;
+  printf("N=4096 (1 warp/frame, 64 regs/lane)  fwd rel-L2 %.3e  inv rel-L2 %.3e  xchg conflicts %d  bins covered once %d  exact-zero imag %d  %s\n",
+         fwd_rel, inv_rel, conflicts, cover, exact0, ok ? "OK" : "FAIL");
   return ok ? 0 : 1;
 }
 
