@@ -226,6 +226,7 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
   for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw[i] = p.tw1[i];
   const SplitLane4096 SL = make_split_4096<false>(lane);
+  const Coop4096 CO = make_coop_4096<false>(lane);
   if (lane == 0) {
     mbar_init(bar, 1);
     fence_mbar_init();
@@ -300,13 +301,27 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
       fwd4096_xread<1>(v, lane, ex);
       __syncwarp();
       fwd4096_pass2(v);
-      cpx nyq = mk(0.f, 0.f);
-      fwd4096_split(v, lane, SL, nyq);
+      // lane 0's self-mirrored rows are shared out over the warp (warpfft4096.cuh "Coop4096")
+      if (lane == 0) {
 #pragma unroll
-      for (int oa = 0; oa < 32; ++oa) stg_stream(spec + lane + 64 * oa, v[oa]);
+        for (int r = 0; r < 64; ++r) ex[r] = v[r];
+      }
+      __syncwarp();
+      if (lane != 0) {
+        cpx x1, x2;
+        split_pair32<0, false>(ex[CO.zi], ex[CO.mi], CO.q, CO.qr, x1, x2);
+        stg_stream(spec + CO.k, x1);
+        stg_stream(spec + C - CO.k, x2);
+        split4096_general<false>(v, SL.q, SL.qr);
 #pragma unroll
-      for (int oa = 0; oa < 32; ++oa) stg_stream(spec + ob1 + 64 * oa, v[32 + oa]);
-      if (lane == 0) stg_stream(spec + C, nyq);
+        for (int oa = 0; oa < 32; ++oa) stg_stream(spec + lane + 64 * oa, v[oa]);
+#pragma unroll
+        for (int oa = 0; oa < 32; ++oa) stg_stream(spec + ob1 + 64 * oa, v[32 + oa]);
+      } else {
+        stg_stream(spec, mk(v[0].x + v[0].y, 0.0f));          // exact DC and Nyquist (kiss_fftr.c:93-99)
+        stg_stream(spec + C, mk(v[0].x - v[0].y, 0.0f));
+        stg_stream(spec + C / 2, mul2(v[16], mk(1.f, -1.f))); // X[1024] = conj(Z[1024])
+      }
       pos += H;
       spec += C + 1;
     }

@@ -94,10 +94,15 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
 }
 
 // ---- N = 4096: one warp per frame, 64 complex registers per lane (warpfft4096.cuh) --------------
-// A lane loads the spectrum columns a0 = lane and a1 = 64 - lane (32 for lane 0): bin a + 64*b, so
-// every load instruction covers one contiguous 256-byte segment and the mirror bin 2048 - k of
-// each of its values sits in the lane's own registers (no shuffles, no split table).
+// A lane owns the spectrum columns a0 = lane and a1 = 64 - lane (32 for lane 0): bin a + 64*b, so
+// the mirror bin 2048 - k of each of its values sits in the lane's own registers (no shuffles, no
+// split table).  Spectrum rows are prefetched one row ahead into a per-warp staging buffer by a
+// 1-D bulk async copy (UBLKCP) on the warp's own mbarrier: rows are only 8-byte aligned
+// ((2049 bins) x 8 B), so the copy moves the 2048 bins that start at the row's first 16-byte
+// boundary and lane 0 fetches the one remaining bin (bin 0 or bin 2048) with a plain load.
 constexpr int kK2Warps4096 = 8;
+constexpr int kK2Stage4096 = 2048 * 8;                       // bytes staged per row
+constexpr int kK2PerWarp4096 = kK2Stage4096 + Geo4096::FX_ROUND_CPX * 8 + 16;
 
 template <bool WIN, bool SCRUB>
 __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(const K2Params p) {
@@ -106,31 +111,80 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_twi = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  cpx* ex = s_twi + C + warp * Geo4096::IX_CPX;
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_twi + C) + warp * kK2PerWarp4096;
+  cpx* stage = reinterpret_cast<cpx*>(wb);
+  cpx* ex = stage + C;
+  const uint32_t bar = smem_u32(ex + Geo4096::FX_ROUND_CPX);
   if (WIN)
     for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
   for (int i = threadIdx.x; i < C; i += blockDim.x) s_twi[i] = p.pre[i];
   const SplitLane4096 SL = make_split_4096<true>(lane);
+  const Coop4096 CO = make_coop_4096<true>(lane);
+  cpx dc = mk(0.f, 0.f);
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+  }
   __syncthreads();
   const long long stride = static_cast<long long>(gridDim.x) * kK2Warps4096;
   const float scale = 2.0f / static_cast<float>(NFFT);    // the split hands over halved values
   const int a1 = Geo4096::row1(lane);
-  for (long long rowi = static_cast<long long>(blockIdx.x) * kK2Warps4096 + warp; rowi < p.rows; rowi += stride) {
-    const cpx* row = p.spec + rowi * (C + 1);
+  uint32_t phase = 0;
+  long long rowi = static_cast<long long>(blockIdx.x) * kK2Warps4096 + warp;
+  // off = 1 when the row starts 8 bytes past a 16-byte boundary: stage[i] = bin i + off
+  auto prefetch = [&](long long r, cpx& extra) {
+    const cpx* row = p.spec + r * (C + 1);
+    const int off = static_cast<int>((reinterpret_cast<uintptr_t>(row) >> 3) & 1);
+    if (lane == 0) {
+      fence_proxy_async_smem();
+      mbar_arrive_expect_tx(bar, kK2Stage4096);
+      bulk_g2s(smem_u32(stage), row + off, kK2Stage4096, bar);
+      extra = ldg_stream(off ? row : row + C);
+    }
+    return off;
+  };
+  cpx extra = mk(0.f, 0.f);
+  int off = 0;
+  if (rowi < p.rows) off = prefetch(rowi, extra);
+  for (; rowi < p.rows; rowi += stride) {
+    mbar_wait(bar, phase);
+    phase ^= 1u;
+    // lane 0's self-mirrored columns are split in place in the staging buffer, one pair per lane
+    // (warpfft4096.cuh "Coop4096"); the general in-register split below then skips lane 0
+    cpx* st = stage - off;
+    if (lane != 0) {
+      cpx x1, x2;
+      split_pair32<0, true>(st[CO.k], st[C - CO.k], CO.q, CO.qr, x1, x2);
+      st[CO.k] = x1;
+      st[C - CO.k] = x2;
+    } else {
+      const cpx x0 = off ? extra : stage[0];
+      const cpx xn = off ? stage[C - 1] : extra;
+      dc = mk(0.5f * (x0.x + xn.x), 0.5f * (x0.x - xn.x));     // only the real parts (kiss_fftr.c:131-132)
+      st[C / 2] = mul2(st[C / 2], mk(1.f, -1.f));
+    }
+    __syncwarp();
     cpx v[64];
 #pragma unroll
-    for (int b = 0; b < 32; ++b) v[b] = ldg_stream(row + lane + 64 * b);
+    for (int b = 0; b < 32; ++b) v[b] = st[lane + 64 * b];
 #pragma unroll
-    for (int b = 0; b < 32; ++b) v[32 + b] = ldg_stream(row + a1 + 64 * b);
-    cpx nyq = mk(0.f, 0.f);
-    if (lane == 0) nyq = ldg_stream(row + C);
-    inv4096_split(v, lane, SL, nyq);
+    for (int b = 0; b < 32; ++b) v[32 + b] = st[a1 + 64 * b];
+    if (lane == 0) v[0] = dc;
+    __syncwarp();                 // every lane has read the staging buffer
+    const long long nxt = rowi + stride;
+    if (nxt < p.rows) off = prefetch(nxt, extra);
+
+    if (lane != 0) split4096_general<true>(v, SL.q, SL.qr);
     inv4096_pass1(v);
     inv4096_twiddle(v, lane, s_twi);
-    __syncwarp();                 // previous row's exchange reads are complete
-    inv4096_xwrite(v, lane, ex);
+    inv4096_xwrite<0>(v, lane, ex);
     __syncwarp();
-    inv4096_xread(v, lane, ex);
+    inv4096_xread<0>(v, lane, ex);
+    __syncwarp();
+    inv4096_xwrite<1>(v, lane, ex);
+    __syncwarp();
+    inv4096_xread<1>(v, lane, ex);
+    __syncwarp();
     inv4096_pass2(v);
     float* dst = p.frames + rowi * NFFT;
 #pragma unroll
@@ -153,7 +207,7 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
 
 static cudaError_t launch_k2_4096(const K2Params& p, cudaStream_t st) {
   const bool win = p.window != nullptr;
-  const int smem = (win ? 4096 * 4 : 0) + 2048 * 8 + kK2Warps4096 * Geo4096::IX_CPX * 8;
+  const int smem = (win ? 4096 * 4 : 0) + 2048 * 8 + kK2Warps4096 * kK2PerWarp4096;
   void (*kern)(const K2Params) = nullptr;
   if (win) kern = p.scrub ? istft_inv_kernel_4096<true, true> : istft_inv_kernel_4096<true, false>;
   else     kern = p.scrub ? istft_inv_kernel_4096<false, true> : istft_inv_kernel_4096<false, false>;

@@ -32,7 +32,7 @@ struct Geo4096 {
   static constexpr int C = 2048;
   // exchange buffers in cpx units; rows padded to an odd length (conflict-free 8-byte accesses)
   static constexpr int FXS = 33, FX_ROUND_CPX = 32 * FXS;   // forward: two rounds of 32 rows x 32 (+1)
-  static constexpr int IXS = 65, IX_CPX = 32 * IXS;         // inverse: 32 rows x 64 (+1)
+                                                            // inverse: two rounds of 32 rows x 32 (+1) as well
   CRLOT_HD static int row1(int lane) { return lane ? 64 - lane : 32; }   // second row/column of a lane
 };
 
@@ -132,6 +132,28 @@ CRLOT_HD void fwd4096_split(cpx (&v)[64], int lane, const SplitLane4096& L, cpx&
     nyq = mk(z0.x - z0.y, 0.0f);
   }
 }
+// ---- lane 0's two self-mirrored rows, shared out over the warp ------------------------------------
+// Lane 0 holds rows/columns 0 and 32 (bins 64p and 32 + 64p), whose mirrors are in its own
+// registers: 31 pairs + DC/Nyquist + bin 1024 that the general pattern above does not cover.  Run
+// in a divergent branch they would cost the whole warp 31 more pair computations per frame, so they
+// go through 64 words of shared memory instead: lane l >= 1 owns ONE of those pairs for the whole
+// kernel (its full twiddle is a lane constant), lane 0 keeps DC, Nyquist and bin 1024.
+//   lanes 1..15 : bins k = 64 l and 2048 - k        (slots  l       and 32 - l  of lane 0)
+//   lanes 16..31: bins k = 32 + 64 (l-16), 2048 - k (slots 16 + l   and 79 - l  of lane 0)
+struct Coop4096 {
+  int zi, mi, k;   // slot of z, slot of the mirror, bin of z
+  cpx q, qr;       // (-/+ i/2) exp(-/+ i pi k/2048) and i times it
+};
+template <bool INV> CRLOT_HD Coop4096 make_coop_4096(int lane) {
+  Coop4096 c;
+  c.zi = lane < 16 ? lane : 16 + lane;
+  c.mi = lane < 16 ? 32 - lane : 79 - lane;
+  c.k = lane < 16 ? 64 * lane : 32 + 64 * (lane - 16);
+  const double th = 3.14159265358979323846 * (double)c.k / 2048.0;
+  c.q = mk((float)(-0.5 * sin(th)), (float)((INV ? 0.5 : -0.5) * cos(th)));
+  c.qr = mk(-c.q.y, c.q.x);
+  return c;
+}
 // bin held by register r of `lane` after the split
 CRLOT_HD int fwd4096_bin(int lane, int r) { return (r < 32 ? lane : Geo4096::row1(lane)) + 64 * (r & 31); }
 
@@ -164,17 +186,16 @@ CRLOT_HD void inv4096_twiddle(cpx (&v)[64], int lane, const cpx* twi) {
     v[32 + ob] = cmulc(v[32 + ob], twi[ob * 64 + a1]);
   }
 }
-CRLOT_HD void inv4096_xwrite(const cpx (&v)[64], int lane, cpx* ex) {
-  const int a1 = Geo4096::row1(lane);
+// exchange in two rounds of 32 columns (8.4 KB per warp): round h moves the lanes' column a_h.
+// The caller puts __syncwarp() between write and read and after the read.
+template <int h> CRLOT_HD void inv4096_xwrite(const cpx (&v)[64], int lane, cpx* ex) {
+  const int col = h == 0 ? lane : Geo4096::row1(lane) - 32;
 #pragma unroll
-  for (int ob = 0; ob < 32; ++ob) {
-    ex[ob * Geo4096::IXS + lane] = v[ob];
-    ex[ob * Geo4096::IXS + a1] = v[32 + ob];
-  }
+  for (int ob = 0; ob < 32; ++ob) ex[ob * Geo4096::FXS + col] = v[32 * h + ob];
 }
-CRLOT_HD void inv4096_xread(cpx (&v)[64], int lane, const cpx* ex) {
+template <int h> CRLOT_HD void inv4096_xread(cpx (&v)[64], int lane, const cpx* ex) {
 #pragma unroll
-  for (int a = 0; a < 64; ++a) v[a] = ex[lane * Geo4096::IXS + a];
+  for (int a = 0; a < 32; ++a) v[32 * h + a] = ex[lane * Geo4096::FXS + a];
 }
 // pass 2: v[oa] = z[lane + 32*oa]
 CRLOT_HD void inv4096_pass2(cpx (&v)[64]) { Dft<64, true>::run(v); }

@@ -2,6 +2,7 @@
 // the CPU (a warp = 32 sequential lanes per phase; a shuffle = reading another lane's array)
 // and compares with a double-precision DFT.  Checks the index algebra (four-step mapping,
 // exchange addressing incl. bank-conflict freedom, mirror lanes) without a GPU.
+#include <algorithm>
 #include <cmath>
 #include <complex>
 #include <cstdio>
@@ -136,7 +137,7 @@ static int run4096() {
   }
   // ---- forward ----
   static cpx v[32][64];
-  std::vector<cpx> ex(Geo4096::IX_CPX);
+  std::vector<cpx> ex(Geo4096::FX_ROUND_CPX);
   for (int l = 0; l < 32; ++l)
     for (int b = 0; b < 64; ++b) { const int i = l + 32 * b; v[l][b] = mk(x[2 * i], x[2 * i + 1]); }
   for (int l = 0; l < 32; ++l) { fwd4096_pass1(v[l]); fwd4096_twiddle(v[l], l, tw); }
@@ -152,13 +153,26 @@ static int run4096() {
   for (int l = 0; l < 32; ++l) fwd4096_xread<1>(v[l], l, ex.data());
   std::vector<cd> Xg(C + 1);
   std::vector<int> seen(C + 1, 0);
+  int sink_bad = 0;
+  cpx snap0[64];
   for (int l = 0; l < 32; ++l) {
     fwd4096_pass2(v[l]);
+    if (l == 0) for (int r = 0; r < 64; ++r) snap0[r] = v[0][r];
     cpx nyq = mk(0, 0);
     fwd4096_split(v[l], l, make_split_4096<false>(l), nyq);
     for (int r = 0; r < 64; ++r) { const int k = fwd4096_bin(l, r); Xg[k] = cd(v[l][r].x, v[l][r].y); ++seen[k]; }
     if (l == 0) { Xg[C] = cd(nyq.x, nyq.y); ++seen[C]; }
   }
+  // lane 0's rows shared out over the warp (Coop4096): same bins, single-factor twiddle
+  double coop_err = 0;
+  for (int l = 1; l < 32; ++l) {
+    const Coop4096 co = make_coop_4096<false>(l);
+    cpx x1, x2;
+    split_pair32<0, false>(snap0[co.zi], snap0[co.mi], co.q, co.qr, x1, x2);
+    coop_err = std::max(coop_err, std::abs(cd(x1.x, x1.y) - Xg[co.k]) / std::abs(Xg[co.k]));
+    coop_err = std::max(coop_err, std::abs(cd(x2.x, x2.y) - Xg[C - co.k]) / std::abs(Xg[C - co.k]));
+  }
+  if (coop_err > 2e-6) sink_bad = 1;
   int cover = 1;
   for (int k = 0; k <= C; ++k) if (seen[k] != 1) cover = 0;
   double err = 0, nrm = 0;
@@ -177,16 +191,18 @@ static int run4096() {
   }
   for (int ob = 0; ob < 32; ++ob) for (int j = 0; j < 2; ++j) for (int hw = 0; hw < 2; ++hw) {
     std::set<int> banks;
-    for (int l = 16 * hw; l < 16 * hw + 16; ++l) banks.insert((ob * Geo4096::IXS + (j ? Geo4096::row1(l) : l)) % 16);
+    for (int l = 16 * hw; l < 16 * hw + 16; ++l) banks.insert((ob * Geo4096::FXS + (j ? Geo4096::row1(l) - 32 : l)) % 16);
     if (banks.size() != 16) ++conflicts;
   }
-  for (int a = 0; a < 64; ++a) for (int hw = 0; hw < 2; ++hw) {
+  for (int a = 0; a < 32; ++a) for (int hw = 0; hw < 2; ++hw) {
     std::set<int> banks;
-    for (int l = 16 * hw; l < 16 * hw + 16; ++l) banks.insert((l * Geo4096::IXS + a) % 16);
+    for (int l = 16 * hw; l < 16 * hw + 16; ++l) banks.insert((l * Geo4096::FXS + a) % 16);
     if (banks.size() != 16) ++conflicts;
   }
-  for (int l = 0; l < 32; ++l) inv4096_xwrite(v[l], l, ex.data());
-  for (int l = 0; l < 32; ++l) inv4096_xread(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) inv4096_xwrite<0>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) inv4096_xread<0>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) inv4096_xwrite<1>(v[l], l, ex.data());
+  for (int l = 0; l < 32; ++l) inv4096_xread<1>(v[l], l, ex.data());
   std::vector<double> y(N);
   for (int l = 0; l < 32; ++l) {
     inv4096_pass2(v[l]);
@@ -199,7 +215,7 @@ static int run4096() {
   err = 0; nrm = 0;
   for (int i = 0; i < N; ++i) { err += (y[i] - x[i]) * (y[i] - x[i]); nrm += (double)x[i] * x[i]; }
   const double inv_rel = std::sqrt(err / nrm);
-  const int ok = fwd_rel < 5e-7 && inv_rel < 5e-7 && exact0 && cover && conflicts == 0;
+  const int ok = fwd_rel < 5e-7 && inv_rel < 5e-7 && exact0 && cover && conflicts == 0 && !sink_bad;
   printf("N=4096 (1 warp/frame, 64 regs/lane)  fwd rel-L2 %.3e  inv rel-L2 %.3e  xchg conflicts %d  bins covered once %d  exact-zero imag %d  %s\n",
          fwd_rel, inv_rel, conflicts, cover, exact0, ok ? "OK" : "FAIL");
   return ok ? 0 : 1;
