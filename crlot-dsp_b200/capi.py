@@ -187,6 +187,29 @@ class Plan:
         _check(lib().crlot_stft_plan_envelope(self._h, _p(out)))
         return out
 
+    # -- spectral-domain hook -------------------------------------------------
+    def set_spectral_gain(self, gain):
+        """Attach a per-bin real gain applied as the inverse kernels load each spectrum row.
+        gain: cuda float32 [bins] (same gains for every frame) or [..., bins] with one row per spectrum
+        row (time-frequency mask, laid out like the spectra); None clears the hook."""
+        if gain is None:
+            self._sgain = None
+            _check(lib().crlot_stft_plan_set_spectral_gain(self._h, C.c_void_p(0), C.c_longlong(0)))
+            return
+        if gain.shape[-1] != self.bins or not gain.is_contiguous():
+            raise CrlotInvalidArgument(1, "gain must be contiguous with bins as the last dimension")
+        self._sgain = gain                      # keep the tensor alive while the plan points at it
+        _check(lib().crlot_stft_plan_set_spectral_gain(self._h, C.c_void_p(gain.data_ptr()),
+                                                       C.c_longlong(0 if gain.dim() == 1 else self.bins)))
+
+    def apply_spectral_gain(self, spec, gain):
+        """The hook as its own in-place pass over spec (complex64 [..., bins])."""
+        rows = spec.numel() // self.bins
+        _check(lib().crlot_spectral_gain_apply(self._h, C.c_void_p(spec.data_ptr()), C.c_longlong(rows),
+                                               C.c_void_p(gain.data_ptr()), C.c_longlong(0 if gain.dim() == 1 else self.bins),
+                                               _stream_ptr(self.device)))
+        return spec
+
     def n_frames(self, length):
         return frame_count(length, self.nfft, self.hop, self.boundary_mode)
 

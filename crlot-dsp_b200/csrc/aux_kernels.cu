@@ -96,6 +96,19 @@ __global__ void division_selftest_kernel(const float2* __restrict__ den_rcp, lon
   if (bad) atomicAdd(mismatches, bad);
 }
 
+// spectral-domain hook as its own pass: one thread per bin, rows strided over the grid's y
+__global__ void spectral_gain_kernel(cpx* spec, long long rows, int bins, const float* gain, long long row_stride) {
+  const long long total = rows * bins;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long r = i / bins;
+    const int k = static_cast<int>(i - r * bins);
+    const float g = __ldg(gain + r * row_stride + k);
+    const cpx x = spec[i];
+    spec[i] = mk(__fmul_rn(x.x, g), __fmul_rn(x.y, g));
+  }
+}
+
 }  // namespace
 
 cudaError_t launch_build_den_rcp(const float* norm, float eps, long long n, float2* den_rcp, cudaStream_t st) {
@@ -149,6 +162,16 @@ int device_sm_count() {
     cached_dev = dev;
   }
   return cached;
+}
+
+cudaError_t launch_spectral_gain(cpx* spec, long long rows, int bins, const float* gain, long long row_stride,
+                                 cudaStream_t st) {
+  if (rows <= 0) return cudaSuccess;
+  const long long total = rows * bins;
+  const long long want = (total + 255) / 256;
+  const int grid = static_cast<int>(want < 8ll * device_sm_count() ? want : 8ll * device_sm_count());
+  spectral_gain_kernel<<<grid, 256, 0, st>>>(spec, rows, bins, gain, row_stride);
+  return cudaGetLastError();
 }
 
 }  // namespace crlot

@@ -152,6 +152,8 @@ struct crlot_plan_s {
   DevArr<float2> den_rcp;      // {max(env, eps), refined reciprocal}: division table of the fused kernel 2+3
   int k1_scrub = 0;            // kernel-1 clean-up mode (kernels.h)
   bool k23_win_ok = true;      // synthesis window can be pre-scaled by 2/N exactly (fused kernel 2+3)
+  const float* sgain = nullptr;   // spectral-domain hook (caller-owned device table), see crlot_stft_plan_set_spectral_gain
+  long long sgain_row_stride = 0;
   unsigned int tiny2 = 0;
   std::vector<float> env_host;
   HostSlot slot[2];
@@ -377,6 +379,26 @@ int crlot_stft_plan_envelope(crlot_plan_t plan, float* host_out) {
   return CRLOT_OK;
 }
 
+// ---- spectral-domain hook -----------------------------------------------------------
+int crlot_stft_plan_set_spectral_gain(crlot_plan_t plan, const float* d_gain, long long row_stride) {
+  if (!plan) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (d_gain && row_stride != 0 && row_stride < plan->bins)
+    return fail(CRLOT_ERR_INVALID_ARGUMENT, "row_stride must be 0 (one gain row for every frame) or >= bins");
+  if (d_gain && reinterpret_cast<uintptr_t>(d_gain) % 4 != 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "gain table must be 4-byte aligned");
+  plan->sgain = d_gain;
+  plan->sgain_row_stride = d_gain ? row_stride : 0;
+  return CRLOT_OK;
+}
+
+int crlot_spectral_gain_apply(crlot_plan_t plan, void* d_spec, long long rows, const float* d_gain, long long row_stride,
+                              void* stream) {
+  if (!plan || !d_spec || !d_gain) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (rows < 0 || (row_stride != 0 && row_stride < plan->bins)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  DeviceGuard g(plan->d.device);
+  CU(launch_spectral_gain(static_cast<cpx*>(d_spec), rows, plan->bins, d_gain, row_stride, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
 // ---- execute --------------------------------------------------------------------------------
 int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
                        long long n_frames, void* d_spec, void* stream) {
@@ -405,6 +427,7 @@ int crlot_istft_execute(crlot_plan_t plan, const void* d_spec, long long rows, f
   k.spec = static_cast<const cpx*>(d_spec); k.rows = rows; k.nfft = plan->d.nfft; k.frames = d_frames;
   k.window = (fuse_win && plan->syn_active) ? plan->win_s.p : nullptr;
   k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
+  k.sgain = plan->sgain; k.sgain_row_stride = plan->sgain_row_stride;
   CU(launch_istft_inv(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
@@ -432,6 +455,7 @@ static void fill_k23(K23Params& k, crlot_plan_t plan, int counter_word) {
   k.gain = plan->d.gain; k.eps = plan->d.eps; k.norm = plan->env.p; k.ring_len = static_cast<long long>(plan->ring_len);
   k.den_rcp = plan->den_rcp.p;
   k.counter = plan->counter.p + counter_word; k.chunk_blocks = 0;
+  k.sgain = plan->sgain; k.sgain_row_stride = plan->sgain_row_stride;
 }
 
 int crlot_selftest_division(crlot_plan_t plan, unsigned long long n, unsigned long long seed, unsigned long long* mismatches) {
@@ -541,6 +565,7 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
         fill_k23(k, plan, 2 + (it & 1));
         k.spec = s.spec.p; k.spec_chan_rows = nf; k.frames_per_chan = nf; k.channels = 1; k.t_offset = t0;
         k.frame_t0 = s0 - t0; k.out = s.out.p; k.out_chan_stride = 0; k.n_out = t1 - t0;
+        if (k.sgain) k.sgain += (static_cast<long long>(c) * F + k_lo) * k.sgain_row_stride;   // rows of this slab
         CU(launch_istft_ola(k, s.stream));
         CU(cudaMemcpyAsync(yout + t0, s.out.p, static_cast<size_t>(t1 - t0) * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
         continue;
@@ -549,6 +574,8 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
       k2.spec = s.spec.p; k2.rows = nf; k2.nfft = N; k2.frames = s.frames.p;
       k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.sa = plan->sa.p; k2.pre = plan->pre.p;
       k2.scrub = plan->d.scrub;
+      k2.sgain = plan->sgain ? plan->sgain + (static_cast<long long>(c) * F + k_lo) * plan->sgain_row_stride : nullptr;
+      k2.sgain_row_stride = plan->sgain_row_stride;
       CU(launch_istft_inv(k2, s.stream));
       K3Params k3{};
       k3.frames = s.frames.p; k3.frames_chan_rows = nf; k3.frames_per_chan = nf; k3.channels = 1; k3.nfft = N; k3.hop = H;

@@ -98,6 +98,7 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
     const long long m1 = min(m0 + p.chunk_blocks, p.m_end);
     const cpx* spec = p.spec + c * p.spec_chan_rows * (C + 1);
     float* out = p.out + c * p.out_chan_stride;
+    const float* sgain = p.sgain ? p.sgain + c * p.spec_chan_rows * p.sgain_row_stride : nullptr;
     const long long k0 = max(0ll, m0 - R + 1);
     const long long k1 = min(m1, F);
 
@@ -125,6 +126,18 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
 #pragma unroll
         for (int b = 0; b < B; ++b) dst[j * B + b] = ok ? ldg_stream(row + a + A * b) : mk(0.f, 0.f);
         dnyq[j] = (ok && a == 0) ? ldg_stream(row + C) : mk(0.f, 0.f);
+      }
+      if (sgain != nullptr) {   // spectral-domain hook: per-bin real gain applied as the rows are loaded
+#pragma unroll
+        for (int j = 0; j < X::M1; ++j) {
+          const int i1 = lane + 32 * j, g = i1 / A, a = i1 % A;
+          if (g < lft) {
+            const float* gr = sgain + (kb + g) * p.sgain_row_stride;
+#pragma unroll
+            for (int b = 0; b < B; ++b) dst[j * B + b] = mul2(dst[j * B + b], splat(__ldg(gr + a + A * b)));
+            if (a == 0) dnyq[j] = mul2(dnyq[j], splat(__ldg(gr + C)));
+          }
+        }
       }
     };
 

@@ -57,6 +57,18 @@ __global__ void __launch_bounds__(kK2Warps * 32, 1) istft_inv_kernel(const K2Par
       for (int b = 0; b < B; ++b) v[j * B + b] = ok ? ldg_stream(row + a + A * b) : mk(0.f, 0.f);
       nyq[j] = (ok && a == 0) ? ldg_stream(row + C) : mk(0.f, 0.f);
     }
+    if (p.sgain != nullptr) {     // spectral-domain hook: per-bin real gain applied as the row is loaded
+#pragma unroll
+      for (int j = 0; j < X::M1; ++j) {
+        const int i1 = lane + 32 * j, g = i1 / A, a = i1 % A;
+        if (g < left) {
+          const float* gr = p.sgain + (row0 + g) * p.sgain_row_stride;
+#pragma unroll
+          for (int b = 0; b < B; ++b) v[j * B + b] = mul2(v[j * B + b], splat(__ldg(gr + a + A * b)));
+          if (a == 0) nyq[j] = mul2(nyq[j], splat(__ldg(gr + C)));
+        }
+      }
+    }
     cpx mid[X::M1];
     auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp)); };
     inv_split_pairs<X>(v, lane, SL, mirror, nyq, mid);
@@ -152,16 +164,28 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
     // lane 0's self-mirrored columns are split in place in the staging buffer, one pair per lane
     // (warpfft4096.cuh "Coop4096"); the general in-register split below then skips lane 0
     cpx* st = stage - off;
+    const float* gr = p.sgain ? p.sgain + rowi * p.sgain_row_stride : nullptr;   // spectral-domain hook
     if (lane != 0) {
+      cpx xa = st[CO.k], xb = st[C - CO.k];
+      if (gr) {
+        xa = mul2(xa, splat(__ldg(gr + CO.k)));
+        xb = mul2(xb, splat(__ldg(gr + C - CO.k)));
+      }
       cpx x1, x2;
-      split_pair32<0, true>(st[CO.k], st[C - CO.k], CO.q, CO.qr, x1, x2);
+      split_pair32<0, true>(xa, xb, CO.q, CO.qr, x1, x2);
       st[CO.k] = x1;
       st[C - CO.k] = x2;
     } else {
-      const cpx x0 = off ? extra : stage[0];
-      const cpx xn = off ? stage[C - 1] : extra;
+      cpx x0 = off ? extra : stage[0];
+      cpx xn = off ? stage[C - 1] : extra;
+      cpx xm = st[C / 2];
+      if (gr) {
+        x0 = mul2(x0, splat(__ldg(gr)));
+        xn = mul2(xn, splat(__ldg(gr + C)));
+        xm = mul2(xm, splat(__ldg(gr + C / 2)));
+      }
       dc = mk(0.5f * (x0.x + xn.x), 0.5f * (x0.x - xn.x));     // only the real parts (kiss_fftr.c:131-132)
-      st[C / 2] = mul2(st[C / 2], mk(1.f, -1.f));
+      st[C / 2] = mul2(xm, mk(1.f, -1.f));
     }
     __syncwarp();
     cpx v[64];
@@ -170,6 +194,13 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
 #pragma unroll
     for (int b = 0; b < 32; ++b) v[32 + b] = st[a1 + 64 * b];
     if (lane == 0) v[0] = dc;
+    if (gr && lane != 0) {        // lane 0's values are already scaled (and split) above
+#pragma unroll
+      for (int b = 0; b < 32; ++b) {
+        v[b] = mul2(v[b], splat(__ldg(gr + lane + 64 * b)));
+        v[32 + b] = mul2(v[32 + b], splat(__ldg(gr + a1 + 64 * b)));
+      }
+    }
     __syncwarp();                 // every lane has read the staging buffer
     const long long nxt = rowi + stride;
     if (nxt < p.rows) off = prefetch(nxt, extra);

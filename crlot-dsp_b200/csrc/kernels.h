@@ -43,6 +43,10 @@ struct K2Params {
   const cpx* sa;
   const cpx* pre;
   int scrub;
+  // spectral-domain hook: X[row][k] *= sgain[row*sgain_row_stride + k] (real gain, one
+  // rounding per component) as the row is loaded; nullptr = none; stride 0 = the same gains for every row
+  const float* sgain;
+  long long sgain_row_stride;
 };
 cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st);
 
@@ -91,11 +95,17 @@ struct K23Params {
   long long n_out;
   unsigned int* counter;        // zeroed work counter
   int chunk_blocks;             // output hop blocks per scheduled chunk (0 = choose)
+  const float* sgain;           // spectral-domain hook, as in K2Params; rows indexed like `spec`
+  long long sgain_row_stride;
   long long m_begin, m_end;     // filled by the launcher: hop blocks [m_begin, m_end) cover [0, n_out)
 };
 bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offset, long long frame_t0,
                          long long out_chan_stride, const void* out, const void* norm);
 cudaError_t launch_istft_ola(K23Params p, cudaStream_t st);
+
+// in-place spectral hook as its own pass: spec[row][k] *= gain[row*row_stride + k]
+cudaError_t launch_spectral_gain(cpx* spec, long long rows, int bins, const float* gain, long long row_stride,
+                                 cudaStream_t st);
 
 // den_rcp[i] = {max(norm[i], eps), div_refined_rcp(max(norm[i], eps))}
 cudaError_t launch_build_den_rcp(const float* norm, float eps, long long n, float2* den_rcp, cudaStream_t st);

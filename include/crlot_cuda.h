@@ -107,6 +107,24 @@ int crlot_stft_plan_info(crlot_plan_t plan, crlot_plan_info* info);
 /* copies the plan's envelope (ring_len floats) to host */
 int crlot_stft_plan_envelope(crlot_plan_t plan, float* host_out);
 
+/* Spectral-domain hook between kernels 1 and 2.  The reference leaves an explicit gap
+ * between IFftPlan::forward and IFftPlan::inverse for per-bin processing
+ *   ref: bench/e2e_benchmark.cc:158-166 (forward; inverse), bench/performance_benchmark.cc:221
+ * -- the reason spectra are materialised at all.  The hook is a REAL gain per bin:
+ *   X'[row][k] = ( fl(Re X[row][k] * g), fl(Im X[row][k] * g) ),  g = d_gain[row*row_stride + k]
+ * row_stride == 0: one table of `bins` gains for every frame (an equaliser);
+ * row_stride >= bins: one row of gains per spectrum row, laid out like the spectra
+ *                     [channels][frames][row_stride] (a time-frequency mask).
+ * crlot_stft_plan_set_spectral_gain attaches the table (device pointer, caller-owned, must stay valid
+ * until cleared with NULL) to the plan: crlot_istft_execute, crlot_istft_ola_execute,
+ * crlot_roundtrip_execute and crlot_roundtrip_host then apply it as each spectrum row is LOADED by
+ * the inverse kernel -- the spectra written by kernel 1 stay untouched and no extra pass over them
+ * is made.  crlot_spectral_gain_apply is the same arithmetic as its own in-place pass; the two routes
+ * give bit-identical frames/audio. */
+int crlot_stft_plan_set_spectral_gain(crlot_plan_t plan, const float* d_gain, long long row_stride);
+int crlot_spectral_gain_apply(crlot_plan_t plan, void* d_spec, long long rows, const float* d_gain,
+                              long long row_stride, void* stream);
+
 /* Kernel 1.  Frame k of channel c = d_signal[c*chan_stride + k*hop + (0..nfft)), samples at or
  * beyond `len` read as zero.  d_spec: [channels][n_frames][nfft/2+1] interleaved (re,im) fp32.
  * replaces: Framer::pop + analysis-window loop + IFftPlan::forward
