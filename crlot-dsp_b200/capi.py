@@ -57,6 +57,7 @@ def lib():
         L = C.CDLL(p)
         L.crlot_cuda_last_error.restype = C.c_char_p
         L.crlot_frame_count.restype = C.c_longlong
+        L.crlot_framequeue_count.restype = C.c_longlong
         L.crlot_ola_ring_len.restype = C.c_size_t
         L.crlot_buf_device_ptr.restype = C.c_void_p
         L.crlot_buf_bytes.restype = C.c_size_t
@@ -116,6 +117,29 @@ def ola_envelope(window, frame, hop, apply_window_inside=True, eps=1e-8):
 
 def frame_count(length, frame, hop, mode):
     return int(lib().crlot_frame_count(C.c_longlong(length), C.c_int(frame), C.c_int(hop), C.c_int(mode)))
+
+
+PAD_CONSTANT, PAD_REFLECT, PAD_EDGE = 0, 1, 2      # dsp::PadMode (ref: dsp/frame/FrameQueue.h:8-12)
+
+
+def framequeue_count(length, frame, hop, center=True):
+    """FrameQueue::getNumFrames() (ref: dsp/frame/FrameQueue.cc:100-115)."""
+    n = int(lib().crlot_framequeue_count(C.c_longlong(length), C.c_int(frame), C.c_int(hop), C.c_int(int(center))))
+    if n < 0:
+        raise CrlotInvalidArgument(1, "Frame size and hop size must be greater than 0")
+    return n
+
+
+def framequeue_extract(signal, frame, hop, center=True, pad_mode=PAD_CONSTANT, device=0):
+    """FrameQueue(...).getAllFrames() on the device: cuda float32 [L] -> [F, frame], bit-exact."""
+    torch = _torch()
+    L = signal.numel()
+    F = framequeue_count(L, frame, hop, center)
+    out = torch.empty((F, frame), dtype=torch.float32, device=signal.device)
+    _check(lib().crlot_framequeue_extract(C.c_void_p(signal.data_ptr() if L else 0), C.c_longlong(L), C.c_int(frame), C.c_int(hop),
+                                          C.c_int(int(center)), C.c_int(pad_mode), C.c_longlong(F), C.c_void_p(out.data_ptr() if F else 0),
+                                          C.c_int(device), _stream_ptr(device)))
+    return out
 
 
 def bytes_per_sample(nfft, hop):
@@ -231,6 +255,23 @@ class Plan:
         _check(lib().crlot_stft_execute(self._h, C.c_void_p(signal.data_ptr()), C.c_longlong(signal.stride(0) if ch > 1 else 0),
                                         C.c_longlong(length), C.c_int(ch), C.c_longlong(F), C.c_void_p(out.data_ptr()),
                                         _stream_ptr(self.device)))
+        return out
+
+    def stft_framequeue(self, signal, center=True, pad_mode=PAD_CONSTANT, length=None, out=None):
+        """Kernel 1 over FrameQueue's frames (centre padding nfft/2, CONSTANT / REFLECT / EDGE) without
+        materialising the padded signal.  signal: cuda float32 [channels, L] -> complex64 [channels, F, bins]."""
+        torch = _torch()
+        if signal.dim() == 1:
+            signal = signal.unsqueeze(0)
+        ch = signal.shape[0]
+        length = signal.shape[1] if length is None else length
+        F = framequeue_count(length, self.nfft, self.hop, center)
+        if out is None:
+            out = torch.empty((ch, F, self.bins), dtype=torch.complex64, device=signal.device)
+        _check(lib().crlot_stft_execute_framequeue(self._h, C.c_void_p(signal.data_ptr()),
+                                                   C.c_longlong(signal.stride(0) if ch > 1 else 0), C.c_longlong(length),
+                                                   C.c_int(ch), C.c_longlong(F), C.c_int(int(center)), C.c_int(pad_mode),
+                                                   C.c_void_p(out.data_ptr()), _stream_ptr(self.device)))
         return out
 
     def istft_frames(self, spec, fuse_synthesis_window=False, out=None):

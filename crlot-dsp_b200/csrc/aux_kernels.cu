@@ -96,6 +96,18 @@ __global__ void division_selftest_kernel(const float2* __restrict__ den_rcp, lon
   if (bad) atomicAdd(mismatches, bad);
 }
 
+// FrameQueue::getAllFrames (reference: dsp/frame/FrameQueue.cc:28-46): pure index math, bit-exact
+__global__ void framequeue_extract_kernel(const float* sig, long long len, int frame, int hop, int pad, int pad_mode,
+                                          long long n_frames, float* frames) {
+  const long long total = n_frames * frame;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long k = i / frame;
+    const int u = static_cast<int>(i - k * frame);
+    frames[i] = pad_value(sig, len, k * hop + u - pad, pad_mode);
+  }
+}
+
 // spectral-domain hook as its own pass: one thread per bin, rows strided over the grid's y
 __global__ void spectral_gain_kernel(cpx* spec, long long rows, int bins, const float* gain, long long row_stride) {
   const long long total = rows * bins;
@@ -171,6 +183,15 @@ cudaError_t launch_spectral_gain(cpx* spec, long long rows, int bins, const floa
   const long long want = (total + 255) / 256;
   const int grid = static_cast<int>(want < 8ll * device_sm_count() ? want : 8ll * device_sm_count());
   spectral_gain_kernel<<<grid, 256, 0, st>>>(spec, rows, bins, gain, row_stride);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_framequeue_extract(const float* sig, long long len, int frame, int hop, int pad, int pad_mode,
+                                      long long n_frames, float* frames, cudaStream_t st) {
+  if (n_frames <= 0) return cudaSuccess;
+  const long long want = (n_frames * frame + 255) / 256;
+  const int grid = static_cast<int>(want < 8ll * device_sm_count() ? want : 8ll * device_sm_count());
+  framequeue_extract_kernel<<<grid, 256, 0, st>>>(sig, len, frame, hop, pad, pad_mode, n_frames, frames);
   return cudaGetLastError();
 }
 

@@ -417,6 +417,56 @@ int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_
   return CRLOT_OK;
 }
 
+// ---- FrameQueue centre / pad front end ---------------------------------------------
+long long crlot_framequeue_count(long long len, int frame, int hop, int center) {
+  // FrameQueue::calculateNumFrames over the padded length (FrameQueue.cc:75,100-115)
+  if (frame <= 0 || hop <= 0 || len < 0) return -1;
+  const long long padded = center ? len + 2ll * (frame / 2) : len;
+  if (padded < frame) return 0;
+  const long long tail = frame > hop ? frame - hop : 0;
+  if (padded < tail) return 0;
+  return (padded - tail) / hop;
+}
+
+int crlot_framequeue_extract(const float* d_signal, long long len, int frame, int hop, int center, int pad_mode,
+                             long long n_frames, float* d_frames, int device, void* stream) {
+  // same checks and messages as the reference constructor (FrameQueue.cc:13-21)
+  if (frame <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Frame size must be greater than 0");
+  if (hop <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Hop size must be greater than 0");
+  if (!d_signal && len > 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Input pointer cannot be null when length > 0");
+  if (len < 0 || len >= (1ll << 31)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "length out of range (the reference indexes with int)");
+  if (pad_mode < CRLOT_PAD_CONSTANT || pad_mode > CRLOT_PAD_EDGE) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad pad mode");
+  const long long F = crlot_framequeue_count(len, frame, hop, center);
+  if (n_frames < 0 || n_frames > F) return fail(CRLOT_ERR_INVALID_ARGUMENT, "n_frames exceeds crlot_framequeue_count");
+  if (n_frames > 0 && !d_frames) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  DeviceGuard g(device);
+  CU(launch_framequeue_extract(d_signal, len, frame, hop, center ? frame / 2 : 0, pad_mode, n_frames, d_frames,
+                               static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+int crlot_stft_execute_framequeue(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
+                                  int channels, long long n_frames, int center, int pad_mode, void* d_spec, void* stream) {
+  if (!plan || !d_signal || !d_spec) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || n_frames < 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (pad_mode < CRLOT_PAD_CONSTANT || pad_mode > CRLOT_PAD_EDGE) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad pad mode");
+  if (len >= (1ll << 31)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "length out of range (the reference indexes with int)");
+  if (n_frames > crlot_framequeue_count(len, plan->d.nfft, plan->d.hop, center))
+    return fail(CRLOT_ERR_INVALID_ARGUMENT, "n_frames exceeds crlot_framequeue_count");
+  if (chan_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_signal) % 16 != 0 || reinterpret_cast<uintptr_t>(d_spec) % 8 != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "signal must be 16-byte aligned with chan_stride a multiple of 4 floats");
+  DeviceGuard g(plan->d.device);
+  K1Params k{};
+  k.sig = d_signal; k.chan_stride = chan_stride; k.len = len; k.channels = channels; k.frames = n_frames;
+  k.pad = center ? plan->d.nfft / 2 : 0; k.pad_mode = pad_mode;
+  k.nfft = plan->d.nfft; k.hop = plan->d.hop;
+  k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
+  k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p;
+  k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
+  CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
 int crlot_istft_execute(crlot_plan_t plan, const void* d_spec, long long rows, float* d_frames, int fuse_win, void* stream) {
   if (!plan || !d_spec || !d_frames) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
   if (rows < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");

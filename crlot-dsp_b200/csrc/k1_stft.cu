@@ -41,31 +41,42 @@ struct K1Smem {
   __host__ __device__ static int total(int rcap, int nwarps) { return kTableBytes + nwarps * per_warp_bytes(rcap); }
 };
 
-// Fill ring positions of absolute samples [abs0, abs0+count) of this channel: the 16-byte
-// multiple that exists in the signal by bulk copy, a ragged remainder by plain loads, zeros
-// beyond the end of the signal.  All lanes call this after a __syncwarp() that follows their
-// last read of the overwritten region.
-__device__ __forceinline__ void ring_fill(float* ring, int mask, const float* sig, long long len, long long abs0,
-                                          int count, uint32_t bar, int lane) {
-  long long avail = len - abs0;
+// Where a frame's samples come from: position q of the (virtually padded) stream of a channel is
+// sample q - pad of the signal; positions outside [pad, pad + len) take FrameQueue's padding value
+// (pad = 0, mode 0 is the Framer case: zeros beyond the end).
+struct SigView {
+  const float* sig;
+  long long len;
+  int pad, pad_mode;
+};
+
+// Fill ring positions of stream positions [abs0, abs0+count) of this channel: the 16-byte
+// multiple that exists in the signal by bulk copy; padding on either side and a ragged remainder
+// by plain loads.  abs0, pad and count are multiples of 4.  All lanes call this after a
+// __syncwarp() that follows their last read of the overwritten region.
+__device__ __forceinline__ void ring_fill(float* ring, int mask, const SigView& sv, long long abs0, int count,
+                                          uint32_t bar, int lane) {
+  const long long lo = abs0 - sv.pad;                  // signal index of the first position
+  int lead = 0;                                        // positions before the signal starts
+  if (lo < 0) lead = static_cast<int>(-lo < count ? -lo : count);
+  long long avail = sv.len - (lo + lead);
   if (avail < 0) avail = 0;
-  if (avail > count) avail = count;
+  if (avail > count - lead) avail = count - lead;
   const int nb = static_cast<int>(avail) & ~3;
-  if (nb < count) {   // only at the tail of a channel
-    for (int i = nb + lane; i < count; i += 32) {
-      const long long a = abs0 + i;
-      ring[a & mask] = (a < len) ? __ldg(sig + a) : 0.0f;
-    }
-    __syncwarp();     // the tail is in place before the barrier phase can complete
+  if (lead > 0 || lead + nb < count) {   // only at the edges of a channel
+    for (int i = lane; i < count; i += 32)
+      if (i < lead || i >= lead + nb) ring[(abs0 + i) & mask] = pad_value(sv.sig, sv.len, lo + i, sv.pad_mode);
+    __syncwarp();     // the edge is in place before the barrier phase can complete
   }
   if (lane == 0) {
     fence_proxy_async_smem();
     mbar_arrive_expect_tx(bar, static_cast<uint32_t>(nb) * 4u);
     if (nb > 0) {
-      const int r0 = static_cast<int>(abs0 & mask);
+      const int r0 = static_cast<int>((abs0 + lead) & mask);
       const int first = min(nb, mask + 1 - r0);
-      bulk_g2s(smem_u32(ring + r0), sig + abs0, static_cast<uint32_t>(first) * 4u, bar);
-      if (nb > first) bulk_g2s(smem_u32(ring), sig + abs0 + first, static_cast<uint32_t>(nb - first) * 4u, bar);
+      const float* src = sv.sig + (lo + lead);
+      bulk_g2s(smem_u32(ring + r0), src, static_cast<uint32_t>(first) * 4u, bar);
+      if (nb > first) bulk_g2s(smem_u32(ring), src + first, static_cast<uint32_t>(nb - first) * 4u, bar);
     }
   }
 }
@@ -125,14 +136,14 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
     const long long c = q / chunks_per_chan;
     const long long first = (q % chunks_per_chan) * frames_per_chunk;
     const long long nfr = min(frames_per_chunk, p.frames - first);
-    const float* sig = p.sig + c * p.chan_stride;
+    const SigView sig{p.sig + c * p.chan_stride, p.len, p.pad, p.pad_mode};
     cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (C + 1);
     long long pos = first * H;
     const int nsteps = static_cast<int>((nfr + G - 1) / G);
 
     int dirty = 0;
     __syncwarp();
-    ring_fill(ring, mask, sig, p.len, pos, S, bar, lane);
+    ring_fill(ring, mask, sig, pos, S, bar, lane);
 
     for (int s = 0; s < nsteps; ++s) {
       mbar_wait(bar, parity);
@@ -173,7 +184,7 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
         }
       }
       __syncwarp();
-      if (s + 1 < nsteps) ring_fill(ring, mask, sig, p.len, pos + S, G * H, bar, lane);
+      if (s + 1 < nsteps) ring_fill(ring, mask, sig, pos + S, G * H, bar, lane);
 
       pass1<X, false>(v);
       twiddle1<X, false>(v, lane, s_tw1);
@@ -248,13 +259,13 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
     const long long c = q / chunks_per_chan;
     const long long first = (q % chunks_per_chan) * frames_per_chunk;
     const int nsteps = static_cast<int>(min(frames_per_chunk, p.frames - first));
-    const float* sig = p.sig + c * p.chan_stride;
+    const SigView sig{p.sig + c * p.chan_stride, p.len, p.pad, p.pad_mode};
     cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (C + 1);
     long long pos = first * H;
 
     int dirty = 0;
     __syncwarp();
-    ring_fill(ring, mask, sig, p.len, pos, NFFT, bar, lane);
+    ring_fill(ring, mask, sig, pos, NFFT, bar, lane);
 
     for (int s = 0; s < nsteps; ++s) {
       mbar_wait(bar, parity);
@@ -288,7 +299,7 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
         }
       }
       __syncwarp();
-      if (s + 1 < nsteps) ring_fill(ring, mask, sig, p.len, pos + NFFT, H, bar, lane);
+      if (s + 1 < nsteps) ring_fill(ring, mask, sig, pos + NFFT, H, bar, lane);
 
       fwd4096_pass1(v);
       fwd4096_twiddle(v, lane, s_tw);

@@ -16,6 +16,7 @@ struct K1Params {
   const float* sig;
   long long chan_stride;     // floats between channels (multiple of 4)
   long long len;             // valid samples per channel
+  int pad, pad_mode;         // FrameQueue front end: frames index the stream [pad | signal | pad] (0, 0 = Framer)
   int channels;
   long long frames;          // frames per channel to compute
   int nfft, hop;
@@ -113,6 +114,10 @@ cudaError_t launch_build_den_rcp(const float* norm, float eps, long long n, floa
 // the plan's own denominators; *mismatches (device) is incremented per differing result
 cudaError_t launch_division_selftest(const float2* den_rcp, long long ring_len, unsigned long long n,
                                      unsigned long long seed, unsigned long long* mismatches, cudaStream_t st);
+
+// FrameQueue::getAllFrames on the device: frames[k][i] = padded[k*hop + i] (bit-exact gather)
+cudaError_t launch_framequeue_extract(const float* sig, long long len, int frame, int hop, int pad, int pad_mode,
+                                      long long n_frames, float* frames, cudaStream_t st);
 
 // ---- helpers ----------------------------------------------------------------------------------
 // x[c][i] = uniform[-1,1) from hash(seed, channel0 + c, i0 + i); same function as oracle/crlot_oracle.c

@@ -3,6 +3,7 @@
 //
 // Same namespaces, class names, method names, argument meaning and exception types as
 //   dsp::BoundaryMode / dsp::Framer                 ref: dsp/frame/framer.h:11-131
+//   dsp::PadMode / dsp::FrameQueue                  ref: dsp/frame/FrameQueue.h:8-112
 //   dsp::WindowType / NormalizationType / WindowLUT ref: dsp/window/WindowLUT.h:13-190
 //   dsp::fft::FftDomain / FftPlanDesc / IFftPlan / MakeFftPlan
 //                                                   ref: dsp/fft/api/fft_api.h:9-51
@@ -99,6 +100,62 @@ class Framer {
   crlot_framer_t h_ = nullptr;
   size_t frame_size_ = 0, hop_size_ = 0, channels_ = 1;
   BoundaryMode boundary_mode_ = BoundaryMode::ZERO_PAD;
+};
+
+// ------------------------------------------------------------------------------------------------
+// FrameQueue (centre / pad front end)            ref: dsp/frame/FrameQueue.h:8-112
+// ------------------------------------------------------------------------------------------------
+enum class PadMode { CONSTANT, REFLECT, EDGE };
+
+class FrameQueue {
+ public:
+  // Same checks, messages and frame layout as the reference constructor (FrameQueue.cc:9-48); the
+  // frames are gathered on the device (crlot_framequeue_extract) and kept as the AoS vector.
+  FrameQueue(const float* in, size_t len, size_t frame_size, size_t hop_size, bool center = true,
+             PadMode pad_mode = PadMode::CONSTANT)
+      : frame_size_(frame_size), hop_size_(hop_size), center_(center), pad_mode_(pad_mode) {
+    if (frame_size == 0) throw std::invalid_argument("Frame size must be greater than 0");
+    if (hop_size == 0) throw std::invalid_argument("Hop size must be greater than 0");
+    if (in == nullptr && len > 0) throw std::invalid_argument("Input pointer cannot be null when length > 0");
+    const long long nf = crlot_framequeue_count((long long)len, (int)frame_size, (int)hop_size, center ? 1 : 0);
+    num_frames_ = nf > 0 ? static_cast<size_t>(nf) : 0;
+    frames_.resize(num_frames_ * frame_size_);
+    if (num_frames_ == 0) return;
+    const int dev = detail::default_device();
+    crlot_buf_t din = nullptr, dfr = nullptr;
+    detail::check(crlot_buf_create((len ? len : 1) * sizeof(float), dev, &din));
+    int rc = crlot_buf_create(frames_.size() * sizeof(float), dev, &dfr);
+    if (rc == CRLOT_OK && len) rc = crlot_buf_upload(din, 0, in, len * sizeof(float), nullptr);
+    if (rc == CRLOT_OK)
+      rc = crlot_framequeue_extract(static_cast<const float*>(crlot_buf_device_ptr(din)), (long long)len, (int)frame_size,
+                                    (int)hop_size, center ? 1 : 0, static_cast<int>(pad_mode), nf,
+                                    static_cast<float*>(crlot_buf_device_ptr(dfr)), dev, nullptr);
+    if (rc == CRLOT_OK) rc = crlot_buf_download(dfr, 0, frames_.data(), frames_.size() * sizeof(float), nullptr);
+    if (rc == CRLOT_OK) rc = crlot_cuda_stream_sync(dev, nullptr);
+    crlot_buf_destroy(din);
+    crlot_buf_destroy(dfr);
+    detail::check(rc);
+  }
+  size_t getNumFrames() const { return num_frames_; }
+  size_t getFrameSize() const { return frame_size_; }
+  size_t getHopSize() const { return hop_size_; }
+  const float* getFrame(size_t frame_idx) const {
+    if (frame_idx >= num_frames_) throw std::out_of_range("Frame index out of range");
+    return &frames_[frame_idx * frame_size_];
+  }
+  void copyFrame(size_t frame_idx, float* output) const {
+    if (frame_idx >= num_frames_) throw std::out_of_range("Frame index out of range");
+    if (output == nullptr) throw std::invalid_argument("Output buffer cannot be null");
+    const float* f = &frames_[frame_idx * frame_size_];
+    for (size_t i = 0; i < frame_size_; ++i) output[i] = f[i];
+  }
+  const std::vector<float>& getAllFrames() const { return frames_; }
+
+ private:
+  size_t frame_size_, hop_size_, num_frames_ = 0;
+  bool center_;
+  PadMode pad_mode_;
+  std::vector<float> frames_;
 };
 
 // ------------------------------------------------------------------------------------------------

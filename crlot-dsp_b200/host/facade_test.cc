@@ -1,7 +1,8 @@
 // facade_test.cc -- exercises the reference-named C++ classes of crlot_dsp.h on a B200, in the
 // shape of the reference's own gtest cases (gtest is not in this image, so plain CHECKs):
 //   tests/framer_test.cc:100-322, tests/window_lut_test.cc:85-215, tests/fft_test.cc:57-250,
-//   tests/ola_accumulator_test.cc:143-330, and the loop of bench/e2e_benchmark.cc:138-186.
+//   tests/ola_accumulator_test.cc:143-330, tests/frame_queue_test.cc:30-420, and the loop of
+//   bench/e2e_benchmark.cc:138-186.
 // It does not link the oracle.  Arrays it produces are written to <outdir>/*.f32 so that
 // tests/test_gpu_facades_cpp.py can compare them with the oracle on the same inputs.
 //
@@ -393,6 +394,78 @@ static void test_framer_stft() {
   CHECK(same);
 }
 
+// ---- FrameQueue (tests/frame_queue_test.cc) -----------------------------------------------------------
+static void test_framequeue() {
+  std::vector<float> x(1000);
+  for (size_t i = 0; i < x.size(); ++i) x[i] = std::sin(2.0 * M_PI * 440.0 * i / 48000.0);
+  {  // BasicConstruction :30-36, hop sizes :69-108
+    FrameQueue fq(x.data(), x.size(), 32, 16);
+    CHECK(fq.getFrameSize() == 32);
+    CHECK(fq.getHopSize() == 16);
+    CHECK(fq.getNumFrames() == (1000 + 32 - 16) / 16);
+    CHECK(fq.getFrame(1) == fq.getFrame(0) + 32);          // AoS continuity :255-260
+    CHECK(fq.getAllFrames().size() == fq.getNumFrames() * 32);
+    for (size_t h : {8u, 16u, 24u}) {
+      FrameQueue q(x.data(), x.size(), 32, h);
+      CHECK(q.getHopSize() == h && q.getNumFrames() > 0);
+    }
+  }
+  {  // odd frame size :39-51, center = false
+    FrameQueue fq(x.data(), x.size(), 31, 15);
+    CHECK(fq.getNumFrames() == (1000 + 30 - 16) / 15);
+    FrameQueue nc(x.data(), x.size(), 32, 16, false);
+    CHECK(nc.getNumFrames() == (1000 - 16) / 16);
+    bool same = true;
+    for (size_t i = 0; i < 32; ++i) same = same && nc.getFrame(3)[i] == x[3 * 16 + i];
+    CHECK(same);
+  }
+  {  // REFLECTIndexMapping :321-364: [1,2,3,4], frame 8, hop 4 -> 4 3 2 1 | 1 2 3 4 ; 1 2 3 4 | 3 2 1 1
+    const float pat[4] = {1.f, 2.f, 3.f, 4.f};
+    FrameQueue fq(pat, 4, 8, 4, true, PadMode::REFLECT);
+    CHECK(fq.getNumFrames() == 2);
+    const float want0[8] = {4, 3, 2, 1, 1, 2, 3, 4}, want1[8] = {1, 2, 3, 4, 3, 2, 1, 1};
+    bool ok = true;
+    for (int i = 0; i < 8; ++i) ok = ok && fq.getFrame(0)[i] == want0[i] && fq.getFrame(1)[i] == want1[i];
+    CHECK(ok);
+    FrameQueue ed(pat, 4, 8, 4, true, PadMode::EDGE);
+    const float e0[8] = {1, 1, 1, 1, 1, 2, 3, 4};
+    ok = true;
+    for (int i = 0; i < 8; ++i) ok = ok && ed.getFrame(0)[i] == e0[i];
+    CHECK(ok);
+  }
+  {  // extreme cases :264-318,367-: empty, single sample, shorter than a frame
+    FrameQueue e(nullptr, 0, 32, 16, true, PadMode::REFLECT);
+    CHECK(e.getNumFrames() == 1);
+    bool zeros = true;
+    for (size_t i = 0; i < 32; ++i) zeros = zeros && e.getFrame(0)[i] == 0.0f;
+    CHECK(zeros);
+    const float one[1] = {1.0f};
+    FrameQueue s1(one, 1, 32, 16, true, PadMode::REFLECT);
+    CHECK(s1.getNumFrames() > 0);
+    bool found = false;
+    for (size_t i = 0; i < 32; ++i) found = found || s1.getFrame(0)[i] == 1.0f;
+    CHECK(found);
+    const float three[3] = {1.f, 2.f, 3.f};
+    FrameQueue s3(three, 3, 32, 16, true, PadMode::REFLECT);
+    CHECK(s3.getNumFrames() > 0);
+    CHECK_THROWS(FrameQueue(three, 3, 0, 16), std::invalid_argument);
+    CHECK_THROWS(FrameQueue(three, 3, 32, 0), std::invalid_argument);
+    CHECK_THROWS(FrameQueue(nullptr, 3, 32, 16), std::invalid_argument);
+    CHECK_THROWS(s3.getFrame(s3.getNumFrames()), std::out_of_range);
+    CHECK_THROWS(s3.copyFrame(0, nullptr), std::invalid_argument);
+  }
+  {  // dumped for the oracle comparison on the Python side
+    std::vector<float> v = noise(777, 99u);
+    dump("fq_in", v.data(), v.size());
+    FrameQueue a(v.data(), v.size(), 64, 16, true, PadMode::REFLECT);
+    dump("fq_reflect_64_16", a.getAllFrames().data(), a.getAllFrames().size());
+    FrameQueue b(v.data(), v.size(), 64, 48, true, PadMode::EDGE);
+    dump("fq_edge_64_48", b.getAllFrames().data(), b.getAllFrames().size());
+    FrameQueue c(v.data(), v.size(), 50, 50, false, PadMode::CONSTANT);
+    dump("fq_const_50_50_nc", c.getAllFrames().data(), c.getAllFrames().size());
+  }
+}
+
 int main(int argc, char** argv) {
   g_out = argc > 1 ? argv[1] : ".";
   int ndev = 0;
@@ -407,6 +480,7 @@ int main(int argc, char** argv) {
     test_ola();
     test_e2e_loop();
     test_framer_stft();
+    test_framequeue();
   } catch (const std::exception& e) {
     std::printf("unexpected exception: %s\n", e.what());
     return 1;

@@ -133,6 +133,27 @@ int crlot_spectral_gain_apply(crlot_plan_t plan, void* d_spec, long long rows, c
 int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
                        long long n_frames, void* d_spec, void* stream);
 
+/* FrameQueue centre / pad front end as an addressing mode of kernel 1.
+ * The stream the frames index is [pad | signal | pad] with pad = nfft/2 when center != 0 (else no
+ * padding), frame k = stream[k*hop, k*hop + nfft); padding values follow getPaddingValueSafe:
+ * CONSTANT zeros, EDGE clamps, REFLECT is reflect101 INCLUDING its asymmetric negative branch
+ * (-1 -> 0, -2 -> 1, ...; n -> n-2) that the reference's tests pin.
+ *   ref: dsp/frame/FrameQueue.cc:9-48,68-115; dsp/frame/Indexing.h:18-70;
+ *        tests/frame_queue_test.cc:264-366
+ * crlot_framequeue_count   = FrameQueue::getNumFrames()  (-1 on zero sizes)
+ * crlot_framequeue_extract = FrameQueue::getAllFrames() on the device, [n_frames][frame], bit-exact
+ * crlot_stft_execute_framequeue = kernel 1 over those frames without materialising them: the padded
+ *   stream is never built, interior frames take the same bulk-copy path as crlot_stft_execute and
+ *   only the pad positions are computed by index.  Lengths are limited to < 2^31 (the reference
+ *   indexes the padded signal with int). */
+enum { CRLOT_PAD_CONSTANT = 0, CRLOT_PAD_REFLECT = 1, CRLOT_PAD_EDGE = 2 };   /* dsp::PadMode */
+long long crlot_framequeue_count(long long len, int frame, int hop, int center);
+int crlot_framequeue_extract(const float* d_signal, long long len, int frame, int hop, int center, int pad_mode,
+                             long long n_frames, float* d_frames, int device, void* stream);
+int crlot_stft_execute_framequeue(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
+                                  int channels, long long n_frames, int center, int pad_mode, void* d_spec,
+                                  void* stream);
+
 /* Kernel 2.  rows spectra -> rows frames of nfft floats, scaled by 1/nfft and cleaned up;
  * with fuse_synthesis_window != 0 each sample is additionally multiplied (one rounding) by the
  * plan's resolved synthesis window, so that crlot_ola_accumulate can be told frames are

@@ -99,6 +99,54 @@ long orc_framer(const float* x, long frames_in, long frame, long hop, long chann
 }
 
 /* ------------------------------------------------------------------------------------ */
+/* FrameQueue (centre / pad front end) restated: dsp/frame/FrameQueue.cc:9-48,68-115,      */
+/* dsp/frame/Indexing.h:18-70.  PadMode: 0 CONSTANT (zeros), 1 REFLECT, 2 EDGE.            */
+/* ------------------------------------------------------------------------------------ */
+
+/* Indexing.h:18-34 -- note the asymmetric negative branch (-i-1), pinned by                */
+/* tests/frame_queue_test.cc:264-366 of the reference                                       */
+static long orc_reflect101(long i, long n) {
+  if (n <= 1) return 0;
+  while (i < 0 || i >= n) {
+    if (i < 0) i = -i - 1;
+    else i = 2 * n - 2 - i;
+  }
+  return i;
+}
+
+/* Indexing.h:46-70: value of the (virtually) padded signal at signed index idx */
+float orc_pad_value(const float* x, long len, long idx, int pad_mode) {
+  if (len <= 0) return 0.0f;
+  if (idx >= 0 && idx < len) return x[idx];
+  switch (pad_mode) {
+    case 2: return idx < 0 ? x[0] : x[len - 1];
+    case 1: return x[orc_reflect101(idx, len)];
+    default: return 0.0f;
+  }
+}
+
+/* FrameQueue.cc:100-115: padded_len = len + 2*(frame/2) when centred; frames that fit */
+long orc_framequeue_count(long len, long frame, long hop, int center) {
+  if (frame <= 0 || hop <= 0 || len < 0) return -1;
+  const long padded = center ? len + 2 * (frame / 2) : len;
+  if (padded < frame) return 0;
+  const long tail = frame > hop ? frame - hop : 0;
+  if (padded < tail) return 0;
+  return (padded - tail) / hop;
+}
+
+/* frame k, sample i = padded[k*hop + i], padded[p] = pad_value(p - pad) (FrameQueue.cc:28-46,68-98) */
+long orc_framequeue(const float* x, long len, long frame, long hop, int center, int pad_mode, float* frames_out,
+                    long max_frames) {
+  const long total = orc_framequeue_count(len, frame, hop, center);
+  if (total < 0 || !frames_out) return total;
+  const long pad = center ? frame / 2 : 0;
+  for (long k = 0; k < total && k < max_frames; ++k)
+    for (long i = 0; i < frame; ++i) frames_out[k * frame + i] = orc_pad_value(x, len, k * hop + i - pad, pad_mode);
+  return total;
+}
+
+/* ------------------------------------------------------------------------------------ */
 /* kissfft restated: mixed-radix decimation-in-time, float, twiddles from double cos/sin */
 /* third_party/kissfft/kiss_fft.c:15-363, kiss_fftr.c:22-155, _kiss_fft_guts.h:87-145     */
 /* ------------------------------------------------------------------------------------ */

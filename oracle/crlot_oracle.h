@@ -35,6 +35,13 @@ long orc_frame_count(long len, long frame, long hop, int boundary_mode);
 long orc_framer(const float* interleaved, long frames_in, long frame, long hop, long channels,
                 int boundary_mode, float* frames_out, long max_frames);
 
+/* FrameQueue centre/pad front end      dsp/frame/FrameQueue.cc:9-48,68-115, dsp/frame/Indexing.h:18-70 */
+enum { ORC_PAD_CONSTANT = 0, ORC_PAD_REFLECT = 1, ORC_PAD_EDGE = 2 };
+float orc_pad_value(const float* x, long len, long idx, int pad_mode);
+long orc_framequeue_count(long len, long frame, long hop, int center);
+long orc_framequeue(const float* x, long len, long frame, long hop, int center, int pad_mode, float* frames_out,
+                    long max_frames);
+
 /* kissfft-based real FFT through the adapter (scrub, strides, 1/N)
  *   dsp/fft/backends/kissfft_adapter.cc:83-168, third_party/kissfft/kiss_fft.c, kiss_fftr.c */
 int orc_rfft(int nfft, int batch, int stride_in, int stride_out, const float* in, float* out_ri);

@@ -25,6 +25,7 @@ _vp = C.c_void_p
 HANN, HAMMING, BLACKMAN, RECT = 0, 1, 2, 3
 NORM_NONE, NORM_SUM_TO_ONE, NORM_L2, NORM_OLA_UNITY, NORM_OLA_SUM_WSQ = 0, 1, 2, 3, 4
 ZERO_PAD, DROP = 0, 1
+PAD_CONSTANT, PAD_REFLECT, PAD_EDGE = 0, 1, 2
 
 
 def build_oracle(force: bool = False) -> str:
@@ -75,6 +76,20 @@ class _Common:
         if n:
             f(_ptr(x), C.c_long(frames_in), C.c_long(frame), C.c_long(hop), C.c_long(channels),
               C.c_int(mode), _ptr(out), C.c_long(n))
+        return out
+
+    def framequeue(self, x, frame, hop, center=True, pad_mode=0):
+        """FrameQueue(...).getAllFrames() -> [F][frame] (pad_mode: 0 CONSTANT, 1 REFLECT, 2 EDGE)."""
+        x = np.ascontiguousarray(x, np.float32)
+        f = self._fn("framequeue")
+        f.restype = C.c_long
+        args = [_ptr(x) if x.size else None, C.c_long(x.size), C.c_long(frame), C.c_long(hop), C.c_int(int(center)), C.c_int(pad_mode)]
+        n = f(*args, None, C.c_long(0))
+        if n < 0:
+            raise ValueError("framequeue: bad arguments")
+        out = np.empty((n, frame), np.float32)
+        if n:
+            f(*args, _ptr(out), C.c_long(n))
         return out
 
     # -- fft ---------------------------------------------------------------------------

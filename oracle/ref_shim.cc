@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "dsp/fft/api/fft_api.h"
+#include "dsp/frame/FrameQueue.h"
 #include "dsp/frame/framer.h"
 #include "dsp/ola/OLAAccumulator.h"
 #include "dsp/ola/kernels.h"
@@ -77,6 +78,22 @@ long ref_framer_chunked(const float* interleaved, long frames_in, long chunk, lo
     }
   }
   return k;
+}
+
+// FrameQueue(in, len, frame, hop, center, pad_mode).getAllFrames()   dsp/frame/FrameQueue.cc:9-48
+// frames_out may be null (count only).  Returns the number of frames, -1 on exception.
+long ref_framequeue(const float* in, long len, long frame, long hop, int center, int pad_mode, float* frames_out,
+                    long max_frames) {
+  try {
+    dsp::FrameQueue fq(in, static_cast<size_t>(len), static_cast<size_t>(frame), static_cast<size_t>(hop), center != 0,
+                       static_cast<dsp::PadMode>(pad_mode));
+    const long n = static_cast<long>(fq.getNumFrames());
+    if (frames_out) {
+      const long m = std::min(n, max_frames);
+      std::memcpy(frames_out, fq.getAllFrames().data(), sizeof(float) * static_cast<size_t>(m * frame));
+    }
+    return n;
+  } catch (...) { return -1; }
 }
 
 // MakeFftPlan({Real,nfft,false,batch,si,so})->forward        kissfft_adapter.cc:83-122

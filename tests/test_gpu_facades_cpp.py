@@ -77,3 +77,11 @@ def test_framer_to_kernel1_vs_oracle(dumps, oracle):
         x = np.ascontiguousarray(inter[:, c])
         frames = np.stack([x[k * H:k * H + N] * w for k in range(F)]).astype(np.float32)
         assert rel_l2(S[c], oracle.rfft_many(frames, N)) < TOL
+
+
+def test_framequeue_facade_vs_oracle(dumps, oracle):
+    """dsp::FrameQueue facade (device gather) against the oracle's FrameQueue restatement, bit-exact."""
+    x = dumps("fq_in")
+    assert np.array_equal(bits(dumps("fq_reflect_64_16")), bits(oracle.framequeue(x, 64, 16, True, po.PAD_REFLECT).ravel()))
+    assert np.array_equal(bits(dumps("fq_edge_64_48")), bits(oracle.framequeue(x, 64, 48, True, po.PAD_EDGE).ravel()))
+    assert np.array_equal(bits(dumps("fq_const_50_50_nc")), bits(oracle.framequeue(x, 50, 50, False, po.PAD_CONSTANT).ravel()))

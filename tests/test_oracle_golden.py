@@ -154,3 +154,13 @@ def test_frame_count_formulas(oracle):
         k = fz.shape[0] - 1                      # last frame: zero tail (framer_test.cc:262-296)
         have = min(N, L - k * H)
         assert np.array_equal(fz[k, :have], x[k * H: k * H + have]) and not fz[k, have:].any()
+
+
+def test_framequeue_golden(oracle, gold):
+    """FrameQueue centre/pad frames from the compiled reference (tests/golden/make_golden_framequeue.py)."""
+    g = gold("framequeue")
+    assert g["pattern_1234_8_4_reflect"].tolist() == [[4, 3, 2, 1, 1, 2, 3, 4], [1, 2, 3, 4, 3, 2, 1, 1]]
+    for L, N, H, center, mode in g["cases"]:
+        want = g[f"f_{L}_{N}_{H}_{center}_{mode}"]
+        got = oracle.framequeue(g[f"x_{L}"], int(N), int(H), bool(center), int(mode))
+        assert got.shape == want.shape and np.array_equal(got.view(np.uint32), want.view(np.uint32)), (L, N, H, center, mode)

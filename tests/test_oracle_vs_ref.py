@@ -63,3 +63,18 @@ def test_roundtrip_random(oracle, ref_strict):
         a, b = oracle.roundtrip(x, N, H, w, mode), ref_strict.roundtrip(x, N, H, w, mode)
         for k in ("spectra", "iframes", "out"):
             assert np.array_equal(bits(a[k]), bits(b[k])), (N, H, k)
+
+
+def test_framequeue_random(oracle, ref_strict):
+    """FrameQueue restatement vs the compiled reference FrameQueue.cc, bit for bit
+    (incl. reflect101's asymmetric negative branch and inputs shorter than the padding)."""
+    rng = np.random.default_rng(23)
+    x4 = np.array([1, 2, 3, 4], np.float32)
+    assert ref_strict.framequeue(x4, 8, 4, True, po.PAD_REFLECT).tolist() == [[4, 3, 2, 1, 1, 2, 3, 4], [1, 2, 3, 4, 3, 2, 1, 1]]
+    for L in [0, 1, 2, 3, 5, 31, 32, 33, 100, 1000]:
+        for N, H in [(8, 4), (32, 16), (32, 32), (16, 4), (256, 64), (32, 8), (9, 3), (8, 20)]:
+            for center in (False, True):
+                for mode in (po.PAD_CONSTANT, po.PAD_REFLECT, po.PAD_EDGE):
+                    x = rng.standard_normal(L).astype(np.float32)
+                    a, b = oracle.framequeue(x, N, H, center, mode), ref_strict.framequeue(x, N, H, center, mode)
+                    assert a.shape == b.shape and np.array_equal(bits(a), bits(b)), (L, N, H, center, mode)
