@@ -385,6 +385,42 @@ class Plan:
         return out
 
 
+    def roundtrip_host_interleaved(self, x, out=None):
+        """x: numpy float32 [L, channels] interleaved -> numpy [n_out, channels] (crlot_roundtrip_host_interleaved)."""
+        x = np.asarray(x)
+        assert x.dtype == np.float32 and x.flags.c_contiguous and x.ndim == 2
+        L, ch = x.shape
+        n_out = self.out_len(L)
+        if out is None:
+            out = np.empty((n_out, ch), np.float32)
+        got = C.c_longlong(0)
+        _check(lib().crlot_roundtrip_host_interleaved(self._h, _p(x), C.c_longlong(L), C.c_int(ch), _p(out), C.byref(got)))
+        assert got.value == n_out
+        return out
+
+
+def deinterleave(aos, chan_stride=None, device=0):
+    """cuda float32 [n, channels] -> [channels, chan_stride] planar (first n columns written)."""
+    torch = _torch()
+    n, ch = aos.shape
+    cs = n if chan_stride is None else chan_stride
+    out = torch.zeros((ch, cs), dtype=torch.float32, device=aos.device)
+    _check(lib().crlot_deinterleave(C.c_void_p(aos.data_ptr()), C.c_longlong(n), C.c_int(ch), C.c_void_p(out.data_ptr()),
+                                    C.c_longlong(cs), C.c_int(device), _stream_ptr(device)))
+    return out
+
+
+def interleave(planar, n=None, device=0):
+    """cuda float32 [channels, stride] planar -> [n, channels] interleaved."""
+    torch = _torch()
+    ch = planar.shape[0]
+    n = planar.shape[1] if n is None else n
+    out = torch.empty((n, ch), dtype=torch.float32, device=planar.device)
+    _check(lib().crlot_interleave(C.c_void_p(planar.data_ptr()), C.c_longlong(planar.stride(0)), C.c_longlong(n), C.c_int(ch),
+                                  C.c_void_p(out.data_ptr()), C.c_int(device), _stream_ptr(device)))
+    return out
+
+
 # ---- drop-in FFT plan (dsp::fft::IFftPlan over host arrays) ---------------------------------------
 class FftPlan:
     def __init__(self, nfft, batch=1, stride_in=1, stride_out=1, in_place=False, device=0):

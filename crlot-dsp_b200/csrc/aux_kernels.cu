@@ -96,6 +96,43 @@ __global__ void division_selftest_kernel(const float2* __restrict__ den_rcp, lon
   if (bad) atomicAdd(mismatches, bad);
 }
 
+// Interleaved (AoS, [n][c]) <-> planar ([c][n]) copies (reference: dsp/ola/aos_to_soa.cc:13-17 and the
+// Framer's interleaved push, dsp/frame/framer.cc:133-141).  One thread per time index; the channel loop
+// is inside the thread so that every 32-byte sector of the interleaved side is consumed by one warp.
+template <int CH>
+__global__ void deinterleave_kernel(const float* aos, long long n, int channels, float* planar, long long chan_stride) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    if (CH == 2) {
+      const float2 v = *reinterpret_cast<const float2*>(aos + 2 * i);
+      planar[i] = v.x;
+      planar[chan_stride + i] = v.y;
+    } else if (CH == 4) {
+      const float4 v = *reinterpret_cast<const float4*>(aos + 4 * i);
+      planar[i] = v.x;
+      planar[chan_stride + i] = v.y;
+      planar[2 * chan_stride + i] = v.z;
+      planar[3 * chan_stride + i] = v.w;
+    } else {
+      for (int c = 0; c < channels; ++c) planar[c * chan_stride + i] = aos[i * channels + c];
+    }
+  }
+}
+template <int CH>
+__global__ void interleave_kernel(const float* planar, long long chan_stride, long long n, int channels, float* aos) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    if (CH == 2) {
+      *reinterpret_cast<float2*>(aos + 2 * i) = make_float2(planar[i], planar[chan_stride + i]);
+    } else if (CH == 4) {
+      *reinterpret_cast<float4*>(aos + 4 * i) =
+          make_float4(planar[i], planar[chan_stride + i], planar[2 * chan_stride + i], planar[3 * chan_stride + i]);
+    } else {
+      for (int c = 0; c < channels; ++c) aos[i * channels + c] = planar[c * chan_stride + i];
+    }
+  }
+}
+
 // FrameQueue::getAllFrames (reference: dsp/frame/FrameQueue.cc:28-46): pure index math, bit-exact
 __global__ void framequeue_extract_kernel(const float* sig, long long len, int frame, int hop, int pad, int pad_mode,
                                           long long n_frames, float* frames) {
@@ -192,6 +229,29 @@ cudaError_t launch_framequeue_extract(const float* sig, long long len, int frame
   const long long want = (n_frames * frame + 255) / 256;
   const int grid = static_cast<int>(want < 8ll * device_sm_count() ? want : 8ll * device_sm_count());
   framequeue_extract_kernel<<<grid, 256, 0, st>>>(sig, len, frame, hop, pad, pad_mode, n_frames, frames);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_deinterleave(const float* aos, long long n, int channels, float* planar, long long chan_stride,
+                                cudaStream_t st) {
+  if (n <= 0 || channels <= 0) return cudaSuccess;
+  const long long want = (n + 255) / 256;
+  const int grid = static_cast<int>(want < 16ll * device_sm_count() ? want : 16ll * device_sm_count());
+  const bool a8 = reinterpret_cast<uintptr_t>(aos) % 8 == 0, a16 = reinterpret_cast<uintptr_t>(aos) % 16 == 0;
+  if (channels == 2 && a8) deinterleave_kernel<2><<<grid, 256, 0, st>>>(aos, n, channels, planar, chan_stride);
+  else if (channels == 4 && a16) deinterleave_kernel<4><<<grid, 256, 0, st>>>(aos, n, channels, planar, chan_stride);
+  else deinterleave_kernel<0><<<grid, 256, 0, st>>>(aos, n, channels, planar, chan_stride);
+  return cudaGetLastError();
+}
+cudaError_t launch_interleave(const float* planar, long long chan_stride, long long n, int channels, float* aos,
+                              cudaStream_t st) {
+  if (n <= 0 || channels <= 0) return cudaSuccess;
+  const long long want = (n + 255) / 256;
+  const int grid = static_cast<int>(want < 16ll * device_sm_count() ? want : 16ll * device_sm_count());
+  const bool a8 = reinterpret_cast<uintptr_t>(aos) % 8 == 0, a16 = reinterpret_cast<uintptr_t>(aos) % 16 == 0;
+  if (channels == 2 && a8) interleave_kernel<2><<<grid, 256, 0, st>>>(planar, chan_stride, n, channels, aos);
+  else if (channels == 4 && a16) interleave_kernel<4><<<grid, 256, 0, st>>>(planar, chan_stride, n, channels, aos);
+  else interleave_kernel<0><<<grid, 256, 0, st>>>(planar, chan_stride, n, channels, aos);
   return cudaGetLastError();
 }
 

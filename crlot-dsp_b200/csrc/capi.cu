@@ -137,7 +137,7 @@ static void envelope_impl(float* norm, const float* w, size_t ring, size_t N, si
 // ---------------------------------------------------------------------------------------------
 struct HostSlot {
   cudaStream_t stream = nullptr;
-  DevArr<float> in, frames, out;
+  DevArr<float> in, frames, out, aos;
   DevArr<cpx> spec;
 };
 
@@ -158,6 +158,8 @@ struct crlot_plan_s {
   std::vector<float> env_host;
   HostSlot slot[2];
   long long slot_frames = 0;   // capacity of the host-path workspace, in frames
+  int slot_group = 0;          // ... and in channels per slab (interleaved host path)
+  bool slot_aos = false;
 };
 
 static cudaError_t upload_cpx(DevArr<cpx>& dst, const std::vector<float>& v) {
@@ -564,8 +566,11 @@ int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long 
 
 // Host-buffer round trip: time slabs through two workspace slots, one stream each, so the
 // H2D copy of slab i+1 and the D2H copy of slab i-1 overlap the kernels of slab i.
-int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_stride, long long len, int channels,
-                         float* h_out, long long out_chan_stride, long long* n_out_per_chan) {
+// aos: h_in / h_out are interleaved [n][channels] (what Framer::push and WavReader hand over,
+// ref: dsp/frame/framer.cc:133-141, io/wav.cc:90-123); every slab carries all channels, is
+// de-interleaved on the device after the copy and re-interleaved before the copy back.
+static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long chan_stride, long long len, int channels,
+                               float* h_out, long long out_chan_stride, long long* n_out_per_chan, bool aos) {
   if (!plan || !h_in || !h_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
   if (channels <= 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
   const int N = plan->d.nfft, H = plan->d.hop;
@@ -573,27 +578,32 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
   const long long n_out = F > 0 ? (F - 1) * H + N : 0;
   if (n_out_per_chan) *n_out_per_chan = n_out;
   if (F == 0) return CRLOT_OK;
+  const int G = aos ? channels : 1;            // channels carried by one slab
+  if (G > 1 && plan->sgain && plan->sgain_row_stride != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "a time-frequency mask with the interleaved multi-channel host path: use the planar entry point");
   DeviceGuard g(plan->d.device);
   // slab = `slab_hops` hops of output; its frames are the ones overlapping that range
   const long long overlap = (N + H - 1) / H - 1;
-  const long long slab_hops = std::min<long long>(std::max<long long>((1ll << 24) / H, 4 * (overlap + 1)), F + overlap);
+  const long long slab_hops = std::min<long long>(std::max<long long>((1ll << 24) / H / G, 4 * (overlap + 1)), F + overlap);
   const long long slab_frames = slab_hops + overlap;
+  const long long ist = ((slab_frames - 1) * H + N + 3) / 4 * 4;      // planar strides inside the workspace
+  const long long ost = (slab_hops * H + N + 3) / 4 * 4;
   // slab offsets are multiples of the hop, so one eligibility test covers every slab
-  const bool fused = plan->k23_win_ok && istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, 0, nullptr, plan->env.p);
-  if (plan->slot_frames < slab_frames) {
+  const bool fused = plan->k23_win_ok && istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, ost, nullptr, plan->env.p);
+  if (plan->slot_frames < slab_frames || plan->slot_group < G || (aos && !plan->slot_aos)) {
     for (auto& s : plan->slot) {
       if (!s.stream) CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-      CU(s.in.alloc(static_cast<size_t>((slab_frames - 1) * H + N)));
-      CU(s.spec.alloc(static_cast<size_t>(slab_frames) * plan->bins));
-      if (!fused) CU(s.frames.alloc(static_cast<size_t>(slab_frames) * N));
-      CU(s.out.alloc(static_cast<size_t>(slab_hops) * H + N));
+      CU(s.in.alloc(static_cast<size_t>(ist) * G));
+      CU(s.spec.alloc(static_cast<size_t>(slab_frames) * plan->bins * G));
+      if (!fused) CU(s.frames.alloc(static_cast<size_t>(slab_frames) * N * G));
+      CU(s.out.alloc(static_cast<size_t>(ost) * G));
+      if (aos) CU(s.aos.alloc(static_cast<size_t>(ist) * G));
     }
-    plan->slot_frames = slab_frames;
+    plan->slot_frames = slab_frames; plan->slot_group = G; plan->slot_aos = aos;
   }
-  // separate work counters per slot are not needed: kernel 1 of a slot resets the shared counter
-  // on its own stream, so give each slot its own counter word.
+  // kernel 1 of a slot resets its work counter on its own stream: one counter word per slot
   int it = 0;
-  for (int c = 0; c < channels; ++c) {
+  for (int c = 0; c < (aos ? 1 : channels); ++c) {
     const float* xin = h_in + static_cast<long long>(c) * chan_stride;
     float* yout = h_out + static_cast<long long>(c) * out_chan_stride;
     for (long long t0 = 0; t0 < n_out; t0 += slab_hops * H, ++it) {
@@ -604,39 +614,77 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
       const long long nf = k_hi - k_lo + 1;
       const long long s0 = k_lo * H;                                   // first input sample of the slab
       const long long s1 = std::min(len, k_hi * H + N);                // one past the last that exists
-      CU(cudaMemcpyAsync(s.in.p, xin + s0, static_cast<size_t>(s1 - s0) * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+      if (aos) {
+        CU(cudaMemcpyAsync(s.aos.p, h_in + s0 * G, static_cast<size_t>(s1 - s0) * G * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+        CU(launch_deinterleave(s.aos.p, s1 - s0, G, s.in.p, ist, s.stream));
+      } else {
+        CU(cudaMemcpyAsync(s.in.p, xin + s0, static_cast<size_t>(s1 - s0) * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+      }
       K1Params k1{};
-      k1.sig = s.in.p; k1.chan_stride = 0; k1.len = s1 - s0; k1.channels = 1; k1.frames = nf; k1.nfft = N; k1.hop = H;
+      k1.sig = s.in.p; k1.chan_stride = G > 1 ? ist : 0; k1.len = s1 - s0; k1.channels = G; k1.frames = nf; k1.nfft = N; k1.hop = H;
       k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p;
       k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2;
       CU(launch_stft_fwd(k1, s.stream));
+      const long long row0 = static_cast<long long>(c) * F + k_lo;     // first spectrum row of the slab (planar mode)
       if (fused) {
         K23Params k{};
         fill_k23(k, plan, 2 + (it & 1));
-        k.spec = s.spec.p; k.spec_chan_rows = nf; k.frames_per_chan = nf; k.channels = 1; k.t_offset = t0;
-        k.frame_t0 = s0 - t0; k.out = s.out.p; k.out_chan_stride = 0; k.n_out = t1 - t0;
-        if (k.sgain) k.sgain += (static_cast<long long>(c) * F + k_lo) * k.sgain_row_stride;   // rows of this slab
+        k.spec = s.spec.p; k.spec_chan_rows = nf; k.frames_per_chan = nf; k.channels = G; k.t_offset = t0;
+        k.frame_t0 = s0 - t0; k.out = s.out.p; k.out_chan_stride = G > 1 ? ost : 0; k.n_out = t1 - t0;
+        if (k.sgain) k.sgain += (G > 1 ? 0 : row0) * k.sgain_row_stride;
         CU(launch_istft_ola(k, s.stream));
-        CU(cudaMemcpyAsync(yout + t0, s.out.p, static_cast<size_t>(t1 - t0) * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
-        continue;
+      } else {
+        K2Params k2{};
+        k2.spec = s.spec.p; k2.rows = nf * G; k2.nfft = N; k2.frames = s.frames.p;
+        k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.sa = plan->sa.p; k2.pre = plan->pre.p;
+        k2.scrub = plan->d.scrub;
+        k2.sgain = plan->sgain ? plan->sgain + (G > 1 ? 0 : row0) * plan->sgain_row_stride : nullptr;
+        k2.sgain_row_stride = plan->sgain_row_stride;
+        CU(launch_istft_inv(k2, s.stream));
+        K3Params k3{};
+        k3.frames = s.frames.p; k3.frames_chan_rows = nf; k3.frames_per_chan = nf; k3.channels = G; k3.nfft = N; k3.hop = H;
+        k3.window = nullptr; k3.gain = plan->d.gain; k3.eps = plan->d.eps; k3.norm = plan->env.p;
+        k3.ring_len = static_cast<long long>(plan->ring_len); k3.t_offset = t0; k3.frame_t0 = s0 - t0; k3.out = s.out.p;
+        k3.out_chan_stride = G > 1 ? ost : 0; k3.n_out = t1 - t0;
+        CU(launch_ola_gather(k3, s.stream));
       }
-      K2Params k2{};
-      k2.spec = s.spec.p; k2.rows = nf; k2.nfft = N; k2.frames = s.frames.p;
-      k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.sa = plan->sa.p; k2.pre = plan->pre.p;
-      k2.scrub = plan->d.scrub;
-      k2.sgain = plan->sgain ? plan->sgain + (static_cast<long long>(c) * F + k_lo) * plan->sgain_row_stride : nullptr;
-      k2.sgain_row_stride = plan->sgain_row_stride;
-      CU(launch_istft_inv(k2, s.stream));
-      K3Params k3{};
-      k3.frames = s.frames.p; k3.frames_chan_rows = nf; k3.frames_per_chan = nf; k3.channels = 1; k3.nfft = N; k3.hop = H;
-      k3.window = nullptr; k3.gain = plan->d.gain; k3.eps = plan->d.eps; k3.norm = plan->env.p;
-      k3.ring_len = static_cast<long long>(plan->ring_len); k3.t_offset = t0; k3.frame_t0 = s0 - t0; k3.out = s.out.p;
-      k3.out_chan_stride = 0; k3.n_out = t1 - t0;
-      CU(launch_ola_gather(k3, s.stream));
-      CU(cudaMemcpyAsync(yout + t0, s.out.p, static_cast<size_t>(t1 - t0) * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+      if (aos) {
+        CU(launch_interleave(s.out.p, ost, t1 - t0, G, s.aos.p, s.stream));
+        CU(cudaMemcpyAsync(h_out + t0 * G, s.aos.p, static_cast<size_t>(t1 - t0) * G * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+      } else {
+        CU(cudaMemcpyAsync(yout + t0, s.out.p, static_cast<size_t>(t1 - t0) * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+      }
     }
   }
   for (auto& s : plan->slot) if (s.stream) CU(cudaStreamSynchronize(s.stream));
+  return CRLOT_OK;
+}
+
+int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_stride, long long len, int channels,
+                         float* h_out, long long out_chan_stride, long long* n_out_per_chan) {
+  return roundtrip_host_impl(plan, h_in, chan_stride, len, channels, h_out, out_chan_stride, n_out_per_chan, false);
+}
+
+int crlot_roundtrip_host_interleaved(crlot_plan_t plan, const float* h_in, long long len, int channels, float* h_out,
+                                     long long* n_out_per_chan) {
+  return roundtrip_host_impl(plan, h_in, 0, len, channels, h_out, 0, n_out_per_chan, true);
+}
+
+int crlot_deinterleave(const float* d_interleaved, long long n, int channels, float* d_planar, long long chan_stride,
+                       int device, void* stream) {
+  if (n < 0 || channels <= 0 || chan_stride < n) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (n > 0 && (!d_interleaved || !d_planar)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  DeviceGuard g(device);
+  CU(launch_deinterleave(d_interleaved, n, channels, d_planar, chan_stride, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+int crlot_interleave(const float* d_planar, long long chan_stride, long long n, int channels, float* d_interleaved,
+                     int device, void* stream) {
+  if (n < 0 || channels <= 0 || chan_stride < n) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (n > 0 && (!d_interleaved || !d_planar)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  DeviceGuard g(device);
+  CU(launch_interleave(d_planar, chan_stride, n, channels, d_interleaved, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
 

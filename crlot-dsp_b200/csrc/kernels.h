@@ -119,6 +119,12 @@ cudaError_t launch_division_selftest(const float2* den_rcp, long long ring_len, 
 cudaError_t launch_framequeue_extract(const float* sig, long long len, int frame, int hop, int pad, int pad_mode,
                                       long long n_frames, float* frames, cudaStream_t st);
 
+// interleaved [n][channels] <-> planar [channels][chan_stride] copies (bit-exact)
+cudaError_t launch_deinterleave(const float* aos, long long n, int channels, float* planar, long long chan_stride,
+                                cudaStream_t st);
+cudaError_t launch_interleave(const float* planar, long long chan_stride, long long n, int channels, float* aos,
+                              cudaStream_t st);
+
 // ---- helpers ----------------------------------------------------------------------------------
 // x[c][i] = uniform[-1,1) from hash(seed, channel0 + c, i0 + i); same function as oracle/crlot_oracle.c
 cudaError_t launch_synth_uniform(float* out, long long chan_stride, int channels, long long n,

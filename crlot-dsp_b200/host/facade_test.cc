@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "crlot_dsp.h"
+#include "crlot_wav.h"
 
 using namespace dsp;
 using namespace dsp::fft;
@@ -466,6 +467,37 @@ static void test_framequeue() {
   }
 }
 
+// ---- WAV ingest -> interleaved round trip (main/main.cc:120-160 reads a stereo file) -----
+// The Python side writes <outdir>/stereo16.wav before starting the driver; skipped when absent.
+static void test_wav_interleaved() {
+  WavReader rd;
+  if (!rd.open(g_out + "/stereo16.wav")) { std::printf("stereo16.wav absent: WAV test skipped\n"); return; }
+  CHECK(rd.is_open() && rd.get_channels() == 2 && rd.get_bits_per_sample() == 16 && rd.get_sample_rate() == 44100);
+  const size_t frames = static_cast<size_t>(rd.get_total_frames());
+  std::vector<float> x = rd.read_all();                     // interleaved [n][2]
+  CHECK(x.size() == frames * 2);
+  size_t got = 123;
+  CHECK(!rd.read(x.data(), 16, &got) && got == 0);          // at the end: false, nothing read (io/wav.cc:86)
+  dump("wav_interleaved", x.data(), x.size());
+  WindowLUT lut(1024, WindowType::HANN);
+  StftRoundTrip rt(1024, 256, lut.data(), lut.data());
+  const size_t n_out = rt.output_len_for(frames);
+  std::vector<float> y(n_out * 2, -1.0f);
+  long long n = 0;
+  detail::check(crlot_roundtrip_host_interleaved(rt.plan(), x.data(), (long long)frames, 2, y.data(), &n));
+  CHECK(static_cast<size_t>(n) == n_out);
+  dump("wav_roundtrip_interleaved", y.data(), y.size());
+  // the same through the planar entry point, channel by channel, must agree bit for bit
+  std::vector<float> pl(frames * 2), yp(n_out * 2);
+  for (size_t i = 0; i < frames; ++i) { pl[i] = x[2 * i]; pl[frames + i] = x[2 * i + 1]; }
+  rt.process(pl.data(), frames, frames, 2, yp.data(), n_out);
+  bool same = true;
+  for (size_t i = 0; i < n_out; ++i) same = same && y[2 * i] == yp[i] && y[2 * i + 1] == yp[n_out + i];
+  CHECK(same);
+  WavReader bad;
+  CHECK(!bad.open(g_out + "/does_not_exist.wav") && !bad.is_open() && bad.get_channels() == 0);
+}
+
 int main(int argc, char** argv) {
   g_out = argc > 1 ? argv[1] : ".";
   int ndev = 0;
@@ -481,6 +513,7 @@ int main(int argc, char** argv) {
     test_e2e_loop();
     test_framer_stft();
     test_framequeue();
+    test_wav_interleaved();
   } catch (const std::exception& e) {
     std::printf("unexpected exception: %s\n", e.what());
     return 1;

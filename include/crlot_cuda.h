@@ -210,6 +210,20 @@ int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long 
 int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_stride, long long len, int channels,
                          float* h_out, long long out_chan_stride, long long* n_out_per_chan);
 
+/* Interleaved (AoS) multichannel I/O.  Framer::push and WavReader hand over [n][channels]
+ * samples (ref: dsp/frame/framer.cc:45,133-141; io/wav.cc:90-123) and OLAAccumulator::push_frame_AoS
+ * de-interleaves with deinterleave_to_scratch (ref: dsp/ola/aos_to_soa.cc:5-19).
+ * crlot_deinterleave / crlot_interleave are those copies on the device (bit-exact);
+ * crlot_roundtrip_host_interleaved is crlot_roundtrip_host for interleaved host buffers: h_in holds
+ * len*channels floats, h_out receives n_out*channels floats; every time slab carries all channels and
+ * is transposed on the device between the PCIe copy and the kernels. */
+int crlot_deinterleave(const float* d_interleaved, long long n, int channels, float* d_planar, long long chan_stride,
+                       int device, void* stream);
+int crlot_interleave(const float* d_planar, long long chan_stride, long long n, int channels, float* d_interleaved,
+                     int device, void* stream);
+int crlot_roundtrip_host_interleaved(crlot_plan_t plan, const float* h_in, long long len, int channels, float* h_out,
+                                     long long* n_out_per_chan);
+
 /* Device generator of the benchmark signal: x[c][i] = uniform[-1,1) from a counter hash of
  * (seed, channel0 + c, i0 + i); identical to oracle/crlot_oracle.c:orc_synth_uniform. */
 int crlot_synth_uniform(float* d_out, long long chan_stride, int channels, long long n, unsigned long long seed,

@@ -19,11 +19,23 @@ EXE = os.path.join(ROOT, "crlot-dsp_b200", "host", "facade_test")
 def dumps(cuda, tmp_path_factory):
     assert os.path.exists(EXE), "host/facade_test not built: run __graft_entry__.build()"
     out = tmp_path_factory.mktemp("facade")
+    # a stereo 16-bit file for the driver's WavReader -> interleaved round-trip case
+    import wave
+    rng = np.random.default_rng(4)
+    pcm = rng.integers(-20000, 20000, (30000, 2)).astype("<i2")
+    with wave.open(os.path.join(str(out), "stereo16.wav"), "wb") as wf:
+        wf.setnchannels(2)
+        wf.setsampwidth(2)
+        wf.setframerate(44100)
+        wf.writeframes(pcm.tobytes())
+    np.save(os.path.join(str(out), "stereo16_pcm.npy"), pcm)
     r = subprocess.run([EXE, str(out)], capture_output=True, text=True, timeout=300)
     print(r.stdout[-3000:], r.stderr[-2000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
 
     def load(name):
+        if name.endswith(".npy"):
+            return np.load(os.path.join(str(out), name))
         return np.fromfile(os.path.join(str(out), name + ".f32"), np.float32)
     return load
 
@@ -85,3 +97,16 @@ def test_framequeue_facade_vs_oracle(dumps, oracle):
     assert np.array_equal(bits(dumps("fq_reflect_64_16")), bits(oracle.framequeue(x, 64, 16, True, po.PAD_REFLECT).ravel()))
     assert np.array_equal(bits(dumps("fq_edge_64_48")), bits(oracle.framequeue(x, 64, 48, True, po.PAD_EDGE).ravel()))
     assert np.array_equal(bits(dumps("fq_const_50_50_nc")), bits(oracle.framequeue(x, 50, 50, False, po.PAD_CONSTANT).ravel()))
+
+
+def test_wav_ingest_and_interleaved_roundtrip(dumps, oracle):
+    """WavReader (s16 -> x/32768, interleaved) and crlot_roundtrip_host_interleaved against the oracle."""
+    pcm = dumps("stereo16_pcm.npy")
+    x = dumps("wav_interleaved").reshape(-1, 2)
+    assert np.array_equal(bits(x), bits((pcm.astype(np.float32) / np.float32(32768.0))))
+    y = dumps("wav_roundtrip_interleaved").reshape(-1, 2)
+    w = oracle.window(po.HANN, 1024)
+    for c in range(2):
+        ref = oracle.roundtrip(np.ascontiguousarray(x[:, c]), 1024, 256, w, po.DROP)
+        assert y.shape[0] == ref["out"].size
+        assert rel_l2(y[:, c], ref["out"]) < TOL
