@@ -423,11 +423,33 @@ def interleave(planar, n=None, device=0):
 
 # ---- drop-in FFT plan (dsp::fft::IFftPlan over host arrays) ---------------------------------------
 class FftPlan:
-    def __init__(self, nfft, batch=1, stride_in=1, stride_out=1, in_place=False, device=0):
+    def __init__(self, nfft, batch=1, stride_in=1, stride_out=1, in_place=False, device=0, complex_domain=False):
         self._h = C.c_void_p()
         self.nfft, self.batch, self.si, self.so = nfft, batch, stride_in, stride_out
-        _check(lib().crlot_fft_plan_create(C.c_int(nfft), C.c_int(int(in_place)), C.c_int(batch), C.c_int(stride_in),
-                                           C.c_int(stride_out), C.c_int(device), C.byref(self._h)))
+        self.complex_domain, self.device = complex_domain, device
+        create = lib().crlot_fft_plan_create_complex if complex_domain else lib().crlot_fft_plan_create
+        _check(create(C.c_int(nfft), C.c_int(int(in_place)), C.c_int(batch), C.c_int(stride_in),
+                      C.c_int(stride_out), C.c_int(device), C.byref(self._h)))
+
+    def _complex(self, fn, x, batch, out_len):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros(out_len if out_len is not None else batch * self.so * self.nfft, np.complex64)
+        _check(fn(self._h, _p(x.view(np.float32)), _p(out.view(np.float32)), C.c_int(batch)))
+        return out
+
+    def forward_complex(self, x, batch=1, out_len=None):
+        return self._complex(lib().crlot_fft_forward_complex, x, batch, out_len)
+
+    def inverse_complex(self, x, batch=1, out_len=None):
+        return self._complex(lib().crlot_fft_inverse_complex, x, batch, out_len)
+
+    def complex_device(self, x, inverse=False):
+        """cuda complex64 [rows, nfft] -> [rows, nfft] (crlot_fft_complex_device, any number of rows)."""
+        torch = _torch()
+        out = torch.empty_like(x)
+        _check(lib().crlot_fft_complex_device(self._h, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()),
+                                              C.c_longlong(x.numel() // self.nfft), C.c_int(int(inverse)), _stream_ptr(self.device)))
+        return out
 
     def __del__(self):
         try:

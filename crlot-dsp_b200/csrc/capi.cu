@@ -703,6 +703,8 @@ int crlot_synth_uniform(float* d_out, long long chan_stride, int channels, long 
 // ---------------------------------------------------------------------------------------------
 struct crlot_fft_s {
   int nfft = 0, batch = 0, si = 0, so = 0, device = 0;
+  bool complex_domain = false;
+  DevArr<cpx> ctw, d_cin, d_cout;   // complex-domain plan: table of the 2n-point geometry, batch buffers
   crlot_plan_t plan = nullptr;
   DevArr<float> d_time;
   DevArr<cpx> d_freq;
@@ -739,14 +741,87 @@ int crlot_fft_plan_create(int nfft, int in_place, int batch, int stride_in, int 
 }
 int crlot_fft_plan_destroy(crlot_fft_t f) {
   if (!f) return CRLOT_OK;
-  crlot_stft_plan_destroy(f->plan);
+  if (f->plan) crlot_stft_plan_destroy(f->plan);
   { DeviceGuard g(f->device); delete f; }
   return CRLOT_OK;
 }
+// ---- complex-domain plan (ref: kissfft_adapter.cc:13-28,56-66,171-246) ------------------
+int crlot_fft_plan_create_complex(int nfft, int in_place, int batch, int stride_in, int stride_out, int device,
+                                  crlot_fft_t* out) {
+  if (!out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (batch < 1 || batch > 16) return fail(CRLOT_ERR_RUNTIME, "Batch size must be between 1 and 16");
+  if (stride_in < 1 || stride_out < 1) return fail(CRLOT_ERR_RUNTIME, "Stride must be at least 1");
+  if (in_place) return fail(CRLOT_ERR_RUNTIME, "In-place FFT is not yet supported");
+  if (nfft != 128 && nfft != 256 && nfft != 512 && nfft != 1024 && nfft != 2048)
+    return fail(CRLOT_ERR_UNSUPPORTED, "complex nfft must be 128, 256, 512, 1024 or 2048 on the GPU path");
+  std::unique_ptr<crlot_fft_s> f(new (std::nothrow) crlot_fft_s);
+  if (!f) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
+  f->nfft = nfft; f->batch = batch; f->si = stride_in; f->so = stride_out; f->device = device; f->complex_domain = true;
+  DeviceGuard g(device);
+  if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
+  const FftTables T = make_fft_tables(2 * nfft);
+  cudaError_t e = upload_cpx(f->ctw, T.tw1);
+  if (e == cudaSuccess) e = f->d_cin.alloc(static_cast<size_t>(batch) * nfft);
+  if (e == cudaSuccess) e = f->d_cout.alloc(static_cast<size_t>(batch) * nfft);
+  if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc");
+  f->h_freq.resize(static_cast<size_t>(batch) * nfft * 2);
+  *out = f.release();
+  return CRLOT_OK;
+}
+
+// contiguous rows on the device (B200 extension: any number of rows per call)
+int crlot_fft_complex_device(crlot_fft_t f, const void* d_in, void* d_out, long long rows, int inverse, void* stream) {
+  if (!f || !d_in || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (!f->complex_domain) return fail(CRLOT_ERR_RUNTIME, "Complex FFT not supported for Real domain plan");
+  if (rows < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (reinterpret_cast<uintptr_t>(d_in) % 8 != 0 || reinterpret_cast<uintptr_t>(d_out) % 8 != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "buffers must be 8-byte aligned");
+  DeviceGuard g(f->device);
+  CfftParams k{};
+  k.in = static_cast<const cpx*>(d_in); k.out = static_cast<cpx*>(d_out); k.rows = rows; k.n = f->nfft;
+  k.inverse = inverse ? 1 : 0; k.tw1 = f->ctw.p;
+  CU(launch_cfft(k, static_cast<cudaStream_t>(stream)));
+  return CRLOT_OK;
+}
+
+// batch b reads in + b*si*n with element stride si, writes out + b*so*n with element stride so
+// (ref: kissfft_adapter.cc:183-201,219-243)
+static int fft_complex_host(crlot_fft_t f, const float* h_in_ri, float* h_out_ri, int batch, int inverse) {
+  if (!f || !h_in_ri || !h_out_ri) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (!f->complex_domain) return fail(CRLOT_ERR_RUNTIME, "Complex FFT not supported for Real domain plan");
+  if (batch < 1 || batch > f->batch) return fail(CRLOT_ERR_RUNTIME, "Invalid batch size");
+  const int n = f->nfft;
+  for (int b = 0; b < batch; ++b)
+    for (int i = 0; i < n; ++i) {
+      const long long s = 2 * (static_cast<long long>(b) * f->si * n + static_cast<long long>(i) * f->si);
+      f->h_freq[2 * (static_cast<size_t>(b) * n + i)] = h_in_ri[s];
+      f->h_freq[2 * (static_cast<size_t>(b) * n + i) + 1] = h_in_ri[s + 1];
+    }
+  DeviceGuard g(f->device);
+  CU(cudaMemcpy(f->d_cin.p, f->h_freq.data(), sizeof(float) * 2 * batch * n, cudaMemcpyHostToDevice));
+  int rc = crlot_fft_complex_device(f, f->d_cin.p, f->d_cout.p, batch, inverse, nullptr);
+  if (rc) return rc;
+  CU(cudaMemcpy(f->h_freq.data(), f->d_cout.p, sizeof(float) * 2 * batch * n, cudaMemcpyDeviceToHost));
+  for (int b = 0; b < batch; ++b)
+    for (int i = 0; i < n; ++i) {
+      const long long o = 2 * (static_cast<long long>(b) * f->so * n + static_cast<long long>(i) * f->so);
+      h_out_ri[o] = f->h_freq[2 * (static_cast<size_t>(b) * n + i)];
+      h_out_ri[o + 1] = f->h_freq[2 * (static_cast<size_t>(b) * n + i) + 1];
+    }
+  return CRLOT_OK;
+}
+int crlot_fft_forward_complex(crlot_fft_t f, const float* h_in_ri, float* h_out_ri, int batch) {
+  return fft_complex_host(f, h_in_ri, h_out_ri, batch, 0);
+}
+int crlot_fft_inverse_complex(crlot_fft_t f, const float* h_in_ri, float* h_out_ri, int batch) {
+  return fft_complex_host(f, h_in_ri, h_out_ri, batch, 1);
+}
+
 // forward: batch b reads in + b*si*n with element stride si; writes out + b*so*(n/2+1) with
 // element stride so (ref: kissfft_adapter.cc:97-98,103,118)
 int crlot_fft_forward(crlot_fft_t f, const float* h_in, float* h_out_ri, int batch) {
   if (!f || !h_in || !h_out_ri) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (f->complex_domain) return fail(CRLOT_ERR_RUNTIME, "Real FFT not supported for Complex domain plan");
   if (batch < 1 || batch > f->batch) return fail(CRLOT_ERR_RUNTIME, "Invalid batch size");
   const int n = f->nfft, nb = n / 2 + 1;
   for (int b = 0; b < batch; ++b)
@@ -768,6 +843,7 @@ int crlot_fft_forward(crlot_fft_t f, const float* h_in, float* h_out_ri, int bat
 // element stride so (ref: kissfft_adapter.cc:139-147,154-165)
 int crlot_fft_inverse(crlot_fft_t f, const float* h_in_ri, float* h_out, int batch) {
   if (!f || !h_in_ri || !h_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (f->complex_domain) return fail(CRLOT_ERR_RUNTIME, "Real FFT not supported for Complex domain plan");
   if (batch < 1 || batch > f->batch) return fail(CRLOT_ERR_RUNTIME, "Invalid batch size");
   const int n = f->nfft, nb = n / 2 + 1;
   for (int b = 0; b < batch; ++b)

@@ -51,6 +51,17 @@ struct K2Params {
 };
 cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st);
 
+// ---- complex-domain plan: rows of n complex points, n in {128, 256, 512, 1024, 2048} --------------
+struct CfftParams {
+  const cpx* in;             // [rows][n]
+  cpx* out;                  // [rows][n]
+  long long rows;
+  int n;
+  int inverse;               // 1: conjugate kernel, times 1/n, clean-up rule on both components
+  const cpx* tw1;            // inter-pass table of the 2n-point real geometry (tables.h)
+};
+cudaError_t launch_cfft(const CfftParams& p, cudaStream_t st);
+
 // ---- kernel 3: gather overlap-add + envelope normalisation ------------------------------------
 // out[c][j] = ( sum_k' fma( f(k',u) , gain, acc ) ) / max(norm[(t_offset + j) % ring_len], eps),
 //   u = j - frame_t0 - k'*hop in [0,nfft), k' ascending in [0,frames),

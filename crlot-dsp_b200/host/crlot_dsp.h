@@ -306,10 +306,14 @@ class IFftPlan {
 class CudaFftPlan final : public IFftPlan {
  public:
   explicit CudaFftPlan(const FftPlanDesc& d) : desc_(d) {
-    if (d.domain != FftDomain::Real)      // the hot path is the real transform; ref: kissfft_adapter.cc:170-239
-      throw std::runtime_error("Complex-domain plans are not provided by the B200 path (Real only)");
-    dsp::detail::check(crlot_fft_plan_create(d.nfft, d.in_place ? 1 : 0, d.batch, d.stride_in, d.stride_out,
-                                             dsp::detail::default_device(), &h_));
+    if (d.domain != FftDomain::Real && d.domain != FftDomain::Complex)
+      throw std::runtime_error("Unsupported FFT domain");                 // ref: kissfft_adapter.cc:14-16
+    if (d.domain == FftDomain::Real)
+      dsp::detail::check(crlot_fft_plan_create(d.nfft, d.in_place ? 1 : 0, d.batch, d.stride_in, d.stride_out,
+                                               dsp::detail::default_device(), &h_));
+    else
+      dsp::detail::check(crlot_fft_plan_create_complex(d.nfft, d.in_place ? 1 : 0, d.batch, d.stride_in, d.stride_out,
+                                                       dsp::detail::default_device(), &h_));
   }
   ~CudaFftPlan() override { crlot_fft_plan_destroy(h_); }
   void forward(const float* in, std::complex<float>* out, int batch = 1) override {
@@ -318,11 +322,11 @@ class CudaFftPlan final : public IFftPlan {
   void inverse(const std::complex<float>* in, float* out, int batch = 1) override {
     dsp::detail::check(crlot_fft_inverse(h_, reinterpret_cast<const float*>(in), out, batch));
   }
-  void forward_complex(const std::complex<float>*, std::complex<float>*, int = 1) override {
-    throw std::runtime_error("Plan is not configured for complex FFT");   // ref: kissfft_adapter.cc:171-173
+  void forward_complex(const std::complex<float>* in, std::complex<float>* out, int batch = 1) override {
+    dsp::detail::check(crlot_fft_forward_complex(h_, reinterpret_cast<const float*>(in), reinterpret_cast<float*>(out), batch));
   }
-  void inverse_complex(const std::complex<float>*, std::complex<float>*, int = 1) override {
-    throw std::runtime_error("Plan is not configured for complex FFT");   // ref: kissfft_adapter.cc:207-209
+  void inverse_complex(const std::complex<float>* in, std::complex<float>* out, int batch = 1) override {
+    dsp::detail::check(crlot_fft_inverse_complex(h_, reinterpret_cast<const float*>(in), reinterpret_cast<float*>(out), batch));
   }
   FftDomain domain() const override { return desc_.domain; }
   int size() const override { return desc_.nfft; }

@@ -311,6 +311,19 @@ int crlot_fft_plan_create(int nfft, int in_place, int batch, int stride_in, int 
 int crlot_fft_plan_destroy(crlot_fft_t plan);
 int crlot_fft_forward(crlot_fft_t plan, const float* h_in, float* h_out_ri, int batch);
 int crlot_fft_inverse(crlot_fft_t plan, const float* h_in_ri, float* h_out, int batch);
+/* Complex-domain plan: FftPlanDesc{Complex,...} + IFftPlan::forward_complex /
+ * inverse_complex.  Same constructor checks and messages as the reference (batch 1..16, strides >= 1,
+ * no in-place; no evenness requirement); sizes 128..2048 (powers of two) run on the GPU, any other
+ * size returns CRLOT_ERR_UNSUPPORTED.  A Real plan refuses the complex calls and vice versa with the
+ * reference's messages.  Host arrays are interleaved (re,im); batch/stride addressing as in
+ *   ref: dsp/fft/backends/kissfft_adapter.cc:171-246
+ * crlot_fft_complex_device is the same transform over `rows` contiguous rows resident on the device. */
+int crlot_fft_plan_create_complex(int nfft, int in_place, int batch, int stride_in, int stride_out, int device,
+                                  crlot_fft_t* out);
+int crlot_fft_forward_complex(crlot_fft_t plan, const float* h_in_ri, float* h_out_ri, int batch);
+int crlot_fft_inverse_complex(crlot_fft_t plan, const float* h_in_ri, float* h_out_ri, int batch);
+int crlot_fft_complex_device(crlot_fft_t plan, const void* d_in, void* d_out, long long rows, int inverse,
+                             void* stream);
 
 /* ---- drop-in OLAAccumulator state (device rings, host pointers at the calls) -------------------- */
 /* replaces dsp::OLAAccumulator   ref: dsp/ola/OLAAccumulator.h:15-164, .cc:13-295 */

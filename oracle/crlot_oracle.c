@@ -431,6 +431,34 @@ int orc_irfft(int nfft, int batch, int si, int so, const float* in_ri, float* ou
   rplan_free(&p);
   return 0;
 }
+/* Complex-domain plan: forward_complex / inverse_complex (kissfft_adapter.cc:171-246): strided
+ * gather into a scratch buffer, kiss_fft, strided scatter; the inverse scales by 1/nfft and applies
+ * the clean-up rule to both components.  Complex plans accept any nfft > 0 (no evenness check). */
+int orc_cfft(int nfft, int inverse, int batch, int si, int so, const float* in_ri, float* out_ri) {
+  cplan p;
+  if (batch < 1 || batch > 16 || si < 1 || so < 1 || nfft <= 0) return -1;
+  if (cplan_init(&p, nfft, inverse)) return -1;
+  cpx* buf = (cpx*)malloc(sizeof(cpx) * (size_t)nfft);
+  cpx* res = (cpx*)malloc(sizeof(cpx) * (size_t)nfft);
+  const cpx* in = (const cpx*)in_ri;
+  cpx* out = (cpx*)out_ri;
+  const float scale = 1.0f / (float)nfft;
+  for (int b = 0; b < batch; ++b) {
+    const cpx* src = in + (long)b * si * nfft;
+    cpx* dst = out + (long)b * so * nfft;
+    for (int i = 0; i < nfft; ++i) buf[i] = src[(long)i * si];
+    cwork(res, buf, 1, p.fac, &p);
+    for (int i = 0; i < nfft; ++i) {
+      cpx v = res[i];
+      if (inverse) { v.r = scrub(v.r * scale); v.i = scrub(v.i * scale); }
+      dst[(long)i * so] = v;
+    }
+  }
+  free(buf); free(res);
+  cplan_free(&p);
+  return 0;
+}
+
 int orc_rfft_many(int nfft, long n_frames, const float* in, float* out_ri) {
   rplan p;
   if (rplan_init(&p, nfft)) return -1;

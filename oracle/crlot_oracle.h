@@ -46,6 +46,8 @@ long orc_framequeue(const float* x, long len, long frame, long hop, int center, 
  *   dsp/fft/backends/kissfft_adapter.cc:83-168, third_party/kissfft/kiss_fft.c, kiss_fftr.c */
 int orc_rfft(int nfft, int batch, int stride_in, int stride_out, const float* in, float* out_ri);
 int orc_irfft(int nfft, int batch, int stride_in, int stride_out, const float* in_ri, float* out);
+/* Complex-domain plan (forward_complex / inverse_complex)   kissfft_adapter.cc:171-246 */
+int orc_cfft(int nfft, int inverse, int batch, int stride_in, int stride_out, const float* in_ri, float* out_ri);
 int orc_rfft_many(int nfft, long n_frames, const float* in, float* out_ri);
 int orc_irfft_many(int nfft, long n_frames, const float* in_ri, float* out);
 

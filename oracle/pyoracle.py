@@ -119,6 +119,19 @@ class _Common:
             raise RuntimeError("irfft plan rejected")
         return out
 
+    def cfft(self, x, nfft, inverse=False, batch=1, stride_in=1, stride_out=1, out_len=None):
+        """Complex-domain plan: forward_complex / inverse_complex over complex64 arrays."""
+        x = np.ascontiguousarray(x, np.complex64)
+        n_out = batch * stride_out * nfft if out_len is None else out_len
+        out = np.zeros(n_out, np.complex64)
+        f = self._fn("cfft")
+        f.restype = C.c_int
+        rc = f(C.c_int(nfft), C.c_int(int(inverse)), C.c_int(batch), C.c_int(stride_in), C.c_int(stride_out),
+               _ptr(x.view(np.float32)), _ptr(out.view(np.float32)))
+        if rc != 0:
+            raise RuntimeError("complex plan rejected")
+        return out
+
     def rfft_many(self, frames, nfft):
         frames = np.ascontiguousarray(frames, np.float32).reshape(-1, nfft)
         out = np.empty((frames.shape[0], nfft // 2 + 1), np.complex64)

@@ -116,6 +116,19 @@ int ref_irfft(int nfft, int batch, int stride_in, int stride_out, const float* i
   } catch (...) { return -1; }
 }
 
+// MakeFftPlan({Complex,...})->forward_complex / inverse_complex    kissfft_adapter.cc:171-246
+int ref_cfft(int nfft, int inverse, int batch, int stride_in, int stride_out, const float* in_ri, float* out_ri) {
+  try {
+    dsp::fft::FftPlanDesc d{dsp::fft::FftDomain::Complex, nfft, false, batch, stride_in, stride_out};
+    auto p = dsp::fft::MakeFftPlan(d);
+    auto* in = reinterpret_cast<const std::complex<float>*>(in_ri);
+    auto* out = reinterpret_cast<std::complex<float>*>(out_ri);
+    if (inverse) p->inverse_complex(in, out, batch);
+    else p->forward_complex(in, out, batch);
+    return 0;
+  } catch (...) { return -1; }
+}
+
 // Many independent frames, one plan (batch=1 per call), contiguous rows.
 int ref_rfft_many(int nfft, long n_frames, const float* in, float* out_ri) {
   try {

@@ -78,3 +78,16 @@ def test_framequeue_random(oracle, ref_strict):
                     x = rng.standard_normal(L).astype(np.float32)
                     a, b = oracle.framequeue(x, N, H, center, mode), ref_strict.framequeue(x, N, H, center, mode)
                     assert a.shape == b.shape and np.array_equal(bits(a), bits(b)), (L, N, H, center, mode)
+
+
+def test_complex_plan_random(oracle, ref_strict):
+    """forward_complex / inverse_complex restatement vs the compiled reference, bit for bit."""
+    rng = np.random.default_rng(29)
+    for n in [1, 2, 3, 4, 5, 8, 30, 64, 100, 128, 256, 512, 1024, 2048, 2 * 7 * 11]:
+        for inv in (False, True):
+            for b, si, so in [(1, 1, 1), (3, 1, 1), (2, 2, 3)]:
+                x = (rng.standard_normal(b * si * n * si + 8) + 1j * rng.standard_normal(b * si * n * si + 8)).astype(np.complex64)
+                if inv and n > 4:
+                    x[3] = np.nan
+                    x[5] *= 1e-36
+                assert np.array_equal(bits(oracle.cfft(x, n, inv, b, si, so)), bits(ref_strict.cfft(x, n, inv, b, si, so))), (n, inv, b, si, so)
