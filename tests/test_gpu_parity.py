@@ -276,3 +276,48 @@ def test_k1_cleanup_inside_a_stream(cuda, dsp, oracle, N, H):
         assert (err / den < TOL) if den > 0 else (err == 0), k
     # the all-zero-but-one-tiny frame comes out exactly zero, as the reference's does
     assert not ref[150].any() and not S[150].any()
+
+
+@pytest.mark.parametrize("N,H,fused_ok", [(2048, 512, True), (4096, 1024, False)])
+def test_full_size_2p30_properties(cuda, dsp, oracle, N, H, fused_ok):
+    """BASELINE configs[1] (c2) and one c4 shard at their FULL size (2^30 samples, 43 GB of device
+    arrays): size-independent properties and slice oracles at ring-aligned offsets spread over the
+    whole signal, including the very end."""
+    if cuda.cuda.get_device_properties(0).total_memory < 60e9:
+        pytest.skip("needs 60 GB of device memory")
+    L = 1 << 30
+    w = oracle.window(po.HANN, N)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP)
+    x = dsp.synth_uniform(1, L, seed=0xC0FFEE)
+    F = plan.n_frames(L)
+    assert F == (L - N) // H + 1
+    out, spec, frames = plan.roundtrip(x)
+    assert out.shape == (1, (F - 1) * H + N)
+    ring = plan.ring_len
+    nblk = L // ring
+    for blk in (0, 1, nblk // 3, nblk // 2 + 1, nblk - 2):
+        s0 = blk * ring
+        n = min(24 * H + N, L - s0)
+        seg = oracle.synth_uniform(0xC0FFEE, 0, s0, n)
+        assert np.array_equal(bits(x[0, s0:s0 + n].cpu().numpy()), bits(seg))           # generator, bit-exact
+        r = oracle.roundtrip(seg, N, H, w, po.DROP)
+        lo, hi = (N if blk else 0), (r["n_frames"] - 1) * H
+        assert rel_l2(out[0, s0 + lo:s0 + hi].cpu().numpy(), r["out"][lo:hi]) < TOL, blk
+        k0 = s0 // H
+        assert rel_l2(spec[0, k0:k0 + r["n_frames"]].cpu().numpy(), r["spectra"]) < TOL, blk
+    # the tail of the signal: last frames and the final N-H samples of the output
+    s0 = (nblk - 1) * ring
+    seg = oracle.synth_uniform(0xC0FFEE, 0, s0, L - s0)
+    r = oracle.roundtrip(seg, N, H, w, po.DROP)
+    assert s0 // H + r["n_frames"] == F
+    assert rel_l2(out[0, s0 + N:].cpu().numpy(), r["out"][N:]) < TOL
+    del frames
+    # determinism and (K2+K3 fused) == (K2 -> K3) over all 2^30 samples, compared on the device
+    if fused_ok:
+        out_f = plan.istft_ola(spec)
+        assert cuda.equal(out_f.view(cuda.int32), out.view(cuda.int32))
+        del out_f
+    # linearity with a power-of-two factor is exact in fp32
+    x.mul_(0.25)
+    out2 = plan.roundtrip_fused(x, spec=spec)[0] if fused_ok else plan.roundtrip(x, spec=spec)[0]
+    assert cuda.equal(out2, out * 0.25)
