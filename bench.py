@@ -305,6 +305,30 @@ def run_c5(args, wl, rank, world, local, torch, dist, dsp):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def bind_to_gpu_numa_node(torch, local):
+    """One process per GPU: run this process on the CPUs of the NUMA node the GPU hangs off, so that
+    the page-locked host buffers of the e2e leg (first touch) and the threads that feed the copy
+    engines sit next to the GPU's PCIe root.  Returns a description for the JSON line, or None when
+    the topology cannot be read (then nothing is changed)."""
+    try:
+        p = torch.cuda.get_device_properties(local)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"gpu": bdf, "numa_node": node, "cpus": len(cpus)}
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -335,6 +359,7 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (the product has no CPU path)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(torch, local)      # pinned host buffers land on the GPU's own NUMA node
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
@@ -558,6 +583,7 @@ def main():
         e2e = {"value": ce * Le * world * n_e2e / float(dt.item()) / 1e6, "unit": "Msamples/s",
                "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": ce * n_out_e * 4, "steps": n_e2e,
                "api": "crlot_roundtrip_host (pinned host buffers, slabbed H2D/compute/D2H pipeline; K1 + fused K2+K3 per slab)",
+               "numa_binding": numa,
                "workload": f"{ce}ch x 2^{int(np.log2(Le))} samples per rank",
                "ceiling": "PCIe: 45.8 GB/s per direction with H2D and D2H running together (tools/pcie_probe.py) = 11.4 Gsamples/s per GPU"}
         del hin, hout
