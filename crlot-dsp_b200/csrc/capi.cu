@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <new>
@@ -1033,6 +1034,7 @@ struct crlot_stream_s {
   long long w = 0, k = 0;            // host mirror of the device counters
   int last_nf = 0;
   DevArr<StreamCounters> ctr;
+  DevArr<unsigned int> done;         // block ticket of the one-launch tick
   DevArr<float> ring, acc, frames;
   DevArr<cpx> spec;
   DevArr<float> h2d, d2h;            // staging of crlot_stream_tick_host
@@ -1052,6 +1054,18 @@ cudaError_t stream_tick_launches(crlot_stream_s* s, const float* d_in, long long
                                  float* d_out, long long out_stride, long long k_base, int nf, cudaStream_t st) {
   crlot_plan_s* p = s->plan;
   const int N = p->d.nfft, H = p->d.hop;
+  // steady state of a low-latency stream (one new frame per stream): the whole tick in one launch
+  static const bool no_fused_tick = getenv("CRLOT_STREAM_NO_FUSED_TICK") != nullptr;   // A/B timing only
+  if (nf == 1 && !no_fused_tick &&
+      stream_tick1_supported(N, H, chunk_len, static_cast<long long>(p->ring_len), out_stride, d_out)) {
+    StreamTick1Params t{};
+    t.ctr = s->ctr.p; t.done = s->done.p; t.chunk = d_in; t.chunk_stride = in_stride; t.w0 = w0; t.chunk_len = chunk_len;
+    t.ring = s->ring.p; t.rcap = s->rcap; t.n_streams = s->S; t.nfft = N; t.hop = H; t.spec = s->spec.p;
+    t.window = p->win_a.p; t.syn_window = p->syn_active ? p->win_s.p : nullptr; t.tw1 = p->tw1.p; t.scrub = p->d.scrub;
+    t.gain = p->d.gain; t.eps = p->d.eps; t.norm = p->env.p; t.ring_len = static_cast<long long>(p->ring_len);
+    t.acc = s->acc.p; t.out = d_out; t.out_stride = out_stride; t.k_base = k_base;
+    return launch_stream_tick1(t, st);
+  }
   cudaError_t e = launch_stream_ingest(s->ctr.p, d_in, in_stride, chunk_len, s->ring.p, s->rcap, s->S, w0, st);
   if (e != cudaSuccess) return e;
   if (nf > 0) {
@@ -1110,6 +1124,8 @@ int crlot_stream_create(crlot_plan_t plan, int n_streams, int max_chunk, crlot_s
     return fail(CRLOT_ERR_UNSUPPORTED, "max_chunk too large for the OLA ring (more than 20 hops per tick)");
   DeviceGuard g(plan->d.device);
   CU(s->ctr.alloc(1));
+  CU(s->done.alloc(1));
+  CU(cudaMemset(s->done.p, 0, sizeof(unsigned int)));
   CU(s->ring.alloc(static_cast<size_t>(n_streams) * rc));
   CU(s->acc.alloc(static_cast<size_t>(n_streams) * plan->ring_len));
   CU(s->spec.alloc(static_cast<size_t>(n_streams) * s->max_nf * plan->bins));
@@ -1175,11 +1191,20 @@ int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, i
   for (long long t = 0; t < n_ticks && status == CRLOT_OK; ++t) {
     const int nf = stream_nf(s, s->w + chunk_len);
     cudaError_t e = cudaSuccess;
+    // steady state (chunk == hop, one frame per stream per tick from here on): the tick is a single
+    // kernel whose arguments do not depend on the tick, so kBurst consecutive ticks are replayed as ONE
+    // graph of kBurst kernel nodes -- the host pays one graph launch per burst instead of per tick
+    constexpr int kBurst = 32;
+    int burst = 1;
+    if (use_graph && nf == 1 && chunk_len == s->plan->d.hop && n_ticks - t >= kBurst && !getenv("CRLOT_STREAM_NO_FUSED_TICK") &&
+        stream_tick1_supported(s->plan->d.nfft, s->plan->d.hop, chunk_len, static_cast<long long>(s->plan->ring_len), out_stride, d_out))
+      burst = kBurst;
+    const int key = burst > 1 ? -burst : nf;
     if (!use_graph) {
       e = stream_tick_launches(s, d_in, in_stride, chunk_len, w0, d_out, out_stride, k_base, nf, st);
     } else {
       cudaGraphExec_t exec = nullptr;
-      for (auto& c : cache) if (c.nf == nf) exec = c.exec;
+      for (auto& c : cache) if (c.nf == key) exec = c.exec;
       if (!exec) {
         // captured on a private stream (the caller's may be the legacy default stream, which
         // cannot capture); capturing only records the launches, the replay goes to `st`
@@ -1187,19 +1212,21 @@ int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, i
         if (!s->host_stream) e = cudaStreamCreateWithFlags(&s->host_stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaStreamBeginCapture(s->host_stream, cudaStreamCaptureModeRelaxed);
         if (e == cudaSuccess) {
-          cudaError_t e1 = stream_tick_launches(s, d_in, in_stride, chunk_len, w0, d_out, out_stride, k_base, nf,
-                                                s->host_stream);
+          cudaError_t e1 = cudaSuccess;
+          for (int b = 0; b < burst && e1 == cudaSuccess; ++b)
+            e1 = stream_tick_launches(s, d_in, in_stride, chunk_len, w0, d_out, out_stride, k_base, nf, s->host_stream);
           e = cudaStreamEndCapture(s->host_stream, &graph);
           if (e1 != cudaSuccess) e = e1;
         }
         if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
         if (graph) cudaGraphDestroy(graph);
-        if (e == cudaSuccess) cache.push_back({nf, exec});
+        if (e == cudaSuccess) cache.push_back({key, exec});
       }
       if (e == cudaSuccess) e = cudaGraphLaunch(exec, st);
     }
     if (e != cudaSuccess) { status = fail_cuda(e, "crlot_stream_run"); break; }
-    s->w += chunk_len; s->k += nf; s->last_nf = nf;
+    s->w += static_cast<long long>(burst) * chunk_len; s->k += static_cast<long long>(burst) * nf; s->last_nf = nf;
+    t += burst - 1;
   }
   if (!cache.empty()) {
     cudaStreamSynchronize(st);            // the executables must outlive their launches

@@ -185,6 +185,29 @@ struct StreamOlaParams {
 };
 cudaError_t launch_stream_ola(const StreamOlaParams& p, cudaStream_t st);
 cudaError_t launch_stream_advance(StreamCounters* ctr, int chunk_len, int nf, cudaStream_t st);
+// the whole tick in one launch when it yields exactly one frame per stream (chunk_len == hop)
+struct StreamTick1Params {
+  StreamCounters* ctr;       // read at the start, advanced by the last block to finish
+  unsigned int* done;        // zero-initialised block ticket
+  const float* chunk;        // chunk of this tick starts at chunk[s*chunk_stride + (w - w0)]
+  long long chunk_stride, w0;
+  int chunk_len;
+  float* ring;               // [n_streams][rcap] ingest rings
+  int rcap, n_streams, nfft, hop;
+  cpx* spec;                 // [n_streams][nfft/2+1]
+  const float* window;       // analysis window
+  const float* syn_window;   // synthesis window or nullptr
+  const cpx* tw1;
+  int scrub;
+  float gain, eps;
+  const float* norm;
+  long long ring_len;
+  float* acc;                // [n_streams][ring_len]
+  float* out;
+  long long out_stride, k_base;
+};
+bool stream_tick1_supported(int nfft, int hop, int chunk_len, long long ring_len, long long out_stride, const void* out);
+cudaError_t launch_stream_tick1(const StreamTick1Params& p, cudaStream_t st);
 
 int device_sm_count();
 

@@ -179,6 +179,220 @@ __global__ void stream_advance_kernel(StreamCounters* ctr, int chunk_len, int nf
   ctr->k += nf;
 }
 
+// ---- the whole tick in ONE kernel, for the steady state of a low-latency stream: exactly one new
+// frame per stream per tick (chunk_len == hop once nfft samples are in) -----------------------------
+// A warp-step owns G streams from the chunk to the output hop: ingest -> frame from the ring ->
+// window + rFFT -> spectra row (kept, crlot_stream_last_spectra) -> irFFT, 1/N, clean-up, synthesis
+// window -> accumulate into the OLA ring at k*hop -> produce(hop).  Same arithmetic in the same order
+// as the five-launch tick above (bit-identical outputs, tests/test_gpu_stream.py), but one launch
+// instead of five: the tick is launch-latency-bound, not bandwidth-bound.  Data a warp wrote and
+// reads back within the tick (ring, spectra) goes through L2 (ld.global.cg) after a __syncwarp().
+// The last block to finish advances the device counters (every block has read them by then).
+__device__ __forceinline__ cpx ldcg2(const void* p) {
+  const float2 v = __ldcg(reinterpret_cast<const float2*>(p));
+  return mk(v.x, v.y);
+}
+
+template <int NFFT, bool SCRUB, bool WIN>
+__global__ void __launch_bounds__(kSWarps * 32) stream_tick1_kernel(const StreamTick1Params p) {
+  using X = GeoX<NFFT>;
+  constexpr int C = X::C, G = X::G, A = X::A, B = X::B;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* s_win = reinterpret_cast<float*>(smem_raw);
+  float* s_wsyn = s_win + NFFT;
+  cpx* s_tw1 = reinterpret_cast<cpx*>(s_wsyn + (WIN ? NFFT : 0));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  cpx* ex = s_tw1 + C + warp * X::XCPX;
+  for (int i = threadIdx.x; i < NFFT; i += blockDim.x) {
+    s_win[i] = p.window[i];
+    if (WIN) s_wsyn[i] = p.syn_window[i];
+  }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  const SplitLane<X::M2> SLF = make_split_fwd<X>(lane);
+  const SplitLane<X::M1> SLI = make_split_inv<X>(lane);
+  const long long w = p.ctr->w, k0 = p.ctr->k;
+  __syncthreads();
+
+  const int mask = p.rcap - 1, H = p.hop, S = p.n_streams, CL = p.chunk_len;
+  const long long steps = (static_cast<long long>(S) + G - 1) / G;
+  const int lpB = mirror_lane<B>(lane), lpA = mirror_lane<A>(lane);
+  const int pos0 = static_cast<int>((k0 * H) & mask);
+  const int e0 = static_cast<int>((k0 * H) % p.ring_len);
+  const float scale = 2.0f / static_cast<float>(NFFT);
+  const float* chunk = p.chunk + (w - p.w0);
+  for (long long step = static_cast<long long>(blockIdx.x) * kSWarps + warp; step < steps;
+       step += static_cast<long long>(gridDim.x) * kSWarps) {
+    const long long s_base = step * G;
+    // 1. ingest the chunks of this step's streams
+    for (int q0 = lane; q0 < G * CL; q0 += 128) {        // four independent loads in flight per lane
+      float val[4];
+      long long dst[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int q = q0 + 32 * u;
+        const int g = q / CL, i = q - g * CL;
+        const long long s = s_base + g;
+        const bool ok = q < G * CL && s < S;
+        dst[u] = ok ? s * p.rcap + ((w + i) & mask) : -1;
+        val[u] = ok ? __ldg(chunk + s * p.chunk_stride + i) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (dst[u] >= 0) p.ring[dst[u]] = val[u];
+    }
+    __syncwarp();
+    // 2. frame k0 of every stream: window + forward real FFT
+    cpx v[32];
+#pragma unroll
+    for (int j = 0; j < X::M1; ++j) {
+      const int i1 = lane + 32 * j, g = i1 / A, a = i1 % A;
+      const long long s = s_base + g;
+      const bool ok = s < S;
+      const float* base = p.ring + (ok ? s : 0) * p.rcap;
+#pragma unroll
+      for (int b = 0; b < B; ++b) {
+        const int off = 2 * a + 2 * A * b;
+        cpx x = mk(0.f, 0.f);
+        if (ok) x = ldcg2(base + ((pos0 + off) & mask));
+        cpx pw = mul2(x, *reinterpret_cast<const cpx*>(s_win + off));
+        if (SCRUB) pw = mk(scrub(pw.x), scrub(pw.y));
+        v[j * B + b] = pw;
+      }
+    }
+    pass1<X, false>(v);
+    twiddle1<X, false>(v, lane, s_tw1);
+    __syncwarp();
+    xchg_write<X>(v, lane, ex);
+    __syncwarp();
+    xchg_read<X>(v, lane, ex);
+    pass2<X, false>(v);
+    {
+      cpx nyq[X::M2], mid[X::M2];
+      auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lpB), __shfl_sync(0xffffffffu, v[r].y, lpB)); };
+      fwd_split_pairs<X>(v, lane, SLF, mirror, nyq, mid);
+      fwd_split_finish<X>(v, lane, mirror, mid);
+#pragma unroll
+      for (int j = 0; j < X::M2; ++j) {
+        const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
+        const long long s = s_base + g;
+        if (s < S) {
+          cpx* row = p.spec + s * (C + 1);
+#pragma unroll
+          for (int oa = 0; oa < A; ++oa) row[ob + B * oa] = v[j * A + oa];
+          if (ob == 0) row[C] = nyq[j];
+        }
+      }
+    }
+    __syncwarp();
+    // 3. inverse real FFT of the same rows (pass-1 view), 1/N, clean-up, synthesis window
+    cpx nyqi[X::M1];
+#pragma unroll
+    for (int j = 0; j < X::M1; ++j) {
+      const int i1 = lane + 32 * j, g = i1 / A, a = i1 % A;
+      const long long s = s_base + g;
+      const bool ok = s < S;
+      const cpx* row = p.spec + (ok ? s : 0) * (C + 1);
+#pragma unroll
+      for (int b = 0; b < B; ++b) v[j * B + b] = ok ? ldcg2(row + a + A * b) : mk(0.f, 0.f);
+      nyqi[j] = (ok && a == 0) ? ldcg2(row + C) : mk(0.f, 0.f);
+    }
+    {
+      cpx mid[X::M1];
+      auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lpA), __shfl_sync(0xffffffffu, v[r].y, lpA)); };
+      inv_split_pairs<X>(v, lane, SLI, mirror, nyqi, mid);
+      inv_split_finish<X>(v, lane, mirror, mid);
+    }
+    pass1<X, true>(v);
+    twiddle1<X, true>(v, lane, s_tw1);
+    __syncwarp();
+    xchg_write<X>(v, lane, ex);
+    __syncwarp();
+    xchg_read<X>(v, lane, ex);
+    pass2<X, true>(v);
+    // 4. accumulate at k0*hop, produce the first hop (normalize_and_clear), keep the rest.
+    //    All accumulator / envelope loads of a register group are issued before the first store, so a
+    //    group costs one L2 round trip instead of one per sample pair.
+#pragma unroll
+    for (int j = 0; j < X::M2; ++j) {
+      const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
+      const long long s = s_base + g;
+      if (s < S) {
+        float* accb = p.acc + s * p.ring_len;
+        float* outb = p.out + s * p.out_stride + (k0 - p.k_base) * H;
+        constexpr int AB = A < 16 ? A : 16;                 // loads batched 16 registers at a time
+#pragma unroll
+        for (int o0 = 0; o0 < A; o0 += AB) {
+          float2 a2[AB], nm[AB];
+          int rps[AB];
+#pragma unroll
+          for (int q = 0; q < AB; ++q) {
+            const int i = 2 * (ob + B * (o0 + q));
+            int rp = e0 + i;
+            if (rp >= p.ring_len) rp -= static_cast<int>(p.ring_len);
+            rps[q] = rp;
+            a2[q] = __ldcg(reinterpret_cast<const float2*>(accb + rp));
+            nm[q] = i < H ? __ldg(reinterpret_cast<const float2*>(p.norm + rp)) : make_float2(1.f, 1.f);
+          }
+#pragma unroll
+          for (int q = 0; q < AB; ++q) {
+            const int oa = o0 + q, i = 2 * (ob + B * oa);
+            float y0 = v[j * A + oa].x * scale, y1 = v[j * A + oa].y * scale;
+            if (SCRUB) {
+              y0 = scrub(y0);
+              y1 = scrub(y1);
+            }
+            if (WIN) {
+              const float2 ws = *reinterpret_cast<const float2*>(s_wsyn + i);
+              y0 = __fmul_rn(y0, ws.x);
+              y1 = __fmul_rn(y1, ws.y);
+            }
+            float2 acc2 = a2[q];
+            acc2.x = __fmaf_rn(y0, p.gain, acc2.x);
+            acc2.y = __fmaf_rn(y1, p.gain, acc2.y);
+            if (i < H) {
+              *reinterpret_cast<float2*>(outb + i) =
+                  make_float2(__fdiv_rn(acc2.x, fmaxf(nm[q].x, p.eps)), __fdiv_rn(acc2.y, fmaxf(nm[q].y, p.eps)));
+              acc2 = make_float2(0.f, 0.f);
+            }
+            a2[q] = acc2;
+          }
+#pragma unroll
+          for (int q = 0; q < AB; ++q) *reinterpret_cast<float2*>(accb + rps[q]) = a2[q];
+        }
+      }
+    }
+  }
+  // 5. the last block to finish advances the counters
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int ticket = atomicAdd(p.done, 1u);
+    if (ticket == gridDim.x - 1) {
+      p.ctr->w = w + CL;
+      p.ctr->k = k0 + 1;
+      *p.done = 0u;
+    }
+  }
+}
+
+template <int NFFT>
+cudaError_t launch_tick1_t(const StreamTick1Params& p, cudaStream_t st) {
+  using X = GeoX<NFFT>;
+  const bool win = p.syn_window != nullptr;
+  const int smem = NFFT * 4 * (win ? 2 : 1) + X::C * 8 + kSWarps * X::XCPX * 8;
+  void (*kern)(const StreamTick1Params) = nullptr;
+  if (win) kern = p.scrub ? stream_tick1_kernel<NFFT, true, true> : stream_tick1_kernel<NFFT, false, true>;
+  else     kern = p.scrub ? stream_tick1_kernel<NFFT, true, false> : stream_tick1_kernel<NFFT, false, false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  const long long steps = (static_cast<long long>(p.n_streams) + X::G - 1) / X::G;
+  long long blocks = (steps + kSWarps - 1) / kSWarps;
+  const long long cap = static_cast<long long>(device_sm_count()) * 2;
+  if (blocks > cap) blocks = cap;
+  kern<<<static_cast<unsigned>(blocks), kSWarps * 32, smem, st>>>(p);
+  return cudaGetLastError();
+}
+
 template <int NFFT>
 cudaError_t launch_fwd_t(const StreamFwdParams& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
@@ -215,6 +429,24 @@ cudaError_t launch_stream_fwd(const StreamFwdParams& p, cudaStream_t st) {
     case 512: return launch_fwd_t<512>(p, st);
     case 1024: return launch_fwd_t<1024>(p, st);
     case 2048: return launch_fwd_t<2048>(p, st);
+    default: return cudaErrorNotSupported;
+  }
+}
+
+bool stream_tick1_supported(int nfft, int hop, int chunk_len, long long ring_len, long long out_stride, const void* out) {
+  if (nfft != 256 && nfft != 512 && nfft != 1024 && nfft != 2048) return false;
+  if (chunk_len != hop || hop % 2 != 0 || hop > nfft) return false;
+  if (ring_len % 2 != 0 || ring_len >= (1ll << 30) || out_stride % 2 != 0) return false;
+  return reinterpret_cast<uintptr_t>(out) % 8 == 0;
+}
+
+cudaError_t launch_stream_tick1(const StreamTick1Params& p, cudaStream_t st) {
+  if (p.n_streams <= 0) return cudaSuccess;
+  switch (p.nfft) {
+    case 256: return launch_tick1_t<256>(p, st);
+    case 512: return launch_tick1_t<512>(p, st);
+    case 1024: return launch_tick1_t<1024>(p, st);
+    case 2048: return launch_tick1_t<2048>(p, st);
     default: return cudaErrorNotSupported;
   }
 }
