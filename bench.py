@@ -518,8 +518,21 @@ def main():
 
     # ---- the same round trip with kernels 2+3 fused (iFFT frames never materialised) --------------
     fused = None
-    if args.workload != "c4" and plan.istft_ola_supported():
+    c4_fused_ok = args.workload == "c4" and plan.istft_ola_supported(t_offset=sh.t0, frame_t0=sh.frame_t0, out=out)
+    if (args.workload != "c4" and plan.istft_ola_supported()) or c4_fused_ok:
         def fstep(record=None):
+            if args.workload == "c4":
+                if world > 1:
+                    halo_exchange()
+                e = [ev() for _ in range(3)]
+                e[0].record()
+                plan.stft(xbuf.unsqueeze(0), length=Ltot, n_frames=F, out=spec)
+                e[1].record()
+                plan.istft_ola(spec, t_offset=sh.t0, frame_t0=sh.frame_t0, n_out=n_out, out=out)
+                e[2].record()
+                if record is not None:
+                    record.append(e)
+                return
             for c0 in range(0, chans, batch):
                 xb = x[c0:c0 + batch]
                 if record is not None:

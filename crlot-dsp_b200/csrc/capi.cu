@@ -504,7 +504,7 @@ int crlot_ola_accumulate(crlot_plan_t plan, const float* d_frames, long long fra
 static void fill_k23(K23Params& k, crlot_plan_t plan, int counter_word) {
   k.nfft = plan->d.nfft; k.hop = plan->d.hop;
   k.window = plan->syn_active ? plan->win_s.p : plan->win_ones.p;
-  k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.scrub = plan->d.scrub;
+  k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
   k.gain = plan->d.gain; k.eps = plan->d.eps; k.norm = plan->env.p; k.ring_len = static_cast<long long>(plan->ring_len);
   k.den_rcp = plan->den_rcp.p;
   k.counter = plan->counter.p + counter_word; k.chunk_blocks = 0;
@@ -537,7 +537,7 @@ int crlot_istft_ola_execute(crlot_plan_t plan, const void* d_spec, long long spe
   if (reinterpret_cast<uintptr_t>(d_spec) % 8 != 0) return fail(CRLOT_ERR_UNSUPPORTED, "buffers must be 8-byte aligned");
   if (!crlot_istft_ola_supported(plan, t_offset, frame_t0, d_out, out_chan_stride))
     return fail(CRLOT_ERR_UNSUPPORTED,
-                "fused inverse+overlap-add needs nfft <= 2048, hop a multiple of 64 (16 for nfft 256, 32 for 512/1024), "
+                "fused inverse+overlap-add needs hop a multiple of 64 (16 for nfft 256, 32 for 512/1024), "
                 "even offsets/strides; use crlot_istft_execute + crlot_ola_accumulate");
   DeviceGuard g(plan->d.device);
   K23Params k{};

@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
               for (int oa = 0; oa < AE; ++oa) {
                 const cpx a = v[j * A + oa];
                 const float4 t = nm[j][oa];
-                all_ok = all_ok && div_tail_ok(a.x) && div_tail_ok(a.y);
+                all_ok = all_ok & div_tail_ok(a.x) & div_tail_ok(a.y);   // no short-circuit: one predicate chain, no branches
                 stg_stream(reinterpret_cast<cpx*>(dst + 2 * B * oa), mk(div_tail(a.x, t.x, t.y), div_tail(a.y, t.z, t.w)));
               }
               if (!all_ok) {                             // operands outside the tail's range: the full division
@@ -365,7 +365,7 @@ bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offs
   switch (nfft) {
     case 256: B2 = 16; break;
     case 512: case 1024: B2 = 32; break;
-    case 2048: B2 = 64; break;
+    case 2048: case 4096: B2 = 64; break;
     default: return false;
   }
   if (hop <= 0 || hop > nfft || hop % B2 != 0) return false;
@@ -386,7 +386,7 @@ cudaError_t launch_istft_ola(K23Params p, cudaStream_t st) {
   if (p.chunk_blocks <= 0) {
     // about 6 chunks per resident warp, between 32 and 256 blocks each: the warm-up re-computation
     // (ceil(N/hop)-1 frames per chunk) stays below a few per cent
-    const long long warps = static_cast<long long>(device_sm_count()) * kK23Warps;
+    const long long warps = static_cast<long long>(device_sm_count()) * (p.nfft == 4096 ? 8 : kK23Warps);
     long long cb = nblocks * p.channels / (6 * warps);
     if (cb < 32) cb = 32;
     if (cb > 256) cb = 256;
@@ -397,6 +397,7 @@ cudaError_t launch_istft_ola(K23Params p, cudaStream_t st) {
     case 512: return launch_k23<512>(p, st);
     case 1024: return launch_k23<1024>(p, st);
     case 2048: return launch_k23<2048>(p, st);
+    case 4096: return launch_istft_ola_4096(p, st);
     default: return cudaErrorNotSupported;
   }
 }

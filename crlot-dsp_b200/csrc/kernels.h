@@ -96,6 +96,7 @@ struct K23Params {
   const float* window;          // device synthesis window or nullptr
   const cpx* tw1;
   const cpx* sa;
+  const cpx* pre;               // nfft == 4096: transposed inverse inter-pass table (tables.h)
   int scrub;
   float gain, eps;
   const float* norm;
@@ -114,6 +115,7 @@ struct K23Params {
 bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offset, long long frame_t0,
                          long long out_chan_stride, const void* out, const void* norm);
 cudaError_t launch_istft_ola(K23Params p, cudaStream_t st);
+cudaError_t launch_istft_ola_4096(const K23Params& p, cudaStream_t st);   // k23_4096.cu, called by launch_istft_ola
 
 // in-place spectral hook as its own pass: spec[row][k] *= gain[row*row_stride + k]
 cudaError_t launch_spectral_gain(cpx* spec, long long rows, int bins, const float* gain, long long row_stride,

@@ -10,7 +10,8 @@ from conftest import bits, rel_l2
 pytestmark = pytest.mark.gpu
 TOL = 1e-5
 SHAPES = [(256, 64), (256, 16), (256, 128), (256, 256), (512, 128), (512, 32), (512, 96), (1024, 256), (1024, 512),
-          (1024, 1024), (2048, 512), (2048, 64), (2048, 1024), (2048, 192), (2048, 2048)]
+          (1024, 1024), (2048, 512), (2048, 64), (2048, 1024), (2048, 192), (2048, 2048),
+          (4096, 1024), (4096, 512), (4096, 2048), (4096, 4096), (4096, 192), (4096, 64)]
 
 
 def dev(t, a):
@@ -37,7 +38,7 @@ def test_fused_is_bit_identical_to_k2_k3(cuda, dsp, oracle, N, H):
         assert np.array_equal(bits(got.cpu().numpy()), bits(want.cpu().numpy())), (ch, F)
 
 
-@pytest.mark.parametrize("N,H", [(256, 64), (1024, 256), (2048, 512)])
+@pytest.mark.parametrize("N,H", [(256, 64), (1024, 256), (2048, 512), (4096, 1024)])
 def test_fused_offsets_and_ragged_output(cuda, dsp, oracle, N, H):
     """t_offset (envelope phase), frame_t0 < 0 (halo frames whose head is cut), frame_t0 > 0 (output
     begins before the first frame), n_out shorter / longer than the covered range, odd n_out."""

@@ -278,7 +278,7 @@ def test_k1_cleanup_inside_a_stream(cuda, dsp, oracle, N, H):
     assert not ref[150].any() and not S[150].any()
 
 
-@pytest.mark.parametrize("N,H,fused_ok", [(2048, 512, True), (4096, 1024, False)])
+@pytest.mark.parametrize("N,H,fused_ok", [(2048, 512, True), (4096, 1024, True)])
 def test_full_size_2p30_properties(cuda, dsp, oracle, N, H, fused_ok):
     """BASELINE configs[1] (c2) and one c4 shard at their FULL size (2^30 samples, 43 GB of device
     arrays): size-independent properties and slice oracles at ring-aligned offsets spread over the

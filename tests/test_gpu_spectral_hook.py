@@ -63,7 +63,7 @@ def test_hook_in_k2_equals_separate_pass(cuda, dsp, oracle, N, H, mask):
         assert np.array_equal(bits(ident.cpu().numpy()), bits(plain.cpu().numpy()))
 
 
-@pytest.mark.parametrize("N,H", [(256, 64), (1024, 256), (2048, 512)])
+@pytest.mark.parametrize("N,H", [(256, 64), (1024, 256), (2048, 512), (4096, 1024)])
 @pytest.mark.parametrize("mask", [False, True])
 def test_hook_in_fused_k23_equals_separate_pass(cuda, dsp, oracle, N, H, mask):
     rng = np.random.default_rng(3 * N + int(mask))
