@@ -27,23 +27,43 @@ __global__ void __launch_bounds__(kK3Threads) ola_gather_kernel(const K3Params p
   float* __restrict__ out = p.out + static_cast<long long>(c) * p.out_chan_stride;
   const long long N = p.nfft, H = p.hop, F = p.frames_per_chan;
   const long long ngroups = (p.n_out + VEC - 1) / VEC;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long grp = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; grp < ngroups; grp += stride) {
-    const long long j = grp * VEC;
-    const long long u = j - p.frame_t0;          // offset from the start of local frame 0
+  const long long tiles = (ngroups + kK3Threads - 1) / kK3Threads;
+  const unsigned int Hu = static_cast<unsigned int>(p.hop), Nu = static_cast<unsigned int>(p.nfft);
+  // A block walks tiles of 256 groups.  The 64-bit divisions (frame index of the tile's first sample,
+  // envelope phase) are done once per tile on block-uniform values; everything per thread is 32-bit
+  // arithmetic relative to the tile (the kernel is a pure stream: the index arithmetic is its only
+  // instruction cost).
+  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const long long j0 = tile * kK3Threads * VEC;          // first output sample of the tile
+    const long long u0 = j0 - p.frame_t0;                  // its offset from the start of local frame 0
+    // frame that contains u0 (floor division, also for negative u0) and the offset inside it
+    long long kq = u0 >= 0 ? u0 / H : -((-u0 + H - 1) / H);
+    const unsigned int rem0 = static_cast<unsigned int>(u0 - kq * H);            // [0, H)
+    long long eb = (p.t_offset + j0) % p.ring_len;
+    const unsigned int dj = threadIdx.x * VEC;             // sample offset inside the tile
+    const long long j = j0 + dj;
+    if (j >= p.n_out) continue;
+    const unsigned int ru = rem0 + dj;                     // u = kq*H + ru
+    const long long k_top = kq + ru / Hu;                  // frame that contains u: floor(u / H)
+    const unsigned int i_top = ru % Hu;                    // u - k_top*H, in [0, H)
     float acc[VEC];
 #pragma unroll
     for (int e = 0; e < VEC; ++e) acc[e] = 0.0f;
-    if (u >= 0) {
-      long long k_hi = u / H;
-      long long k_lo = (u - N + H) < 0 ? 0 : (u - N + H) / H;   // ceil((u-N+1)/H) for aligned u
-      if (VEC == 1) k_lo = (u - N + 1) <= 0 ? 0 : (u - N + 1 + H - 1) / H;
-      if (k_hi > F - 1) k_hi = F - 1;
+    // contributing frames k = k_top - m, m = 0 .. (N - 1 - i_top)/H (VEC == 4: N, H, i_top multiples
+    // of 4, so the whole group shares them), clipped to [0, F); summed in ASCENDING k
+    unsigned int m_max = (Nu - (VEC == 4 ? 4u : 1u) - i_top) / Hu;
+    long long k_lo = k_top - m_max, k_hi = k_top;
+    if (k_lo < 0) k_lo = 0;
+    if (k_hi > F - 1) k_hi = F - 1;
+    if (k_hi >= k_lo) {
+      const float* fp = frames + k_lo * N + (static_cast<long long>(k_top - k_lo) * H + i_top);
+      unsigned int i = static_cast<unsigned int>(k_top - k_lo) * Hu + i_top;      // offset inside frame k_lo
+      const int cnt = static_cast<int>(k_hi - k_lo + 1);
+      const long long step = N - H;                        // next frame, same output sample
 #pragma unroll 4
-      for (long long k = k_lo; k <= k_hi; ++k) {
-        const long long i = u - k * H;
+      for (int q = 0; q < cnt; ++q) {
         if (VEC == 4) {
-          const float4 y = ldg_stream4(reinterpret_cast<const float4*>(frames + k * N + i));
+          const float4 y = ldg_stream4(reinterpret_cast<const float4*>(fp));
           float4 f = y;
           if (WIN) {
             const float4 w = __ldg(reinterpret_cast<const float4*>(p.window + i));
@@ -55,15 +75,18 @@ __global__ void __launch_bounds__(kK3Threads) ola_gather_kernel(const K3Params p
           acc[2] = __fmaf_rn(f.z, p.gain, acc[2]);
           acc[3] = __fmaf_rn(f.w, p.gain, acc[3]);
         } else {
-          float f = __ldg(frames + k * N + i);
+          float f = __ldg(fp);
           if (WIN) f = __fmul_rn(f, __ldg(p.window + i));
           acc[0] = __fmaf_rn(f, p.gain, acc[0]);
         }
+        fp += step;
+        i -= Hu;
       }
     }
-    const long long e0 = (p.t_offset + j) % p.ring_len;
+    eb += dj;
+    while (eb >= p.ring_len) eb -= p.ring_len;
     if (VEC == 4) {
-      const float4 nm = __ldg(reinterpret_cast<const float4*>(p.norm + e0));
+      const float4 nm = __ldg(reinterpret_cast<const float4*>(p.norm + eb));
       float4 o;
       o.x = __fdiv_rn(acc[0], fmaxf(nm.x, p.eps));
       o.y = __fdiv_rn(acc[1], fmaxf(nm.y, p.eps));
@@ -76,7 +99,7 @@ __global__ void __launch_bounds__(kK3Threads) ola_gather_kernel(const K3Params p
         for (int e = 0; e < 4 && j + e < p.n_out; ++e) out[j + e] = t[e];
       }
     } else {
-      out[j] = __fdiv_rn(acc[0], fmaxf(__ldg(p.norm + e0), p.eps));
+      out[j] = __fdiv_rn(acc[0], fmaxf(__ldg(p.norm + eb), p.eps));
     }
   }
 }
@@ -93,6 +116,7 @@ cudaError_t launch_ola_gather(const K3Params& p, cudaStream_t st) {
                    (reinterpret_cast<uintptr_t>(p.norm) % 16 == 0) &&
                    (!win || reinterpret_cast<uintptr_t>(p.window) % 16 == 0);
   const long long groups = vec ? (p.n_out + 3) / 4 : p.n_out;
+  if (p.t_offset < 0) return cudaErrorInvalidValue;
   long long blocks = (groups + kK3Threads - 1) / kK3Threads;
   const long long cap = static_cast<long long>(device_sm_count()) * 16;
   if (blocks > cap) blocks = cap;
