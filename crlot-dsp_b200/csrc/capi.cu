@@ -1043,6 +1043,13 @@ struct crlot_stream_s {
 
 namespace {
 
+// CRLOT_STREAM_NO_FUSED_TICK=1 keeps every tick on the five-launch path (A/B timing and the
+// bit-identity test of the one-kernel tick); read once
+bool stream_fused_tick_enabled() {
+  static const bool on = getenv("CRLOT_STREAM_NO_FUSED_TICK") == nullptr;
+  return on;
+}
+
 int stream_nf(const crlot_stream_s* s, long long w_new) {
   const int N = s->plan->d.nfft, H = s->plan->d.hop;
   const long long total = w_new >= N ? (w_new - N) / H + 1 : 0;   // Framer DROP count, framer.cc:106-115
@@ -1055,8 +1062,7 @@ cudaError_t stream_tick_launches(crlot_stream_s* s, const float* d_in, long long
   crlot_plan_s* p = s->plan;
   const int N = p->d.nfft, H = p->d.hop;
   // steady state of a low-latency stream (one new frame per stream): the whole tick in one launch
-  static const bool no_fused_tick = getenv("CRLOT_STREAM_NO_FUSED_TICK") != nullptr;   // A/B timing only
-  if (nf == 1 && !no_fused_tick &&
+  if (nf == 1 && stream_fused_tick_enabled() &&
       stream_tick1_supported(N, H, chunk_len, static_cast<long long>(p->ring_len), out_stride, d_out)) {
     StreamTick1Params t{};
     t.ctr = s->ctr.p; t.done = s->done.p; t.chunk = d_in; t.chunk_stride = in_stride; t.w0 = w0; t.chunk_len = chunk_len;
@@ -1196,7 +1202,7 @@ int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, i
     // graph of kBurst kernel nodes -- the host pays one graph launch per burst instead of per tick
     constexpr int kBurst = 32;
     int burst = 1;
-    if (use_graph && nf == 1 && chunk_len == s->plan->d.hop && n_ticks - t >= kBurst && !getenv("CRLOT_STREAM_NO_FUSED_TICK") &&
+    if (use_graph && nf == 1 && chunk_len == s->plan->d.hop && n_ticks - t >= kBurst && stream_fused_tick_enabled() &&
         stream_tick1_supported(s->plan->d.nfft, s->plan->d.hop, chunk_len, static_cast<long long>(s->plan->ring_len), out_stride, d_out))
       burst = kBurst;
     const int key = burst > 1 ? -burst : nf;
