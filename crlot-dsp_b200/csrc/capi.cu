@@ -151,6 +151,7 @@ struct crlot_plan_s {
   DevArr<cpx> tw1, sa, pre;
   DevArr<unsigned int> counter;
   DevArr<float2> den_rcp;      // {max(env, eps), refined reciprocal}: division table of the fused kernel 2+3
+  bool generic = false;        // any-size kernels (k_generic.cu): nfft outside the register-FFT set, or hop % 4 != 0
   int k1_scrub = 0;            // kernel-1 clean-up mode (kernels.h)
   bool k23_win_ok = true;      // synthesis window can be pre-scaled by 2/N exactly (fused kernel 2+3)
   const float* sgain = nullptr;   // spectral-domain hook (caller-owned device table), see crlot_stft_plan_set_spectral_gain
@@ -280,13 +281,19 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
   if (desc->hop <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Hop size must be greater than 0");
   if (!(desc->eps > 0.0f)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Invalid OLA configuration");
   if (desc->boundary_mode != CRLOT_ZERO_PAD && desc->boundary_mode != CRLOT_DROP) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad boundary mode");
-  if (!supported_nfft(desc->nfft)) return fail(CRLOT_ERR_UNSUPPORTED, "nfft must be 256, 512, 1024, 2048 or 4096 on the GPU path");
-  if (desc->hop % 4 != 0 || desc->hop > desc->nfft) return fail(CRLOT_ERR_UNSUPPORTED, "hop must be a multiple of 4 and <= nfft on the GPU path");
+  if (desc->nfft % 2 != 0) return fail(CRLOT_ERR_RUNTIME, "FFT size must be even for real FFT");
+  // register-FFT kernels: nfft in {256..4096} and hop % 4 == 0; everything else the reference's plan accepts
+  // runs on the any-size kernels (k_generic.cu), up to 16384 points
+  const bool generic = !supported_nfft(desc->nfft) || desc->hop % 4 != 0;
+  if (generic && !generic_len_supported(desc->nfft / 2))
+    return fail(CRLOT_ERR_UNSUPPORTED, "nfft must be an even number <= 16384 on the GPU path");
+  if (desc->hop > desc->nfft) return fail(CRLOT_ERR_UNSUPPORTED, "hop must be <= nfft on the GPU path");
   DeviceGuard g(desc->device);
   if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
   std::unique_ptr<crlot_plan_s> p(new (std::nothrow) crlot_plan_s);
   if (!p) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
   p->d = *desc;
+  p->generic = generic;
   p->bins = desc->nfft / 2 + 1;
   const int N = desc->nfft;
   // analysis window (ones = none)
@@ -353,7 +360,7 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
       CU(cudaStreamSynchronize(nullptr));
     }
   }
-  const FftTables T = make_fft_tables(N);
+  const FftTables T = generic ? make_generic_tables(N) : make_fft_tables(N);
   CU(upload_cpx(p->tw1, T.tw1));
   CU(upload_cpx(p->sa, T.sa));
   if (!T.pre.empty()) CU(upload_cpx(p->pre, T.pre));
@@ -407,7 +414,8 @@ int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_
                        long long n_frames, void* d_spec, void* stream) {
   if (!plan || !d_signal || !d_spec) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
   if (channels <= 0 || n_frames < 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
-  if (chan_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_signal) % 16 != 0 || reinterpret_cast<uintptr_t>(d_spec) % 8 != 0)
+  if (reinterpret_cast<uintptr_t>(d_spec) % 8 != 0) return fail(CRLOT_ERR_UNSUPPORTED, "buffers must be 8-byte aligned");
+  if (!plan->generic && (chan_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_signal) % 16 != 0))
     return fail(CRLOT_ERR_UNSUPPORTED, "signal must be 16-byte aligned with chan_stride a multiple of 4 floats");
   DeviceGuard g(plan->d.device);
   K1Params k{};
@@ -416,6 +424,7 @@ int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_
   k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
   k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p;
   k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
+  k.generic = plan->generic;
   CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
@@ -456,7 +465,8 @@ int crlot_stft_execute_framequeue(crlot_plan_t plan, const float* d_signal, long
   if (len >= (1ll << 31)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "length out of range (the reference indexes with int)");
   if (n_frames > crlot_framequeue_count(len, plan->d.nfft, plan->d.hop, center))
     return fail(CRLOT_ERR_INVALID_ARGUMENT, "n_frames exceeds crlot_framequeue_count");
-  if (chan_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_signal) % 16 != 0 || reinterpret_cast<uintptr_t>(d_spec) % 8 != 0)
+  if (reinterpret_cast<uintptr_t>(d_spec) % 8 != 0) return fail(CRLOT_ERR_UNSUPPORTED, "buffers must be 8-byte aligned");
+  if (!plan->generic && (chan_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_signal) % 16 != 0))
     return fail(CRLOT_ERR_UNSUPPORTED, "signal must be 16-byte aligned with chan_stride a multiple of 4 floats");
   DeviceGuard g(plan->d.device);
   K1Params k{};
@@ -466,6 +476,7 @@ int crlot_stft_execute_framequeue(crlot_plan_t plan, const float* d_signal, long
   k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
   k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p;
   k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
+  k.generic = plan->generic;
   CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
@@ -480,7 +491,7 @@ int crlot_istft_execute(crlot_plan_t plan, const void* d_spec, long long rows, f
   k.spec = static_cast<const cpx*>(d_spec); k.rows = rows; k.nfft = plan->d.nfft; k.frames = d_frames;
   k.window = (fuse_win && plan->syn_active) ? plan->win_s.p : nullptr;
   k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
-  k.sgain = plan->sgain; k.sgain_row_stride = plan->sgain_row_stride;
+  k.sgain = plan->sgain; k.sgain_row_stride = plan->sgain_row_stride; k.generic = plan->generic;
   CU(launch_istft_inv(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
@@ -524,7 +535,7 @@ int crlot_selftest_division(crlot_plan_t plan, unsigned long long n, unsigned lo
 
 int crlot_istft_ola_supported(crlot_plan_t plan, long long t_offset, long long frame_t0, const float* d_out,
                               long long out_chan_stride) {
-  if (!plan || !plan->k23_win_ok) return 0;
+  if (!plan || !plan->k23_win_ok || plan->generic) return 0;
   return istft_ola_supported(plan->d.nfft, plan->d.hop, static_cast<long long>(plan->ring_len), t_offset, frame_t0,
                              out_chan_stride, d_out, plan->env.p) ? 1 : 0;
 }
@@ -590,7 +601,7 @@ static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long c
   const long long ist = ((slab_frames - 1) * H + N + 3) / 4 * 4;      // planar strides inside the workspace
   const long long ost = (slab_hops * H + N + 3) / 4 * 4;
   // slab offsets are multiples of the hop, so one eligibility test covers every slab
-  const bool fused = plan->k23_win_ok && istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, ost, nullptr, plan->env.p);
+  const bool fused = !plan->generic && plan->k23_win_ok && istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, ost, nullptr, plan->env.p);
   if (plan->slot_frames < slab_frames || plan->slot_group < G || (aos && !plan->slot_aos)) {
     for (auto& s : plan->slot) {
       if (!s.stream) CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
@@ -625,6 +636,7 @@ static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long c
       k1.sig = s.in.p; k1.chan_stride = G > 1 ? ist : 0; k1.len = s1 - s0; k1.channels = G; k1.frames = nf; k1.nfft = N; k1.hop = H;
       k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p;
       k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2;
+      k1.generic = plan->generic;
       CU(launch_stft_fwd(k1, s.stream));
       const long long row0 = static_cast<long long>(c) * F + k_lo;     // first spectrum row of the slab (planar mode)
       if (fused) {
@@ -640,7 +652,7 @@ static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long c
         k2.window = plan->syn_active ? plan->win_s.p : nullptr; k2.tw1 = plan->tw1.p; k2.sa = plan->sa.p; k2.pre = plan->pre.p;
         k2.scrub = plan->d.scrub;
         k2.sgain = plan->sgain ? plan->sgain + (G > 1 ? 0 : row0) * plan->sgain_row_stride : nullptr;
-        k2.sgain_row_stride = plan->sgain_row_stride;
+        k2.sgain_row_stride = plan->sgain_row_stride; k2.generic = plan->generic;
         CU(launch_istft_inv(k2, s.stream));
         K3Params k3{};
         k3.frames = s.frames.p; k3.frames_chan_rows = nf; k3.frames_per_chan = nf; k3.channels = G; k3.nfft = N; k3.hop = H;
@@ -704,7 +716,7 @@ int crlot_synth_uniform(float* d_out, long long chan_stride, int channels, long 
 // ---------------------------------------------------------------------------------------------
 struct crlot_fft_s {
   int nfft = 0, batch = 0, si = 0, so = 0, device = 0;
-  bool complex_domain = false;
+  bool complex_domain = false, generic = false;
   DevArr<cpx> ctw, d_cin, d_cout;   // complex-domain plan: table of the 2n-point geometry, batch buffers
   crlot_plan_t plan = nullptr;
   DevArr<float> d_time;
@@ -721,8 +733,10 @@ int crlot_fft_plan_create(int nfft, int in_place, int batch, int stride_in, int 
   if (batch < 1 || batch > 16) return fail(CRLOT_ERR_RUNTIME, "Batch size must be between 1 and 16");
   if (stride_in < 1 || stride_out < 1) return fail(CRLOT_ERR_RUNTIME, "Stride must be at least 1");
   if (in_place) return fail(CRLOT_ERR_RUNTIME, "In-place FFT is not yet supported");
+  if (nfft <= 0) return fail(CRLOT_ERR_RUNTIME, "FFT size must be greater than 0");
   if (nfft % 2 != 0) return fail(CRLOT_ERR_RUNTIME, "FFT size must be even for real FFT");
-  if (!supported_nfft(nfft)) return fail(CRLOT_ERR_UNSUPPORTED, "nfft must be 256, 512, 1024, 2048 or 4096 on the GPU path");
+  if (!supported_nfft(nfft) && !generic_len_supported(nfft / 2))
+    return fail(CRLOT_ERR_UNSUPPORTED, "real nfft must be <= 16384 on the GPU path");
   std::unique_ptr<crlot_fft_s> f(new (std::nothrow) crlot_fft_s);
   if (!f) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
   f->nfft = nfft; f->batch = batch; f->si = stride_in; f->so = stride_out; f->device = device;
@@ -753,14 +767,16 @@ int crlot_fft_plan_create_complex(int nfft, int in_place, int batch, int stride_
   if (batch < 1 || batch > 16) return fail(CRLOT_ERR_RUNTIME, "Batch size must be between 1 and 16");
   if (stride_in < 1 || stride_out < 1) return fail(CRLOT_ERR_RUNTIME, "Stride must be at least 1");
   if (in_place) return fail(CRLOT_ERR_RUNTIME, "In-place FFT is not yet supported");
-  if (nfft != 128 && nfft != 256 && nfft != 512 && nfft != 1024 && nfft != 2048)
-    return fail(CRLOT_ERR_UNSUPPORTED, "complex nfft must be 128, 256, 512, 1024 or 2048 on the GPU path");
+  if (nfft <= 0) return fail(CRLOT_ERR_RUNTIME, "FFT size must be greater than 0");
+  const bool generic = nfft != 128 && nfft != 256 && nfft != 512 && nfft != 1024 && nfft != 2048;
+  if (generic && !generic_len_supported(nfft))
+    return fail(CRLOT_ERR_UNSUPPORTED, "complex nfft must be <= 8192 on the GPU path");
   std::unique_ptr<crlot_fft_s> f(new (std::nothrow) crlot_fft_s);
   if (!f) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
-  f->nfft = nfft; f->batch = batch; f->si = stride_in; f->so = stride_out; f->device = device; f->complex_domain = true;
+  f->nfft = nfft; f->batch = batch; f->si = stride_in; f->so = stride_out; f->device = device; f->complex_domain = true; f->generic = generic;
   DeviceGuard g(device);
   if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
-  const FftTables T = make_fft_tables(2 * nfft);
+  const FftTables T = generic ? make_generic_tables(2 * nfft) : make_fft_tables(2 * nfft);
   cudaError_t e = upload_cpx(f->ctw, T.tw1);
   if (e == cudaSuccess) e = f->d_cin.alloc(static_cast<size_t>(batch) * nfft);
   if (e == cudaSuccess) e = f->d_cout.alloc(static_cast<size_t>(batch) * nfft);
@@ -780,7 +796,7 @@ int crlot_fft_complex_device(crlot_fft_t f, const void* d_in, void* d_out, long 
   DeviceGuard g(f->device);
   CfftParams k{};
   k.in = static_cast<const cpx*>(d_in); k.out = static_cast<cpx*>(d_out); k.rows = rows; k.n = f->nfft;
-  k.inverse = inverse ? 1 : 0; k.tw1 = f->ctw.p;
+  k.inverse = inverse ? 1 : 0; k.tw1 = f->ctw.p; k.generic = f->generic ? 1 : 0;
   CU(launch_cfft(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
 }
@@ -1116,7 +1132,8 @@ int crlot_stream_create(crlot_plan_t plan, int n_streams, int max_chunk, crlot_s
   if (n_streams <= 0 || max_chunk <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "n_streams and max_chunk must be positive");
   if (plan->d.boundary_mode != CRLOT_DROP)
     return fail(CRLOT_ERR_UNSUPPORTED, "streaming needs BoundaryMode::DROP (chunked ZERO_PAD emits premature frames)");
-  if (plan->d.nfft > 2048) return fail(CRLOT_ERR_UNSUPPORTED, "streaming supports nfft <= 2048");
+  if (plan->generic || plan->d.nfft > 2048)
+    return fail(CRLOT_ERR_UNSUPPORTED, "streaming supports nfft in {256, 512, 1024, 2048} with hop % 4 == 0");
   const int N = plan->d.nfft, H = plan->d.hop;
   std::unique_ptr<crlot_stream_s> s(new (std::nothrow) crlot_stream_s);
   if (!s) return fail(CRLOT_ERR_ALLOC, "host allocation failed");

@@ -380,6 +380,7 @@ cudaError_t launch_k1(const K1Params& p, cudaStream_t st) {
 
 cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st) {
   if (p.frames <= 0 || p.channels <= 0) return cudaSuccess;
+  if (p.generic) return launch_stft_fwd_generic(p, st);
   switch (p.nfft) {
     case 256: return launch_k1<256>(p, st);
     case 512: return launch_k1<512>(p, st);

@@ -271,6 +271,7 @@ cudaError_t launch_k2(const K2Params& p, cudaStream_t st) {
 
 cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st) {
   if (p.rows <= 0) return cudaSuccess;
+  if (p.generic) return launch_istft_inv_generic(p, st);
   switch (p.nfft) {
     case 256: return launch_k2<256>(p, st);
     case 512: return launch_k2<512>(p, st);

@@ -124,6 +124,7 @@ cudaError_t launch_cfft_n(const CfftParams& p, cudaStream_t st) {
 
 cudaError_t launch_cfft(const CfftParams& p, cudaStream_t st) {
   if (p.rows <= 0) return cudaSuccess;
+  if (p.generic) return launch_cfft_generic(p, st);
   switch (p.n) {
     case 128: return launch_cfft_n<256>(p, st);
     case 256: return launch_cfft_n<512>(p, st);

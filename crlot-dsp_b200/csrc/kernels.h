@@ -30,8 +30,11 @@ struct K1Params {
   int chunk_steps;           // steps (of G frames) per scheduled chunk
   int scrub;                 // 0 none, 1 reference clean-up on every windowed sample, 2 same via screening
   unsigned int tiny2;        // scrub == 2: 2*bits(tiny_thr) - 2 (see k1_stft.cu)
+  int generic;               // 1: any-size kernel (k_generic.cu); tw1/sa are then make_generic_tables' (tables.h)
 };
 cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st);
+cudaError_t launch_stft_fwd_generic(const K1Params& p, cudaStream_t st);   // k_generic.cu, called by launch_stft_fwd
+bool generic_len_supported(int complex_len);
 
 // ---- kernel 2: inverse real FFT * (1/nfft) + clean-up (+ synthesis window) --------------------
 struct K2Params {
@@ -48,8 +51,10 @@ struct K2Params {
   // rounding per component) as the row is loaded; nullptr = none; stride 0 = the same gains for every row
   const float* sgain;
   long long sgain_row_stride;
+  int generic;               // as in K1Params
 };
 cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st);
+cudaError_t launch_istft_inv_generic(const K2Params& p, cudaStream_t st);
 
 // ---- complex-domain plan: rows of n complex points, n in {128, 256, 512, 1024, 2048} --------------
 struct CfftParams {
@@ -59,8 +64,10 @@ struct CfftParams {
   int n;
   int inverse;               // 1: conjugate kernel, times 1/n, clean-up rule on both components
   const cpx* tw1;            // inter-pass table of the 2n-point real geometry (tables.h)
+  int generic;               // 1: any n (k_generic.cu); tw1 is then exp(-2 pi i k / n), k < n
 };
 cudaError_t launch_cfft(const CfftParams& p, cudaStream_t st);
+cudaError_t launch_cfft_generic(const CfftParams& p, cudaStream_t st);
 
 // ---- kernel 3: gather overlap-add + envelope normalisation ------------------------------------
 // out[c][j] = ( sum_k' fma( f(k',u) , gain, acc ) ) / max(norm[(t_offset + j) % ring_len], eps),

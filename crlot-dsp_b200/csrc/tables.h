@@ -54,4 +54,27 @@ inline FftTables make_fft_tables(int nfft) {
   return t;
 }
 
+// Tables of the any-size kernels (k_generic.cu) for a real transform of nfft points (complex length
+// M = nfft/2): tw1[k] = exp(-2 pi i k / M), k < M, and sa[k] = exp(-i pi (k/M + 1/2)), k < M -- the
+// split factor kiss_fftr calls super_twiddles[k-1] (reference: third_party/kissfft/kiss_fftr.c:49-56).
+// For a complex plan of n points pass nfft = 2n and use tw1 only.
+inline FftTables make_generic_tables(int nfft) {
+  const double pi = 3.141592653589793238462643383279502884;
+  FftTables t;
+  t.nfft = nfft;
+  t.C = nfft / 2;
+  const int M = t.C > 0 ? t.C : 1;
+  t.tw1.resize(2 * (size_t)M);
+  t.sa.resize(2 * (size_t)M);
+  for (int k = 0; k < M; ++k) {
+    const double ph = -2.0 * pi * (double)k / (double)M;
+    t.tw1[2 * k] = (float)std::cos(ph);
+    t.tw1[2 * k + 1] = (float)std::sin(ph);
+    const double ps = -pi * ((double)k / (double)M + 0.5);
+    t.sa[2 * k] = (float)std::cos(ps);
+    t.sa[2 * k + 1] = (float)std::sin(ps);
+  }
+  return t;
+}
+
 }  // namespace crlot

@@ -34,6 +34,12 @@ static int g_fail = 0, g_checks = 0;
     if (!ok__) { ++g_fail; std::printf("FAIL %s:%d  %s should throw %s\n", __FILE__, __LINE__, #expr, #extype); } \
   } while (0)
 
+#define CHECK_NOTHROW(expr)                                 \
+  do {                                                      \
+    ++g_checks;                                             \
+    try { expr; } catch (...) { ++g_fail; std::printf("FAIL %s:%d  %s threw\n", __FILE__, __LINE__, #expr); } \
+  } while (0)
+
 static std::string g_out;
 static void dump(const char* name, const float* p, size_t n) {
   const std::string path = g_out + "/" + name + ".f32";
@@ -238,6 +244,48 @@ static void test_fft() {
     }
     CHECK(same);
     CHECK_THROWS(plan->forward(x.data(), X.data(), 5), std::runtime_error);
+  }
+  {  // StrideLayoutVerification :450-520 -- nfft 128 (an any-size plan here), batch 3, strides 2 / 2
+    const int n = 128, nb = 65, B = 3;
+    auto plan = MakeFftPlan({FftDomain::Real, n, false, B, 2, 2});
+    std::vector<float> x(static_cast<size_t>(B) * n * 2, 0.0f);
+    for (int b = 0; b < B; ++b)
+      for (int i = 0; i < n; ++i) x[(static_cast<size_t>(b) * n + i) * 2] = std::sin(2.0f * (float)M_PI * (b + 1) * i / n);
+    std::vector<std::complex<float>> X(static_cast<size_t>(B) * nb * 2);
+    plan->forward(x.data(), X.data(), B);
+    for (int b = 0; b < B; ++b) {
+      int peak = 0;
+      float best = 0.0f;
+      for (int k = 0; k < nb; ++k) {
+        const float m = std::abs(X[(static_cast<size_t>(b) * nb + k) * 2]);
+        if (m > best) { best = m; peak = k; }
+      }
+      CHECK(peak == b + 1);
+    }
+  }
+  {  // InvalidConfiguration :229-237 -- complex plans of even and odd size are accepted; mixed-radix sizes work
+    CHECK_NOTHROW(MakeFftPlan({FftDomain::Complex, 512, false, 1, 1, 1}));
+    CHECK_NOTHROW(MakeFftPlan({FftDomain::Complex, 513, false, 1, 1, 1}));
+    for (int n : {513, 480, 1000}) {
+      auto plan = MakeFftPlan({FftDomain::Complex, n, false, 1, 1, 1});
+      std::vector<std::complex<float>> x(n), X(n), y(n);
+      std::vector<float> r = noise(2 * n, 900 + n);
+      for (int i = 0; i < n; ++i) x[i] = {r[2 * i], r[2 * i + 1]};
+      plan->forward_complex(x.data(), X.data());
+      plan->inverse_complex(X.data(), y.data());
+      double e = 0;
+      for (int i = 0; i < n; ++i) e += std::norm(y[i] - x[i]);
+      CHECK(std::sqrt(e / n) < 1e-5);
+    }
+    auto rp = MakeFftPlan({FftDomain::Real, 480, false, 1, 1, 1});            // 30 ms at 16 kHz
+    std::vector<float> x = noise(480, 77), y(480);
+    std::vector<std::complex<float>> X(241);
+    rp->forward(x.data(), X.data());
+    rp->inverse(X.data(), y.data());
+    double e = 0;
+    for (int i = 0; i < 480; ++i) e += (double)(y[i] - x[i]) * (y[i] - x[i]);
+    CHECK(std::sqrt(e / 480) < 1e-5);
+    CHECK(X[0].imag() == 0.0f && X[240].imag() == 0.0f);
   }
 }
 

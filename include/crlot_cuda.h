@@ -76,8 +76,10 @@ long long crlot_frame_count(long long len, int frame, int hop, int boundary_mode
 typedef struct crlot_plan_s* crlot_plan_t;
 
 typedef struct crlot_stft_desc {
-  int nfft;                      /* frame size N: 256, 512, 1024, 2048 or 4096                       */
-  int hop;                       /* hop H: multiple of 4, 0 < H <= N                                  */
+  int nfft;                      /* frame size N: any even N <= 16384 (ref: kissfft_adapter.cc:36-39).  */
+                                 /*   256..4096 (powers of two) with hop % 4 == 0 run the register-FFT  */
+                                 /*   kernels; every other shape the any-size kernels (k_generic.cu)    */
+  int hop;                       /* hop H: 0 < H <= N                                                  */
   int boundary_mode;             /* CRLOT_ZERO_PAD / CRLOT_DROP (Framer boundary mode)                 */
   const float* analysis_window;  /* host, N floats, or NULL (no multiply before the FFT)              */
                                  /*   ref: bench/e2e_benchmark.cc:154-156                             */
@@ -304,7 +306,9 @@ const float* crlot_framer_device_ptr(crlot_framer_t f, long long* chan_stride, l
 /* replaces dsp::fft::MakeFftPlan / IFftPlan::{forward,inverse} for FftDomain::Real
  *   ref: dsp/fft/api/fft_api.h:16-51; dsp/fft/backends/kissfft_adapter.cc:13-63,83-168
  * Argument rules and their failures (CRLOT_ERR_RUNTIME) mirror the adapter: batch 1..16,
- * strides >= 1, in_place unsupported, even nfft.  nfft must also be one the GPU path has. */
+ * strides >= 1, in_place unsupported, even nfft.  Every even nfft <= 16384 runs on the GPU (the
+ * reference's own tests use 128 with strides 2/2, tests/fft_test.cc:450-520); larger sizes return
+ * CRLOT_ERR_UNSUPPORTED. */
 typedef struct crlot_fft_s* crlot_fft_t;
 int crlot_fft_plan_create(int nfft, int in_place, int batch, int stride_in, int stride_out, int device,
                           crlot_fft_t* out);
@@ -313,8 +317,9 @@ int crlot_fft_forward(crlot_fft_t plan, const float* h_in, float* h_out_ri, int 
 int crlot_fft_inverse(crlot_fft_t plan, const float* h_in_ri, float* h_out, int batch);
 /* Complex-domain plan: FftPlanDesc{Complex,...} + IFftPlan::forward_complex /
  * inverse_complex.  Same constructor checks and messages as the reference (batch 1..16, strides >= 1,
- * no in-place; no evenness requirement); sizes 128..2048 (powers of two) run on the GPU, any other
- * size returns CRLOT_ERR_UNSUPPORTED.  A Real plan refuses the complex calls and vice versa with the
+ * no in-place; no evenness requirement: tests/fft_test.cc:229-237 builds a 513-point plan).  Every size
+ * 1..8192 runs on the GPU: 128..2048 (powers of two) on the register-FFT core, the others on the
+ * mixed-radix any-size kernel; larger sizes return CRLOT_ERR_UNSUPPORTED.  A Real plan refuses the complex calls and vice versa with the
  * reference's messages.  Host arrays are interleaved (re,im); batch/stride addressing as in
  *   ref: dsp/fft/backends/kissfft_adapter.cc:171-246
  * crlot_fft_complex_device is the same transform over `rows` contiguous rows resident on the device. */
