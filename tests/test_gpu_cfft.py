@@ -81,8 +81,9 @@ def test_error_behaviour(cuda, dsp):
         dsp.FftPlan(256, stride_in=0, complex_domain=True)
     with pytest.raises(dsp.CrlotError, match="In-place"):
         dsp.FftPlan(256, in_place=True, complex_domain=True)
+    dsp.FftPlan(100, complex_domain=True)                          # any size <= 8192 (tests/test_gpu_generic.py)
     with pytest.raises(dsp.CrlotUnsupported):
-        dsp.FftPlan(100, complex_domain=True)
+        dsp.FftPlan(8200, complex_domain=True)
     real, cplx = dsp.FftPlan(256), dsp.FftPlan(256, batch=2, complex_domain=True)
     with pytest.raises(dsp.CrlotError, match="Complex FFT not supported for Real domain plan"):
         real.forward_complex(np.zeros(256, np.complex64))

@@ -190,7 +190,9 @@ def test_edge_cases(cuda, dsp, oracle):
     with pytest.raises(ValueError):
         dsp.Plan(1024, 256, eps=0.0)                        # OLAConfig::isValid
     with pytest.raises(dsp.CrlotError):
-        dsp.Plan(1000, 250)                                 # not a GPU-path size: error, never a CPU fallback
+        dsp.Plan(16386, 4096)                               # beyond the GPU path's sizes: error, never a CPU fallback
+    with pytest.raises(dsp.CrlotError):
+        dsp.Plan(1001, 250)                                 # odd real size (kissfft_adapter.cc:36-39)
 
 
 def test_scrub_rules(cuda, dsp, oracle, gold):
