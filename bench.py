@@ -46,6 +46,24 @@ WORKLOADS = {
 }
 SEED = 0xC0FFEE
 
+# stdout carries exactly ONE JSON line.  Libraries write to file descriptor 1 behind Python's back (NCCL prints
+# its "NCCL version ..." banner there when NCCL_DEBUG is set on the box), so fd 1 is pointed at stderr for the
+# whole run and the line goes to the saved descriptor.
+_JSON_FD = None
+
+
+def claim_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, data)
+
 
 # ------------------------------------------------------------------------------------------------
 # CPU arms (the only places bench.py touches oracle/)
@@ -109,7 +127,7 @@ def run_reference_arm(args, wl, rank, world):
         "e2e": {"value": v / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -300,7 +318,7 @@ def run_c5(args, wl, rank, world, local, torch, dist, dsp):
                        "generator": "counter hash uniform[-1,1), seed 0xC0FFEE"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": (1 if chunk == H else 5) * T * args.steps, "clocks": clk,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -341,6 +359,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     wl = dict(WORKLOADS[args.workload])
     if args.length_log2:
@@ -656,7 +675,7 @@ def main():
                        "generator": "counter hash uniform[-1,1), seed 0xC0FFEE"},
             "roofline": roofline, "fused_k23": fused, "reconstruction": recon, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
