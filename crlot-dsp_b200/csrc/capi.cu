@@ -1066,6 +1066,12 @@ bool stream_fused_tick_enabled() {
   return on;
 }
 
+// CRLOT_STREAM_NO_PDL=1: one-kernel ticks without programmatic dependent launch (A/B timing)
+bool stream_pdl_enabled() {
+  static const bool on = getenv("CRLOT_STREAM_NO_PDL") == nullptr;
+  return on;
+}
+
 int stream_nf(const crlot_stream_s* s, long long w_new) {
   const int N = s->plan->d.nfft, H = s->plan->d.hop;
   const long long total = w_new >= N ? (w_new - N) / H + 1 : 0;   // Framer DROP count, framer.cc:106-115
@@ -1086,6 +1092,7 @@ cudaError_t stream_tick_launches(crlot_stream_s* s, const float* d_in, long long
     t.window = p->win_a.p; t.syn_window = p->syn_active ? p->win_s.p : nullptr; t.tw1 = p->tw1.p; t.scrub = p->d.scrub;
     t.gain = p->d.gain; t.eps = p->d.eps; t.norm = p->env.p; t.ring_len = static_cast<long long>(p->ring_len);
     t.acc = s->acc.p; t.out = d_out; t.out_stride = out_stride; t.k_base = k_base;
+    t.pdl = stream_pdl_enabled() ? 1 : 0;
     return launch_stream_tick1(t, st);
   }
   cudaError_t e = launch_stream_ingest(s->ctr.p, d_in, in_stride, chunk_len, s->ring.p, s->rcap, s->S, w0, st);

@@ -214,6 +214,7 @@ struct StreamTick1Params {
   float* acc;                // [n_streams][ring_len]
   float* out;
   long long out_stride, k_base;
+  int pdl;                   // 1: launch with programmatic stream serialization (prologue overlaps the previous tick)
 };
 bool stream_tick1_supported(int nfft, int hop, int chunk_len, long long ring_len, long long out_stride, const void* out);
 cudaError_t launch_stream_tick1(const StreamTick1Params& p, cudaStream_t st);

@@ -203,6 +203,11 @@ __global__ void __launch_bounds__(kSWarps * 32) stream_tick1_kernel(const Stream
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_wsyn + (WIN ? NFFT : 0));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   cpx* ex = s_tw1 + C + warp * X::XCPX;
+  // Programmatic dependent launch: the next tick's blocks may start as soon as every block of this one is
+  // running; they do their prologue (tables into shared memory, per-lane split constants -- nothing a tick
+  // writes) while this tick computes, and wait below for this grid to complete and flush before touching
+  // the counters, rings or spectra.  Both instructions are no-ops in a launch without the attribute.
+  if (p.pdl) asm volatile("griddepcontrol.launch_dependents;");
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) {
     s_win[i] = p.window[i];
     if (WIN) s_wsyn[i] = p.syn_window[i];
@@ -210,6 +215,7 @@ __global__ void __launch_bounds__(kSWarps * 32) stream_tick1_kernel(const Stream
   for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
   const SplitLane<X::M2> SLF = make_split_fwd<X>(lane);
   const SplitLane<X::M1> SLI = make_split_inv<X>(lane);
+  if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
   const long long w = p.ctr->w, k0 = p.ctr->k;
   __syncthreads();
 
@@ -389,6 +395,19 @@ cudaError_t launch_tick1_t(const StreamTick1Params& p, cudaStream_t st) {
   long long blocks = (steps + kSWarps - 1) / kSWarps;
   const long long cap = static_cast<long long>(device_sm_count()) * 2;
   if (blocks > cap) blocks = cap;
+  if (p.pdl) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(static_cast<unsigned>(blocks));
+    cfg.blockDim = dim3(kSWarps * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, p);
+  }
   kern<<<static_cast<unsigned>(blocks), kSWarps * 32, smem, st>>>(p);
   return cudaGetLastError();
 }
