@@ -7,8 +7,9 @@
 // is a mixed-radix transform with a generic butterfly for any prime factor (third_party/kissfft/
 // kiss_fft.c:236-328).  These kernels give the drop-in the same domain ON THE GPU (there is no CPU
 // path behind any entry point): one thread block per row, the row in shared memory,
-// a Stockham autosort transform whose stages are the prime factors of the length (4s first), each
-// output of a stage computed by one thread as an R-term sum -- simple, conflict-light, and O(n*sum R).
+// a Stockham autosort transform whose stages are the prime factors of the length (4s first): radix 4, 2,
+// 3 and 5 stages as one thread per butterfly (exact +-i rotations, like kissfft's kf_bfly4/2/3/5), any
+// other prime factor with each output computed by one thread as an R-term sum (kf_bfly_generic).
 // They are the compatibility path, not the benchmark path: a row costs a block-wide barrier per
 // stage and the twiddles come from global memory through L1.
 //
@@ -32,6 +33,9 @@ struct GenStages {
   int len;                       // complex length M
   int count;
   int radix[kGenMaxStages];      // product == len
+  // exact division of an index < 2^16 by the stage's stride s and by its radix R without a divide:
+  // floor(n / d) == umulhi(n, floor(2^32 / d) + 1) for n, d < 2^16
+  unsigned int mul_s[kGenMaxStages], mul_r[kGenMaxStages];
 };
 
 GenStages factorize(int len) {
@@ -44,6 +48,12 @@ GenStages factorize(int len) {
   for (int r = 3; r * r <= n; r += 2)
     while (n % r == 0) { push(r); n /= r; }
   if (n > 1) push(n);
+  unsigned int s = 1;
+  for (int i = 0; i < g.count && i < kGenMaxStages; ++i) {
+    g.mul_s[i] = static_cast<unsigned int>((1ull << 32) / s + 1);      // s == 1: 2^32 + 1 wraps to 1, handled in the kernel
+    g.mul_r[i] = static_cast<unsigned int>((1ull << 32) / static_cast<unsigned int>(g.radix[i]) + 1);
+    s *= static_cast<unsigned int>(g.radix[i]);
+  }
   return g;
 }
 
@@ -58,9 +68,84 @@ __device__ cpx* gen_stages(cpx* x, cpx* y, const GenStages& g, const cpx* __rest
   for (int st = 0; st < g.count; ++st) {
     const int R = g.radix[st];
     const int m = n / R, wr = M / R;
+    const unsigned int ms = g.mul_s[st], mr = g.mul_r[st];
+    if (R == 4) {
+      // one thread per butterfly: four inputs, the 4-point DFT with exact +-i rotations, three twiddles
+      for (int bt = threadIdx.x; bt < M / 4; bt += blockDim.x) {
+        const int p = s == 1 ? bt : static_cast<int>(__umulhi(static_cast<unsigned int>(bt), ms));
+        const int q = bt - p * s;
+        const cpx* xin = x + q + s * p;
+        const cpx a0 = xin[0], a1 = xin[s * m], a2 = xin[2 * s * m], a3 = xin[3 * s * m];
+        const cpx e0 = a0 + a2, e1 = a0 - a2, o0 = a1 + a3, o1 = a1 - a3;
+        const cpx r = INV ? mk(-o1.y, o1.x) : mk(o1.y, -o1.x);          // -i*o1 forward, +i*o1 inverse
+        const cpx b0 = e0 + o0, b1 = e1 + r, b2 = e0 - o0, b3 = e1 - r;
+        const int w1 = p * s;
+        const cpx t1 = tw[w1], t2 = tw[2 * w1], t3 = tw[3 * w1];
+        cpx* yo = y + q + 4 * s * p;
+        yo[0] = b0;
+        yo[s] = INV ? cmulc(b1, t1) : cmul(b1, t1);
+        yo[2 * s] = INV ? cmulc(b2, t2) : cmul(b2, t2);
+        yo[3 * s] = INV ? cmulc(b3, t3) : cmul(b3, t3);
+      }
+    } else if (R == 2) {
+      for (int bt = threadIdx.x; bt < M / 2; bt += blockDim.x) {
+        const int p = s == 1 ? bt : static_cast<int>(__umulhi(static_cast<unsigned int>(bt), ms));
+        const int q = bt - p * s;
+        const cpx a0 = x[q + s * p], a1 = x[q + s * p + s * m];
+        const cpx t1 = tw[p * s], d = a0 - a1;
+        y[q + 2 * s * p] = a0 + a1;
+        y[q + 2 * s * p + s] = INV ? cmulc(d, t1) : cmul(d, t1);
+      }
+    } else if (R == 3) {
+      const float c = 0.86602540378443864676f;                          // sin(2 pi / 3)
+      for (int bt = threadIdx.x; bt < M / 3; bt += blockDim.x) {
+        const int p = s == 1 ? bt : static_cast<int>(__umulhi(static_cast<unsigned int>(bt), ms));
+        const int q = bt - p * s;
+        const cpx* xin = x + q + s * p;
+        const cpx a0 = xin[0], a1 = xin[s * m], a2 = xin[2 * s * m];
+        const cpx t = a1 + a2, u = a1 - a2;
+        const cpx m1 = fma2(t, splat(-0.5f), a0);
+        const cpx m2 = INV ? mk(-c * u.y, c * u.x) : mk(c * u.y, -c * u.x);   // -+ i sin(2 pi/3) u
+        const cpx b1 = m1 + m2, b2 = m1 - m2;
+        const int w1 = p * s;
+        const cpx t1 = tw[w1], t2 = tw[2 * w1];
+        cpx* yo = y + q + 3 * s * p;
+        yo[0] = a0 + t;
+        yo[s] = INV ? cmulc(b1, t1) : cmul(b1, t1);
+        yo[2 * s] = INV ? cmulc(b2, t2) : cmul(b2, t2);
+      }
+    } else if (R == 5) {
+      const float c1 = 0.30901699437494742410f, c2 = -0.80901699437494742410f;   // cos(2 pi/5), cos(4 pi/5)
+      const float s1 = 0.95105651629515357212f, s2 = 0.58778525229247312917f;    // sin(2 pi/5), sin(4 pi/5)
+      for (int bt = threadIdx.x; bt < M / 5; bt += blockDim.x) {
+        const int p = s == 1 ? bt : static_cast<int>(__umulhi(static_cast<unsigned int>(bt), ms));
+        const int q = bt - p * s;
+        const cpx* xin = x + q + s * p;
+        const cpx a0 = xin[0], a1 = xin[s * m], a2 = xin[2 * s * m], a3 = xin[3 * s * m], a4 = xin[4 * s * m];
+        const cpx t1 = a1 + a4, t2 = a2 + a3, t3 = a1 - a4, t4 = a2 - a3;
+        const cpx m1 = fma2(t2, splat(c2), fma2(t1, splat(c1), a0));
+        const cpx m2 = fma2(t2, splat(c1), fma2(t1, splat(c2), a0));
+        const cpx n1 = fma2(t4, splat(s2), mul2(t3, splat(s1)));
+        const cpx n2 = fma2(t4, splat(-s1), mul2(t3, splat(s2)));
+        // forward: b1 = m1 - i n1, b4 = m1 + i n1, b2 = m2 - i n2, b3 = m2 + i n2; inverse: signs swapped
+        const cpx r1 = INV ? mk(-n1.y, n1.x) : mk(n1.y, -n1.x);
+        const cpx r2 = INV ? mk(-n2.y, n2.x) : mk(n2.y, -n2.x);
+        const cpx b1 = m1 + r1, b4 = m1 - r1, b2 = m2 + r2, b3 = m2 - r2;
+        const int w1 = p * s;
+        const cpx u1 = tw[w1], u2 = tw[2 * w1], u3 = tw[3 * w1], u4 = tw[4 * w1];
+        cpx* yo = y + q + 5 * s * p;
+        yo[0] = a0 + t1 + t2;
+        yo[s] = INV ? cmulc(b1, u1) : cmul(b1, u1);
+        yo[2 * s] = INV ? cmulc(b2, u2) : cmul(b2, u2);
+        yo[3 * s] = INV ? cmulc(b3, u3) : cmul(b3, u3);
+        yo[4 * s] = INV ? cmulc(b4, u4) : cmul(b4, u4);
+      }
+    } else
     for (int idx = threadIdx.x; idx < M; idx += blockDim.x) {
-      const int q = idx % s, t = idx / s;
-      const int j = t % R, p = t / R;
+      const int t = s == 1 ? idx : static_cast<int>(__umulhi(static_cast<unsigned int>(idx), ms));   // idx / s
+      const int q = idx - t * s;
+      const int p = static_cast<int>(__umulhi(static_cast<unsigned int>(t), mr));                     // t / R
+      const int j = t - p * R;
       const cpx* xin = x + q + s * p;
       cpx acc = xin[0];
       int jk = 0;
@@ -179,8 +264,10 @@ __global__ void __launch_bounds__(256) cfft_generic_kernel(const CfftParams p, c
   }
 }
 
+// a radix-4 stage has len/4 butterflies: a quarter of the row length in threads keeps every thread busy in
+// the butterfly stages; short rows then leave room for more resident blocks (rows in flight) per SM
 int gen_threads(int len) {
-  int t = (len + 31) / 32 * 32;
+  int t = (len / 4 + 31) / 32 * 32;
   return t < 32 ? 32 : (t > 256 ? 256 : t);
 }
 
@@ -191,8 +278,9 @@ cudaError_t gen_prepare(Kern kern, int len, int* smem) {
   return cudaSuccess;
 }
 
-int gen_grid(long long rows) {
-  const long long cap = 8ll * device_sm_count();
+int gen_grid(long long rows, int len) {
+  const int per_sm = 2048 / gen_threads(len) < 32 ? 2048 / gen_threads(len) : 32;
+  const long long cap = static_cast<long long>(per_sm) * device_sm_count();
   return static_cast<int>(rows < cap ? (rows > 0 ? rows : 1) : cap);
 }
 
@@ -208,7 +296,7 @@ cudaError_t launch_stft_fwd_generic(const K1Params& p, cudaStream_t st) {
   int smem = 0;
   cudaError_t e = gen_prepare(stft_fwd_generic_kernel, g.len, &smem);
   if (e != cudaSuccess) return e;
-  stft_fwd_generic_kernel<<<gen_grid(p.frames * p.channels), gen_threads(g.len), smem, st>>>(p, g);
+  stft_fwd_generic_kernel<<<gen_grid(p.frames * p.channels, g.len), gen_threads(g.len), smem, st>>>(p, g);
   return cudaGetLastError();
 }
 
@@ -220,7 +308,7 @@ cudaError_t launch_istft_inv_generic(const K2Params& p, cudaStream_t st) {
   int smem = 0;
   cudaError_t e = gen_prepare(istft_inv_generic_kernel, g.len, &smem);
   if (e != cudaSuccess) return e;
-  istft_inv_generic_kernel<<<gen_grid(p.rows), gen_threads(g.len), smem, st>>>(p, g);
+  istft_inv_generic_kernel<<<gen_grid(p.rows, g.len), gen_threads(g.len), smem, st>>>(p, g);
   return cudaGetLastError();
 }
 
@@ -234,11 +322,11 @@ cudaError_t launch_cfft_generic(const CfftParams& p, cudaStream_t st) {
   if (p.inverse) {
     e = gen_prepare(cfft_generic_kernel<true>, g.len, &smem);
     if (e != cudaSuccess) return e;
-    cfft_generic_kernel<true><<<gen_grid(p.rows), gen_threads(g.len), smem, st>>>(p, g);
+    cfft_generic_kernel<true><<<gen_grid(p.rows, g.len), gen_threads(g.len), smem, st>>>(p, g);
   } else {
     e = gen_prepare(cfft_generic_kernel<false>, g.len, &smem);
     if (e != cudaSuccess) return e;
-    cfft_generic_kernel<false><<<gen_grid(p.rows), gen_threads(g.len), smem, st>>>(p, g);
+    cfft_generic_kernel<false><<<gen_grid(p.rows, g.len), gen_threads(g.len), smem, st>>>(p, g);
   }
   return cudaGetLastError();
 }
