@@ -68,15 +68,54 @@ def emit(line):
 # ------------------------------------------------------------------------------------------------
 # CPU arms (the only places bench.py touches oracle/)
 # ------------------------------------------------------------------------------------------------
-def cpu_roundtrip_throughput(nfft, hop, per_thread_len, threads, reps=1):
-    """All-thread reference-CPU throughput in samples/s on a bounded sample.  Each thread runs
-    `reps` independent mono round trips of per_thread_len samples (the reference is
-    single-threaded; independent channels are the only parallelism it admits)."""
+HWY_NOTE = ("reference CPU path (oracle/_ref = the unmodified reference sources); Highway OLA kernels replaced by the "
+            "reference's own scalar kernels auto-vectorised by GCC (Highway is not vendored), driven from one Python "
+            "thread per core (ctypes releases the GIL)")
+
+
+_CPU_CHECKER = None
+
+
+def _cpu_checker():
+    global _CPU_CHECKER
+    if _CPU_CHECKER is None:
+        _CPU_CHECKER = _cpu_checker_probe()
+    return _CPU_CHECKER
+
+
+def _cpu_checker_probe():
+    """(module, oracle, ref-or-None, isa): the compiled reference when oracle/_ref travelled with the repo --
+    the faster of its two ISA builds on this host (x86-64-v3 = AVX2+FMA, x86-64-v4 = AVX-512; -march=native
+    cannot be used for a library built in another container) -- else None (callers fall back to the port)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle as po
     orc = po.Oracle()
-    if po.Ref.available():
-        ref = po.Ref()
+    if not po.Ref.available():
+        return po, orc, None, None
+    cands = ["v3"] + (["v4"] if po.Ref.best_isa() == "v4" else [])
+    if len(cands) == 1:
+        return po, orc, po.Ref(isa="v3"), "x86-64-v3 (AVX2+FMA)"
+    w = orc.window(po.HANN, 2048)
+    x = orc.synth_uniform(SEED, 0, 0, 1 << 20)
+    best = None
+    for isa in cands:
+        r = po.Ref(isa=isa)
+        r.roundtrip(x, 2048, 512, w, po.DROP, taps=False)
+        t0 = time.perf_counter()
+        r.roundtrip(x, 2048, 512, w, po.DROP, taps=False)
+        dt = time.perf_counter() - t0
+        if best is None or dt < best[0]:
+            best = (dt, isa, r)
+    names = {"v3": "x86-64-v3 (AVX2+FMA)", "v4": "x86-64-v4 (AVX-512)"}
+    return po, orc, best[2], names[best[1]] + ", the faster of the v3/v4 builds on this host"
+
+
+def cpu_roundtrip_throughput(nfft, hop, per_thread_len, threads, reps=1):
+    """Reference-CPU throughput in samples/s on a bounded sample.  Each thread runs `reps` independent mono
+    round trips of per_thread_len samples (the reference is single-threaded; independent channels are the only
+    parallelism it admits).  Returns (samples/s, kind, seconds, isa)."""
+    po, orc, ref, isa = _cpu_checker()
+    if ref is not None:
         w = orc.window(po.HANN, nfft)
         xs = [orc.synth_uniform(SEED, t, 0, per_thread_len) for t in range(threads)]
         bar = threading.Barrier(threads + 1)
@@ -98,8 +137,8 @@ def cpu_roundtrip_throughput(nfft, hop, per_thread_len, threads, reps=1):
         kind = "reference"
     else:
         dt = sum(orc.bench_roundtrip_mt(threads, per_thread_len, nfft, hop, po.HANN, SEED)[0] for _ in range(reps))
-        kind = "port"
-    return threads * per_thread_len * reps / dt, kind, dt
+        kind, isa = "port", "x86-64-v3 (plain-C port, oracle/crlot_oracle.c)"
+    return threads * per_thread_len * reps / dt, kind, dt, isa
 
 
 def run_reference_arm(args, wl, rank, world):
@@ -109,21 +148,24 @@ def run_reference_arm(args, wl, rank, world):
     per = 1 << 22
     reps = 8                                   # ~1-2 s of work per step on 16 threads
     vals = []
-    kind = "port"
+    kind, isa = "port", None
     for i in range(args.warmup + args.steps):
-        v, kind, dt = cpu_roundtrip_throughput(wl["nfft"], wl["hop"], per, threads, reps)
+        v, kind, dt, isa = cpu_roundtrip_throughput(wl["nfft"], wl["hop"], per, threads, reps)
         if i >= args.warmup:
             vals.append((v, dt))
     v = float(np.mean([a for a, _ in vals]))
-    sample = f"{threads} threads x {reps} x 2^22 samples (independent mono round trips) per step, frame {wl['nfft']} hop {wl['hop']}"
+    one, _, dt1, _ = cpu_roundtrip_throughput(wl["nfft"], wl["hop"], per, 1, 2)
+    sample = (f"{threads} threads x {reps} x 2^22 samples (independent mono round trips) per step, frame {wl['nfft']} "
+              f"hop {wl['hop']}; ISA {isa}")
     line = {
-        "impl": "reference", "metric": "stft_istft_roundtrip_throughput", "value": v / 1e6, "unit": "Msamples/s",
+        # the line is the reference's own code only when oracle/_ref is present; the builder's C port is labelled as such
+        "impl": "reference" if kind == "reference" else "port", "metric": "stft_istft_roundtrip_throughput", "value": v / 1e6, "unit": "Msamples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": float(np.mean([b for _, b in vals])) * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["name"], "note": "reference CPU path on host cores; Highway kernels replaced by the "
-                   "reference's scalar kernels auto-vectorised by GCC (Highway not vendored)"},
-        "cpu_baseline": {"value": v / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": sample},
+        "config": {"workload": wl["name"], "note": HWY_NOTE},
+        "cpu_baseline": {"value": v / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind, "sample": sample, "isa": isa,
+                         "one_core": {"value": one / 1e6, "unit": "Msamples/s", "sample": f"1 thread x 2 x 2^22 samples ({dt1:.1f} s)"}},
         "e2e": {"value": v / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -221,10 +263,61 @@ class Clocks:
 
 
 # ------------------------------------------------------------------------------------------------
+# GPU arm: shared context
+# ------------------------------------------------------------------------------------------------
+class Ctx:
+    """torch / torch.distributed / the binding, this rank's place in the job, the HBM peak."""
+
+    def __init__(self, torch, dist, dsp, rank, world, local):
+        self.torch, self.dist, self.dsp = torch, dist, dsp
+        self.rank, self.world, self.local = rank, world, local
+        self.dev = torch.device("cuda", local)
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            self.peak, self.peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        else:
+            self.peak, self.peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+        self.group = None                      # crlot_shard_group (NCCL), created on first use
+
+    def ev(self):
+        return self.torch.cuda.Event(enable_timing=True)
+
+    def sync_all(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        t = self.torch.tensor([float(v)], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def shard_group(self):
+        if self.group is None:
+            from crlot_dsp_b200 import sharding
+            self.group = sharding.ShardGroup(self.rank, self.world, self.local, self.dist)
+        return self.group
+
+    def oracle(self):
+        """CPU checker for the untimed parity figures; rank 0 loads (and if needed builds) it first."""
+        if self.rank != 0 and self.world > 1:
+            self.dist.barrier()
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import pyoracle as po
+        orc = po.Oracle()
+        if self.rank == 0 and self.world > 1:
+            self.dist.barrier()
+        return po, orc
+
+
+# ------------------------------------------------------------------------------------------------
 # GPU arm, streaming workload (c5)
 # ------------------------------------------------------------------------------------------------
-def run_c5(args, wl, rank, world, local, torch, dist, dsp):
-    dev = torch.device("cuda", local)
+def measure_c5(ctx, wl, steps, warmup, e2e=True):
+    """4096 streams fed in 64-sample chunks through the device-resident rings; a step = 512 ticks.
+    Returns the dict of figures (rank-independent after the max-over-ranks reduction)."""
+    torch, dsp, rank, world, local, dev = ctx.torch, ctx.dsp, ctx.rank, ctx.world, ctx.local, ctx.dev
     N, H, chunk = wl["nfft"], wl["hop"], wl["chunk"]
     assert wl["channels"] % world == 0
     S = wl["channels"] // world
@@ -234,48 +327,51 @@ def run_c5(args, wl, rank, world, local, torch, dist, dsp):
     st = dsp.Stream(plan, S, max_chunk=chunk)
     x = dsp.synth_uniform(S, T * chunk, seed=SEED, channel0=rank * S, device=local)
     out = torch.empty((S, (T + 1) * chunk), dtype=torch.float32, device=dev)
-    ev = lambda: torch.cuda.Event(enable_timing=True)
 
-    def sync_all():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         st.run(x, chunk, n_ticks=T, out=out)
-    sync_all()
+    ctx.sync_all()
     clocks = Clocks(local)
     if rank == 0:
         clocks.start()
-    t_beg, t_end = ev(), ev()
-    sync_all()
+    t_beg, t_end = ctx.ev(), ctx.ev()
+    ctx.sync_all()
     t_beg.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         st.run(x, chunk, n_ticks=T, out=out)
     t_end.record()
-    sync_all()
+    ctx.sync_all()
     clk = clocks.stop() if rank == 0 else None
-    tmax = torch.tensor([t_beg.elapsed_time(t_end)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    ms = float(tmax.item())
+    ms = ctx.max_over_ranks(t_beg.elapsed_time(t_end))
     total = S * world * T * chunk
-    value = total * args.steps / (ms * 1e-3)
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
-    else:
-        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    value = total * steps / (ms * 1e-3)
     bps = dsp.bytes_per_sample(N, H)
     gbps = bps * (value / world) / 1e9
     roofline = {"bound": "hbm", "kernel": "one tick = stream_tick1_kernel (ingest + window/rFFT + irFFT + OLA ring + produce in ONE launch; 32 ticks per CUDA graph)",
-                "achieved": gbps, "peak": peak, "unit": "GB/s", "frac": gbps / peak, "traffic": None, "peak_source": peak_src,
+                "achieved": gbps, "peak": ctx.peak, "unit": "GB/s", "frac": gbps / ctx.peak, "traffic": None, "peak_source": ctx.peak_src,
                 "note": "latency/launch-bound by construction: a tick moves 19 MB per GPU and its working set is "
                         "L2-resident; the figure to read is tick_latency_us",
-                "path": {"bytes_per_sample": bps, "achieved_GBps_per_gpu": gbps, "frac_of_measured": gbps / peak}}
+                "path": {"bytes_per_sample": bps, "achieved_GBps_per_gpu": gbps, "frac_of_measured": gbps / ctx.peak}}
 
-    e2e = None
-    if not args.no_e2e:
+    # parity of the ticks just run (untimed): the streaming state was never reset, so stream 0 of this rank has
+    # consumed x[0] repeated warmup+steps times and `out` holds the outputs of the last step.  Compare 2^12 of them
+    # with the oracle's round trip of the same periodic signal, restarted at a multiple of ring_len (slice oracle).
+    po, orc = ctx.oracle()
+    k_base = st.frames_processed() - T                           # frame whose hop sits at out[:, 0]
+    a0, n_cmp, period = k_base * H, 1 << 12, T * chunk
+    base = -(-a0 // plan.ring_len) * plan.ring_len
+    xs = x[0].cpu().numpy()
+    seg = xs[(base + np.arange(n_cmp + 3 * N)) % period]
+    want = orc.roundtrip(seg, N, H, orc.window(po.HAMMING, N), po.DROP, taps=False)["out"][N:N + n_cmp].astype(np.float64)
+    got = out[0, base + N - a0:base + N - a0 + n_cmp].cpu().numpy().astype(np.float64)
+    rel = ctx.max_over_ranks(float(np.sqrt(np.sum((got - want) ** 2) / np.sum(want ** 2))))
+    res = {"parity": {"rel_l2_max_over_ranks": rel, "samples_per_rank": n_cmp, "bar": "1e-5 relative L2 (north_star)",
+                      "checker": "oracle round trip of the same (periodic) input, slice at the last step's sample offset"},
+           "value": value / 1e6, "unit": "Msamples/s", "ms_per_step": ms / steps, "tick_latency_us": ms / steps / T * 1e3,
+           "streams_per_rank": S, "chunk": chunk, "ticks_per_step": T, "roofline": roofline, "clocks": clk,
+           "gpu_launches": (1 if chunk == H else 5) * T * steps, "frame": N, "hop": H}
+
+    if e2e:
         ticks = min(T, 256)
         hin = torch.empty((S, ticks * chunk), dtype=torch.float32).pin_memory()
         hin.copy_(x[:, :ticks * chunk])
@@ -283,46 +379,59 @@ def run_c5(args, wl, rank, world, local, torch, dist, dsp):
         hin_np, hout_np = hin.numpy(), hout.numpy()
         for t in range(8):
             st.tick_host(hin_np[:, t * chunk:(t + 1) * chunk], hout_np)
-        sync_all()
+        ctx.sync_all()
         lat = []
         t0 = time.perf_counter()
         for t in range(ticks):
             a = time.perf_counter()
             st.tick_host(hin_np[:, t * chunk:(t + 1) * chunk], hout_np)      # returns when h_out is complete
             lat.append(time.perf_counter() - a)
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": S * world * ticks * chunk / float(dt.item()) / 1e6, "unit": "Msamples/s",
-               "h2d_bytes_per_step": S * chunk * 4, "d2h_bytes_per_step": S * H * (chunk // H) * 4, "steps": ticks,
-               "api": "crlot_stream_tick_host: per tick H2D of the chunk, one fused tick kernel, D2H of the hop, synchronous",
-               "tick_latency_us": {"median": float(np.median(lat)) * 1e6, "p99": float(np.percentile(lat, 99)) * 1e6}}
+        dt = ctx.max_over_ranks(time.perf_counter() - t0)
+        res["e2e"] = {"value": S * world * ticks * chunk / dt / 1e6, "unit": "Msamples/s",
+                      "h2d_bytes_per_step": S * chunk * 4, "d2h_bytes_per_step": S * H * (chunk // H) * 4, "steps": ticks,
+                      "api": "crlot_stream_tick_host: per tick H2D of the chunk, one fused tick kernel, D2H of the hop, synchronous",
+                      "tick_latency_us": {"median": float(np.median(lat)) * 1e6, "p99": float(np.percentile(lat, 99)) * 1e6}}
+        if hasattr(st, "tick_host_pipelined"):
+            res["e2e"]["pipelined"] = st.bench_pipelined(hin_np, chunk, ticks)
+    st.close()
+    plan.close()
+    del x, out
+    torch.cuda.empty_cache()
+    return res
 
+
+def run_c5(args, wl, ctx):
+    r = measure_c5(ctx, wl, args.steps, args.warmup, e2e=not args.no_e2e)
     cpu = None
-    if rank == 0 and not args.no_cpu and world == 1:
-        threads = os.cpu_count() or 1
-        per, reps = 1 << 22, 8
-        v, kind, dt = cpu_roundtrip_throughput(N, H, per, threads, reps)
-        cpu = {"value": v / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
-               "sample": f"{threads} threads x {reps} x 2^22 samples, independent mono round trips, frame {N} hop {H} Hann "
-                         f"({dt:.1f} s); Highway kernels replaced by the reference's scalar kernels (Highway not vendored)"}
-    if rank == 0:
-        line = {
-            "metric": "stft_istft_roundtrip_throughput", "value": value / 1e6, "unit": "Msamples/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["name"], "frame": N, "hop": H, "streams_per_rank": S, "chunk": chunk,
-                       "ticks_per_step": T, "tick_latency_us": ms / args.steps / T * 1e3,
-                       "cache": "working set (rings 29 MB + chunk) is L2-resident by nature of the workload; inputs of a "
-                                "step (512 MB) stream from HBM",
-                       "generator": "counter hash uniform[-1,1), seed 0xC0FFEE"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": (1 if chunk == H else 5) * T * args.steps, "clocks": clk,
-        }
-        emit(line)
+    if ctx.rank == 0 and not args.no_cpu and ctx.world == 1:
+        cpu = cpu_baseline_dict(wl["nfft"], wl["hop"], 1 << 22, 8)
+    if ctx.rank == 0:
+        emit({"metric": "stft_istft_roundtrip_throughput", "value": r["value"], "unit": "Msamples/s",
+              "n_gpus": ctx.world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+              "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+              "config": {"workload": wl["name"], "frame": r["frame"], "hop": r["hop"], "streams_per_rank": r["streams_per_rank"],
+                         "chunk": r["chunk"], "ticks_per_step": r["ticks_per_step"], "tick_latency_us": r["tick_latency_us"],
+                         "cache": "working set (rings 29 MB + chunk) is L2-resident by nature of the workload; inputs of a "
+                                  "step (512 MB) stream from HBM",
+                         "generator": "counter hash uniform[-1,1), seed 0xC0FFEE"},
+              "roofline": r["roofline"], "parity": r["parity"], "cpu_baseline": cpu, "e2e": r.get("e2e"),
+              "gpu_launches": r["gpu_launches"], "clocks": r["clocks"]})
+
+
+def cpu_baseline_dict(N, H, per, reps):
+    """The reference CPU path on all host threads AND on one core."""
+    threads = os.cpu_count() or 1
+    v, kind, dt, isa = cpu_roundtrip_throughput(N, H, per, threads, reps)
+    one, _, dt1, _ = cpu_roundtrip_throughput(N, H, min(per, 1 << 22), 1, 3)
+    return {"value": v / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind, "isa": isa,
+            "sample": f"{threads} threads x {reps} x 2^{int(math.log2(per))} samples, independent mono round trips, frame {N} hop {H} Hann "
+                      f"({dt:.1f} s); ISA {isa}; {HWY_NOTE}",
+            "one_core": {"value": one / 1e6, "unit": "Msamples/s", "cores": 1,
+                         "sample": f"1 thread x 3 x 2^{int(math.log2(min(per, 1 << 22)))} samples ({dt1:.1f} s)"}}
 
 
 # ------------------------------------------------------------------------------------------------
-# GPU arm
+# GPU arm, batch workloads (c2, c3, c4)
 # ------------------------------------------------------------------------------------------------
 def bind_to_gpu_numa_node(torch, local):
     """One process per GPU: run this process on the CPUs of the NUMA node the GPU hangs off, so that
@@ -348,6 +457,352 @@ def bind_to_gpu_numa_node(torch, local):
         return None
 
 
+def pcie_ceiling(ctx, nbytes=1 << 30, reps=3):
+    """What plain page-locked cudaMemcpyAsync traffic reaches on this box with ALL ranks copying at once:
+    every rank moves `nbytes` host->device on one stream and `nbytes` device->host on another, concurrently
+    (one copy per direction per repetition, no batched-memcpy API).  A sample costs 4 bytes each way, so the
+    e2e ceiling in samples/s is bytes-per-direction-per-second / 4.  Returns aggregate Msamples/s + GB/s."""
+    torch = ctx.torch
+    h_in = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    d_in = torch.empty(nbytes, dtype=torch.uint8, device=ctx.dev)
+    d_out = torch.empty(nbytes, dtype=torch.uint8, device=ctx.dev)
+    s1, s2 = torch.cuda.Stream(ctx.dev), torch.cuda.Stream(ctx.dev)
+
+    def both():
+        with torch.cuda.stream(s1):
+            d_in.copy_(h_in, non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_out.copy_(d_out, non_blocking=True)
+    both()
+    ctx.sync_all()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        both()
+    torch.cuda.synchronize()
+    dt = ctx.max_over_ranks(time.perf_counter() - t0)
+    per_dir = nbytes * reps / dt                                   # bytes/s per direction per rank
+    del h_in, h_out, d_in, d_out
+    return {"GBps_per_direction_per_gpu": per_dir / 1e9, "aggregate_GBps_both_directions": 2 * per_dir * ctx.world / 1e9,
+            "Msamples_per_s_aggregate": per_dir / 4 * ctx.world / 1e6,
+            "how": f"all {ctx.world} rank(s) at once: {reps} x (1 GiB pinned H2D on one stream + 1 GiB D2H on another), plain cudaMemcpyAsync, wall clock, max over ranks"}
+
+
+def measure_batch(ctx, key, wl, steps, warmup, detail):
+    """One batch workload (c2 / c3 / c4) on this job's ranks: the three-kernel path, the K1 + fused K2+K3 path,
+    the fully fused path where the plan supports it, and a per-rank parity figure against a slice oracle.
+    detail = True adds the reconstruction SNR block."""
+    torch, dist, dsp, rank, world, local, dev = ctx.torch, ctx.dist, ctx.dsp, ctx.rank, ctx.world, ctx.local, ctx.dev
+    from crlot_dsp_b200 import sharding
+    N, H = wl["nfft"], wl["hop"]
+    w = dsp.window_make(dsp.HANN, N)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP, device=local)
+    ev = ctx.ev
+    sh = group = None
+
+    # ---- lay the workload out on this rank ------------------------------------------------------
+    if key == "c2":
+        chans, L, batch = 1, wl["length"], 1
+        x = dsp.synth_uniform(1, L, seed=SEED, channel0=rank, device=local)
+        local_samples, scaling, chan0 = L, "weak", rank
+    elif key == "c3":
+        chan0, chans = sharding.channel_shard(wl["channels"], rank, world)
+        L = wl["length"]
+        batch = min(32, chans)                      # workspace batch: 32 ch = 21.5 GB of spectra+frames
+        x = dsp.synth_uniform(chans, L, seed=SEED, channel0=chan0, device=local)
+        local_samples, scaling = chans * L, "strong"
+    else:  # c4: rank r owns the output/time range [r*S, (r+1)*S); halos from BOTH neighbours (csrc/shard.cu)
+        chans, batch, chan0 = 1, 1, 0
+        S = wl["length"]
+        sh = sharding.make_time_shard(S * world, N, H, rank, world)
+        left, right = sh.left_halo, sh.right_halo
+        xbuf = torch.zeros(left + S + right + 16, dtype=torch.float32, device=dev)
+        dsp.synth_uniform(1, S, seed=SEED, channel0=0, i0=rank * S, device=local, out=xbuf[left:left + S].unsqueeze(0))
+        local_samples, scaling = S, "weak"
+        group = ctx.shard_group() if world > 1 else None
+
+    # workspaces
+    if key == "c4":
+        Ltot = left + S + right
+        F, n_out = sh.n_frames, sh.n_out
+        spec = torch.empty((1, F, plan.bins), dtype=torch.complex64, device=dev)
+        frames = torch.empty((1, F, N), dtype=torch.float32, device=dev)
+        out = torch.empty((1, n_out), dtype=torch.float32, device=dev)
+    else:
+        F = plan.n_frames(L)
+        spec = torch.empty((batch, F, plan.bins), dtype=torch.complex64, device=dev)
+        frames = torch.empty((batch, F, N), dtype=torch.float32, device=dev)
+        out = torch.empty((chans, plan.out_len(L)), dtype=torch.float32, device=dev)
+
+    halo_ev = []
+
+    def halo_exchange(record):
+        """the (frame-hop)-sample neighbour exchange: crlot_halo_exchange (ncclSend/ncclRecv in one group) on the
+        compute stream, INSIDE the timed region"""
+        if group is None:
+            return
+        if record:
+            e0, e1 = ev(), ev()
+            e0.record()
+        sharding.halo_exchange(xbuf, sh, group)
+        if record:
+            e1.record()
+            halo_ev.append((e0, e1))
+
+    def step(rec=None):
+        if key == "c4":
+            halo_exchange(rec is not None)
+            e = [ev() for _ in range(4)] if rec is not None else None
+            if e: e[0].record()
+            plan.stft(xbuf.unsqueeze(0), length=Ltot, n_frames=F, out=spec)
+            if e: e[1].record()
+            plan.istft_frames(spec, fuse_synthesis_window=True, out=frames)
+            if e: e[2].record()
+            plan.ola(frames, prewindowed=True, t_offset=sh.t0, frame_t0=sh.frame_t0, n_out=n_out, out=out)
+            if e:
+                e[3].record()
+                rec.append(e)
+            return 3
+        launches = 0
+        for c0 in range(0, chans, batch):
+            xb = x[c0:c0 + batch]
+            nb = xb.shape[0]
+            e = [ev() for _ in range(4)] if rec is not None else None
+            if e: e[0].record()
+            plan.stft(xb, out=spec[:nb])
+            if e: e[1].record()
+            plan.istft_frames(spec[:nb], fuse_synthesis_window=True, out=frames[:nb])
+            if e: e[2].record()
+            plan.ola(frames[:nb], prewindowed=True, out=out[c0:c0 + nb])
+            if e:
+                e[3].record()
+                rec.append(e)
+            launches += 3
+        return launches
+
+    for _ in range(warmup):
+        step()
+    ctx.sync_all()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    rec = []
+    t_beg, t_end = ev(), ev()
+    ctx.sync_all()
+    t_beg.record()
+    launches = 0
+    for _ in range(steps):
+        launches += step(rec)
+    t_end.record()
+    ctx.sync_all()
+    clk = clocks.stop() if rank == 0 else None
+    ms = ctx.max_over_ranks(t_beg.elapsed_time(t_end))
+    kt = {"k1": [e[0].elapsed_time(e[1]) for e in rec], "k2": [e[1].elapsed_time(e[2]) for e in rec],
+          "k3": [e[2].elapsed_time(e[3]) for e in rec]}
+    halo_ms = ctx.max_over_ranks(float(np.mean([a.elapsed_time(b) for a, b in halo_ev]))) if halo_ev else None
+    total_samples = local_samples * world
+    value = total_samples * steps / (ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (rank 0's launches) --------------------------------------
+    peak = ctx.peak
+    bins = N // 2 + 1
+    frames_per_launch = F * (batch if key != "c4" else 1)
+    samples_per_launch = frames_per_launch * H             # new samples consumed per launch
+    alg = {"k1": 4.0 * samples_per_launch + 8.0 * bins * frames_per_launch,
+           "k2": (8.0 * bins + 4.0 * N) * frames_per_launch,
+           "k3": 4.0 * N * frames_per_launch + 4.0 * samples_per_launch}
+    kavg = {k: float(np.mean(kt[k])) for k in ("k1", "k2", "k3")}
+    dom = max(kavg, key=kavg.get)
+    names = {"k1": "stft_fwd_kernel (K1 frame+window+rFFT)", "k2": "istft_inv_kernel (K2 irFFT+synthesis window)",
+             "k3": "ola_gather_kernel (K3 gather overlap-add)"}
+    achieved = alg[dom] / (kavg[dom] * 1e-3) / 1e9
+    per_kernel = {k: {"ms": kavg[k], "alg_GB": alg[k] / 1e9, "GBps": alg[k] / (kavg[k] * 1e-3) / 1e9,
+                      "frac": alg[k] / (kavg[k] * 1e-3) / 1e9 / peak} for k in kavg}
+    worst = min(per_kernel, key=lambda k: per_kernel[k]["frac"])
+    path_gbps = dsp.bytes_per_sample(N, H) * (value / world) / 1e9
+    roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": ctx.peak_src, "per_kernel": per_kernel,
+                "min_frac_kernel": {"kernel": names[worst], "frac": per_kernel[worst]["frac"], "ms": per_kernel[worst]["ms"]},
+                "path": {"bytes_per_sample": dsp.bytes_per_sample(N, H), "achieved_GBps_per_gpu": path_gbps,
+                         "frac_of_measured": path_gbps / peak, "frac_of_8TBps_nominal": path_gbps / 8000.0}}
+    # measured DRAM traffic of the dominant kernel, from the committed ncu --set full capture
+    # (profiles/traffic.json: bytes per frame, read+write, per kernel and frame size)
+    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_path):
+        tj = json.load(open(traffic_path))
+        ent = tj.get("kernels", {}).get(f"{dom}_n{N}_h{H}")
+        if ent:
+            roofline["traffic"] = ent["dram_bytes_per_frame"] * frames_per_launch
+            roofline["traffic_source"] = f"profiles/traffic.json ({ent['source']}), bytes/frame x frames per launch"
+
+    # ---- parity of the three-kernel output of THIS rank (untimed): slice oracle at the rank's own offset ------
+    def parity(tag):
+        po, orc = ctx.oracle()
+        n_cmp = 1 << 16
+        if key == "c4":
+            a, want = orc.slice_roundtrip(SEED, 0, sh.t0, n_cmp, N, H, orc.window(po.HANN, N), plan.ring_len)
+            got = out[0, a - sh.t0:a - sh.t0 + n_cmp]
+        else:
+            c = chans - 1
+            a, want = orc.slice_roundtrip(SEED, chan0 + c, 0, n_cmp, N, H, orc.window(po.HANN, N), plan.ring_len)
+            got = out[c, a:a + n_cmp]
+        got = got.cpu().numpy().astype(np.float64)
+        err = float(np.sqrt(np.sum((got - want) ** 2) / np.sum(want.astype(np.float64) ** 2)))
+        return {"rel_l2_max_over_ranks": ctx.max_over_ranks(err), "samples_per_rank": n_cmp, "path": tag,
+                "checker": "oracle/crlot_oracle.c (pinned bit-for-bit to the compiled reference), slice at each rank's own "
+                           "sample offset / channel", "bar": "1e-5 relative L2 (north_star)"}
+    par = parity("K1 -> K2 -> K3")
+
+    # ---- reconstruction quality (north_star: "the round-trip reconstruction SNR must be reported") ----------
+    recon = None
+    if detail:
+        if key == "c4":       # out[0, j] is output sample t0 + j = rank*S + j, xbuf[left + j] the same input sample
+            hi = min(S, n_out) - N
+            xin, yout = xbuf[left + N:left + hi], out[0, N:hi]
+        else:
+            xin, yout = x[chans - 1, N:L - N], out[chans - 1, N:L - N]
+        num = den = 0.0
+        for o in range(0, xin.numel(), 1 << 26):
+            a_, b_ = xin[o:o + (1 << 26)].double(), yout[o:o + (1 << 26)].double()
+            num += float((a_ * a_).sum().item()); den += float(((a_ - b_) ** 2).sum().item())
+        recon = {"snr_db_vs_input": 10.0 * math.log10(num / den) if den > 0 else float("inf"),
+                 "samples": int(xin.numel()),
+                 "note": "the reference normalises by the window SUM envelope (norm_builder.cc), so its own round trip is "
+                         "a scaled copy of the input (~7.3 dB for Hann at 75 % overlap); parity is judged against the reference",
+                 "vs_reference": {"rel_l2": par["rel_l2_max_over_ranks"], "samples": par["samples_per_rank"],
+                                  "checker": par["checker"], "bar": par["bar"]}}
+
+    # ---- the same round trip with kernels 2+3 fused (iFFT frames never materialised) --------------
+    def timed_variant(fn, n_ev):
+        for _ in range(warmup):
+            fn(None)
+        ctx.sync_all()
+        vrec = []
+        b, e = ev(), ev()
+        b.record()
+        for _ in range(steps):
+            fn(vrec)
+        e.record()
+        ctx.sync_all()
+        return ctx.max_over_ranks(b.elapsed_time(e)), vrec
+
+    fused = None
+    t_off, f_t0 = (sh.t0, sh.frame_t0) if key == "c4" else (0, 0)
+    if plan.istft_ola_supported(t_offset=t_off, frame_t0=f_t0, out=out):
+        def fstep(vrec):
+            if key == "c4":
+                halo_exchange(False)
+                e = [ev() for _ in range(3)] if vrec is not None else None
+                if e: e[0].record()
+                plan.stft(xbuf.unsqueeze(0), length=Ltot, n_frames=F, out=spec)
+                if e: e[1].record()
+                plan.istft_ola(spec, t_offset=sh.t0, frame_t0=sh.frame_t0, n_out=n_out, out=out)
+                if e:
+                    e[2].record()
+                    vrec.append(e)
+                return
+            for c0 in range(0, chans, batch):
+                xb = x[c0:c0 + batch]
+                nb = xb.shape[0]
+                e = [ev() for _ in range(3)] if vrec is not None else None
+                if e: e[0].record()
+                plan.stft(xb, out=spec[:nb])
+                if e: e[1].record()
+                plan.istft_ola(spec[:nb], out=out[c0:c0 + nb])
+                if e:
+                    e[2].record()
+                    vrec.append(e)
+        fms, frec = timed_variant(fstep, 3)
+        fk1 = float(np.mean([e[0].elapsed_time(e[1]) for e in frec]))
+        fk23 = float(np.mean([e[1].elapsed_time(e[2]) for e in frec]))
+        alg23 = (8.0 * bins + 4.0 * H) * frames_per_launch
+        fbps = 8.0 + 16.0 * bins / H
+        fval = total_samples * steps / (fms * 1e-3)
+        fused = {"value": fval / 1e6, "unit": "Msamples/s", "ms_per_step": fms / steps,
+                 "kernels": "stft_fwd_kernel (K1) + istft_ola_kernel (K2+K3 fused, bit-identical output)",
+                 "k1_ms": fk1, "k23_ms": fk23, "k23_alg_GB": alg23 / 1e9, "k23_GBps": alg23 / (fk23 * 1e-3) / 1e9,
+                 "k23_frac": alg23 / (fk23 * 1e-3) / 1e9 / peak, "bytes_per_sample": fbps,
+                 "path_GBps_per_gpu": fbps * (fval / world) / 1e9, "path_frac_of_measured": fbps * (fval / world) / 1e9 / peak,
+                 "parity": parity("K1 -> fused K2+K3"),
+                 "note": "the fused path moves 8+16*bins/hop bytes per sample instead of 8+16*bins/hop+8*N/hop; `value` "
+                         "above stays on the three-kernel path that BASELINE.json's north_star names"}
+
+    # ---- fully fused round trip: K1 -> hook -> K2+K3 in ONE kernel, spectra never materialised (8 B/sample) -------
+    fused_all = None
+    if hasattr(plan, "roundtrip_fused_all") and plan.roundtrip_fused_all_supported():
+        def astep(vrec):
+            if key == "c4":
+                halo_exchange(False)
+                plan.roundtrip_fused_all(xbuf.unsqueeze(0), length=Ltot, n_frames=F, t_offset=sh.t0, frame_t0=sh.frame_t0,
+                                         n_out=n_out, out=out)
+                return
+            plan.roundtrip_fused_all(x, out=out)
+        ams, _ = timed_variant(astep, 0)
+        aval = total_samples * steps / (ams * 1e-3)
+        fused_all = {"value": aval / 1e6, "unit": "Msamples/s", "ms_per_step": ams / steps, "bytes_per_sample": 8.0,
+                     "path_GBps_per_gpu": 8.0 * (aval / world) / 1e9,
+                     "kernels": "roundtrip_fused_kernel (frame + window + rFFT + [hook] + irFFT + synthesis window + OLA + normalise in one launch)",
+                     "bound": "FMA/issue (8 B/sample is far below the HBM roofline)", "parity": parity("fully fused")}
+
+    res = {"key": key, "value": value / 1e6, "unit": "Msamples/s", "ms_per_step": ms / steps, "scaling": scaling,
+           "channels_per_rank": chans, "samples_per_rank": local_samples, "frames_per_launch": frames_per_launch,
+           "frame": N, "hop": H, "roofline": roofline, "fused_k23": fused, "fused_all": fused_all, "parity": par,
+           "reconstruction": recon, "gpu_launches": launches, "clocks": clk, "halo_ms_per_step": halo_ms}
+    if key == "c4":
+        res["halo"] = {"bytes_per_direction": int(max(sh.left_halo, sh.right_halo)) * 4, "ms_per_step_max_over_ranks": halo_ms,
+                       "api": "crlot_halo_exchange: ncclSend/ncclRecv pairs in one ncclGroup on the compute stream, inside the timed region"
+                              if world > 1 else "single rank: no neighbours"}
+
+    # ---- e2e: host buffers through the C-ABI host entry point, copies inside the timed region -----
+    if detail == "full":
+        Le = wl["length"]
+        ce = 1 if key != "c3" else min(chans, 4)
+        nbytes = ce * Le * 4
+        hin = torch.empty((ce, Le), dtype=torch.float32).pin_memory()
+        hin.copy_(x[:ce, :Le] if key != "c4" else xbuf[left:left + Le].unsqueeze(0))
+        n_out_e = plan.out_len(Le)
+        hout = torch.empty((ce, n_out_e), dtype=torch.float32).pin_memory()
+        hin_np, hout_np = hin.numpy(), hout.numpy()
+        plan.roundtrip_host(hin_np, out=hout_np)                 # warm-up (allocates the slab workspace)
+        ctx.sync_all()
+        n_e2e = max(1, min(steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            plan.roundtrip_host(hin_np, out=hout_np)             # synchronous: returns when h_out is complete
+        torch.cuda.synchronize()
+        dt = ctx.max_over_ranks(time.perf_counter() - t0)
+        e2e_val = ce * Le * world * n_e2e / dt / 1e6
+        del hin, hout
+        ceil_ = pcie_ceiling(ctx)
+        res["e2e"] = {"value": e2e_val, "unit": "Msamples/s",
+                      "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": ce * n_out_e * 4, "steps": n_e2e,
+                      "api": "crlot_roundtrip_host (pinned host buffers, slabbed H2D/compute/D2H pipeline; K1 + fused K2+K3 per slab)",
+                      "workload": f"{ce}ch x 2^{int(np.log2(Le))} samples per rank",
+                      "ceiling_aggregate": ceil_["Msamples_per_s_aggregate"], "frac_of_ceiling": e2e_val / ceil_["Msamples_per_s_aggregate"],
+                      "ceiling": ceil_}
+
+    plan.close()
+    return res
+
+
+def facade_loop_figure(N, H):
+    """The reference's own per-frame loop (bench/e2e_benchmark.cc:149-176: pop -> window -> forward -> inverse ->
+    push_frame_AoS -> produce) written against the drop-in facades dsp::Framer / IFftPlan / OLAAccumulator
+    (host/facade_test --loop), 2^22 samples.  Every call is a host-pointer call: this is the source-compatible
+    drop-in, latency-bound by design; StftRoundTrip (the e2e figure) is the fast route."""
+    exe = os.path.join(ROOT, "crlot-dsp_b200", "host", "facade_test")
+    if not os.path.exists(exe):
+        return None
+    try:
+        r = subprocess.run([exe, "--loop", str(1 << 22), str(N), str(H)], capture_output=True, text=True, timeout=240)
+        for ln in r.stdout.splitlines():
+            if ln.startswith("{"):
+                return json.loads(ln)
+    except Exception as e:                                     # a figure, not a gate
+        return {"error": str(e)}
+    return {"error": (r.stdout + r.stderr)[-300:]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -358,6 +813,7 @@ def main():
     ap.add_argument("--length-log2", type=int, default=None, help="override samples per channel (debug)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-legs", action="store_true", help="skip the sharded c3/c4, streaming c5 and facade-loop legs of the default line")
     args = ap.parse_args()
     claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -378,305 +834,78 @@ def main():
     import crlot_dsp_b200 as dsp
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (the product has no CPU path)"
     torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
     numa = bind_to_gpu_numa_node(torch, local)      # pinned host buffers land on the GPU's own NUMA node
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
+    ctx = Ctx(torch, dist, dsp, rank, world, local)
 
     if args.workload == "c5":
-        run_c5(args, wl, rank, world, local, torch, dist, dsp)
+        run_c5(args, wl, ctx)
         if world > 1:
             dist.destroy_process_group()
         return
 
-    N, H = wl["nfft"], wl["hop"]
-    w = dsp.window_make(dsp.HANN, N)
-    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP, device=local)
-    halo = N - H
+    r = measure_batch(ctx, args.workload, wl, args.steps, args.warmup, detail="full" if not args.no_e2e else True)
+    torch.cuda.empty_cache()
 
-    # ---- lay the workload out on this rank ------------------------------------------------------
-    if args.workload == "c2":
-        chans, L, batch = 1, wl["length"], 1
-        x = dsp.synth_uniform(1, L, seed=SEED, channel0=rank, device=local)
-        local_samples = L
-        scaling = "weak"
-    elif args.workload == "c3":
-        assert wl["channels"] % world == 0
-        chans, L = wl["channels"] // world, wl["length"]
-        batch = min(32, chans)                      # workspace batch: 32 ch = 21.5 GB of spectra+frames
-        x = dsp.synth_uniform(chans, L, seed=SEED, channel0=rank * chans, device=local)
-        local_samples = chans * L
-        scaling = "strong"
-    else:  # c4: rank r owns the output/time range [r*S, (r+1)*S); halos from BOTH neighbours (sharding.py)
-        from crlot_dsp_b200 import sharding
-        chans, batch = 1, 1
-        S = wl["length"]
-        sh = sharding.make_time_shard(S * world, N, H, rank, world)
-        left, right = sh.left_halo, sh.right_halo
-        xbuf = torch.zeros(left + S + right, dtype=torch.float32, device=dev)
-        dsp.synth_uniform(1, S, seed=SEED, channel0=0, i0=rank * S, device=local, out=xbuf[left:left + S].unsqueeze(0))
-        local_samples = S
-        scaling = "weak"
-
-    def halo_exchange():
-        """NCCL send/recv of the (frame-hop)-sample halos between neighbouring ranks."""
-        sharding.halo_exchange(xbuf, sh)
-
-    # workspaces
-    if args.workload == "c4":
-        Ltot = left + S + right
-        F, n_out = sh.n_frames, sh.n_out
-        spec = torch.empty((1, F, plan.bins), dtype=torch.complex64, device=dev)
-        frames = torch.empty((1, F, N), dtype=torch.float32, device=dev)
-        out = torch.empty((1, n_out), dtype=torch.float32, device=dev)
-    else:
-        F = plan.n_frames(L)
-        spec = torch.empty((batch, F, plan.bins), dtype=torch.complex64, device=dev)
-        frames = torch.empty((batch, F, N), dtype=torch.float32, device=dev)
-        out = torch.empty((chans, plan.out_len(L)), dtype=torch.float32, device=dev)
-
-    ev = lambda: torch.cuda.Event(enable_timing=True)
-    kt = {"k1": [], "k2": [], "k3": []}
-
-    def step(record=False):
-        launches = 0
-        if args.workload == "c4":
-            if world > 1:
-                halo_exchange()
-            e = [ev() for _ in range(4)] if record else None
-            if record: e[0].record()
-            plan.stft(xbuf.unsqueeze(0), length=Ltot, n_frames=F, out=spec)
-            if record: e[1].record()
-            plan.istft_frames(spec, fuse_synthesis_window=True, out=frames)
-            if record: e[2].record()
-            plan.ola(frames, prewindowed=True, t_offset=sh.t0, frame_t0=sh.frame_t0, n_out=n_out, out=out)
-            if record: e[3].record()
-            if record:
-                kt["_ev"].append(e)
-            return 3
-        for c0 in range(0, chans, batch):
-            xb = x[c0:c0 + batch]
-            e = [ev() for _ in range(4)] if record else None
-            if record: e[0].record()
-            plan.stft(xb, out=spec)
-            if record: e[1].record()
-            plan.istft_frames(spec, fuse_synthesis_window=True, out=frames)
-            if record: e[2].record()
-            plan.ola(frames, prewindowed=True, out=out[c0:c0 + batch])
-            if record: e[3].record()
-            if record:
-                kt["_ev"].append(e)
-            launches += 3
-        return launches
-
-    def sync_all():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
-        step()
-    sync_all()
-    clocks = Clocks(local)
-    if rank == 0:
-        clocks.start()
-    kt["_ev"] = []
-    t_beg, t_end = ev(), ev()
-    sync_all()
-    t_beg.record()
-    launches = 0
-    for _ in range(args.steps):
-        launches += step(record=True)
-    t_end.record()
-    sync_all()
-    clk = clocks.stop() if rank == 0 else None
-    ms = t_beg.elapsed_time(t_end)
-    for e in kt["_ev"]:
-        kt["k1"].append(e[0].elapsed_time(e[1])); kt["k2"].append(e[1].elapsed_time(e[2])); kt["k3"].append(e[2].elapsed_time(e[3]))
-    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    ms = float(tmax.item())
-    total_samples = local_samples * world
-    value = total_samples * args.steps / (ms * 1e-3)
-
-    # ---- roofline of the dominant kernel (rank 0's launches) --------------------------------------
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
-    else:
-        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-    bins = N // 2 + 1
-    frames_per_launch = F * (batch if args.workload != "c4" else 1)
-    samples_per_launch = frames_per_launch * H             # new samples consumed per launch
-    alg = {"k1": 4.0 * samples_per_launch + 8.0 * bins * frames_per_launch,
-           "k2": (8.0 * bins + 4.0 * N) * frames_per_launch,
-           "k3": 4.0 * N * frames_per_launch + 4.0 * samples_per_launch}
-    kavg = {k: float(np.mean(kt[k])) for k in ("k1", "k2", "k3")}
-    dom = max(kavg, key=kavg.get)
-    names = {"k1": "stft_fwd_kernel (K1 frame+window+rFFT)", "k2": "istft_inv_kernel (K2 irFFT+synthesis window)",
-             "k3": "ola_gather_kernel (K3 gather overlap-add)"}
-    achieved = alg[dom] / (kavg[dom] * 1e-3) / 1e9
-    per_kernel = {k: {"ms": kavg[k], "alg_GB": alg[k] / 1e9, "GBps": alg[k] / (kavg[k] * 1e-3) / 1e9,
-                      "frac": alg[k] / (kavg[k] * 1e-3) / 1e9 / peak} for k in kavg}
-    path_gbps = dsp.bytes_per_sample(N, H) * (value / world) / 1e9
-    roofline = {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "per_kernel": per_kernel,
-                "path": {"bytes_per_sample": dsp.bytes_per_sample(N, H), "achieved_GBps_per_gpu": path_gbps,
-                         "frac_of_measured": path_gbps / peak, "frac_of_8TBps_nominal": path_gbps / 8000.0}}
-
-    # measured DRAM traffic of the dominant kernel, from the committed ncu --set full capture
-    # (profiles/traffic.json: bytes per frame, read+write, per kernel and frame size)
-    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(traffic_path):
-        tj = json.load(open(traffic_path))
-        ent = tj.get("kernels", {}).get(f"{dom}_n{N}_h{H}")
-        if ent:
-            roofline["traffic"] = ent["dram_bytes_per_frame"] * frames_per_launch
-            roofline["traffic_source"] = f"profiles/traffic.json ({ent['source']}), bytes/frame x frames per launch"
-
-    # ---- the same round trip with kernels 2+3 fused (iFFT frames never materialised) --------------
-    fused = None
-    c4_fused_ok = args.workload == "c4" and plan.istft_ola_supported(t_offset=sh.t0, frame_t0=sh.frame_t0, out=out)
-    if (args.workload != "c4" and plan.istft_ola_supported()) or c4_fused_ok:
-        def fstep(record=None):
-            if args.workload == "c4":
-                if world > 1:
-                    halo_exchange()
-                e = [ev() for _ in range(3)]
-                e[0].record()
-                plan.stft(xbuf.unsqueeze(0), length=Ltot, n_frames=F, out=spec)
-                e[1].record()
-                plan.istft_ola(spec, t_offset=sh.t0, frame_t0=sh.frame_t0, n_out=n_out, out=out)
-                e[2].record()
-                if record is not None:
-                    record.append(e)
-                return
-            for c0 in range(0, chans, batch):
-                xb = x[c0:c0 + batch]
-                if record is not None:
-                    e = [ev() for _ in range(3)]
-                    e[0].record()
-                plan.stft(xb, out=spec)
-                if record is not None:
-                    e[1].record()
-                plan.istft_ola(spec, out=out[c0:c0 + batch])
-                if record is not None:
-                    e[2].record()
-                    record.append(e)
-        for _ in range(args.warmup):
-            fstep()
-        sync_all()
-        rec = []
-        f_beg, f_end = ev(), ev()
-        f_beg.record()
-        for _ in range(args.steps):
-            fstep(rec)
-        f_end.record()
-        sync_all()
-        fms = torch.tensor([f_beg.elapsed_time(f_end)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(fms, op=dist.ReduceOp.MAX)
-        fms = float(fms.item())
-        fk1 = float(np.mean([e[0].elapsed_time(e[1]) for e in rec]))
-        fk23 = float(np.mean([e[1].elapsed_time(e[2]) for e in rec]))
-        alg23 = (8.0 * bins + 4.0 * H) * frames_per_launch
-        fbps = 8.0 + 16.0 * bins / H
-        fval = total_samples * args.steps / (fms * 1e-3)
-        fused = {"value": fval / 1e6, "unit": "Msamples/s", "ms_per_step": fms / args.steps,
-                 "kernels": "stft_fwd_kernel (K1) + istft_ola_kernel (K2+K3 fused, bit-identical output)",
-                 "k1_ms": fk1, "k23_ms": fk23, "k23_alg_GB": alg23 / 1e9, "k23_GBps": alg23 / (fk23 * 1e-3) / 1e9,
-                 "k23_frac": alg23 / (fk23 * 1e-3) / 1e9 / peak, "bytes_per_sample": fbps,
-                 "path_GBps_per_gpu": fbps * (fval / world) / 1e9, "path_frac_of_measured": fbps * (fval / world) / 1e9 / peak,
-                 "note": "the fused path moves 8+16*bins/hop bytes per sample instead of 8+16*bins/hop+8*N/hop; `value` "
-                         "above stays on the three-kernel path that BASELINE.json's north_star names"}
-
-    # ---- e2e: host buffers through the C-ABI host entry point, copies inside the timed region -----
-    e2e = None
-    if not args.no_e2e:
-        Le = wl["length"] if args.workload != "c3" else wl["length"]
-        ce = 1 if args.workload != "c3" else min(chans, 4)
-        nbytes = ce * Le * 4
-        hin = torch.empty((ce, Le), dtype=torch.float32).pin_memory()
-        hin.copy_(x[:ce, :Le] if args.workload != "c4" else xbuf[left:left + Le].unsqueeze(0))
-        n_out_e = plan.out_len(Le)
-        hout = torch.empty((ce, n_out_e), dtype=torch.float32).pin_memory()
-        hin_np, hout_np = hin.numpy(), hout.numpy()
-        plan.roundtrip_host(hin_np, out=hout_np)                 # warm-up (allocates the slab workspace)
-        sync_all()
-        n_e2e = max(1, min(args.steps, 3))
-        t0 = time.perf_counter()
-        for _ in range(n_e2e):
-            plan.roundtrip_host(hin_np, out=hout_np)             # synchronous: returns when h_out is complete
-        torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": ce * Le * world * n_e2e / float(dt.item()) / 1e6, "unit": "Msamples/s",
-               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": ce * n_out_e * 4, "steps": n_e2e,
-               "api": "crlot_roundtrip_host (pinned host buffers, slabbed H2D/compute/D2H pipeline; K1 + fused K2+K3 per slab)",
-               "numa_binding": numa,
-               "workload": f"{ce}ch x 2^{int(np.log2(Le))} samples per rank",
-               "ceiling": "PCIe: 45.8 GB/s per direction with H2D and D2H running together (tools/pcie_probe.py) = 11.4 Gsamples/s per GPU"}
-        del hin, hout
-
-    # ---- reconstruction quality of the round trip just measured (untimed, north_star: "the round-trip
-    # reconstruction SNR must be reported").  vs the input: what the reference's own OLA normalisation
-    # gives (sum-of-window envelope, not sum of squares: ~7.3 dB for Hann at 75 % overlap, SURVEY 0.3);
-    # vs the reference: the CPU reference/oracle on the first 2^18 samples of the same input (checker only).
-    step()
-    torch.cuda.synchronize()
-    if args.workload == "c4":       # out[0, j] is output sample t0 + j = rank*S + j, xbuf[left + j] the same input sample
-        hi = min(S, n_out) - N
-        xin, yout = xbuf[left + N:left + hi], out[0, N:hi]
-    else:
-        c_last = ((chans - 1) // batch) * batch
-        xin, yout = x[c_last, N:L - N], out[c_last, N:L - N]
-    num = den = 0.0
-    for o in range(0, xin.numel(), 1 << 26):
-        a_, b_ = xin[o:o + (1 << 26)].double(), yout[o:o + (1 << 26)].double()
-        num += float((a_ * a_).sum().item()); den += float(((a_ - b_) ** 2).sum().item())
-    recon = {"snr_db_vs_input": 10.0 * math.log10(num / den) if den > 0 else float("inf"),
-             "samples": int(xin.numel()),
-             "note": "the reference normalises by the window SUM envelope (norm_builder.cc), so its own round trip is "
-                     "a scaled copy of the input (~7.3 dB for Hann at 75 % overlap); parity is judged against the reference"}
-    if rank == 0 and not args.no_cpu and world == 1:
-        sys.path.insert(0, os.path.join(ROOT, "oracle"))
-        import pyoracle as po
-        seg = (1 << 18) + N
-        xs = (xbuf[left:left + seg] if args.workload == "c4" else x[c_last, :seg]).cpu().numpy()
-        orc = po.Ref() if po.Ref.available() else po.Oracle()
-        want = orc.roundtrip(xs, N, H, po.Oracle().window(po.HANN, N), po.DROP, taps=False)["out"][N:1 << 18].astype(np.float64)
-        got = (out[0] if args.workload == "c4" else out[c_last])[N:1 << 18].cpu().numpy().astype(np.float64)
-        err = float(np.sum((got - want) ** 2))
-        recon["vs_reference"] = {"rel_l2": math.sqrt(err / float(np.sum(want ** 2))),
-                                 "snr_db": 10.0 * math.log10(float(np.sum(want ** 2)) / err) if err > 0 else float("inf"),
-                                 "samples": int(want.size), "checker": "reference" if po.Ref.available() else "port",
-                                 "bar": "1e-5 relative L2 (north_star)"}
+    # ---- the other BASELINE configs as legs of the same line (driver-visible): the sharded configs c3 (256 channels,
+    # strong scaling, no collective) and c4 (one signal, time shards + NCCL halo inside the timed region), and the
+    # streaming config c5 -- each with its own parity figure.  Shorter timed regions (<= 5 steps) than the headline.
+    sharded = streaming = floop = None
+    if args.workload == "c2" and not args.no_legs and not args.length_log2:
+        ksteps = max(2, min(args.steps, 5))
+        sharded = {}
+        for key in ("c3", "c4"):
+            leg = measure_batch(ctx, key, WORKLOADS[key], ksteps, 3, detail=False)
+            torch.cuda.empty_cache()
+            sharded[key] = {"workload": WORKLOADS[key]["name"], "value": leg["value"], "unit": "Msamples/s", "steps": ksteps, "warmup": 3,
+                            "ms_per_step": leg["ms_per_step"], "scaling": leg["scaling"], "channels_per_rank": leg["channels_per_rank"],
+                            "samples_per_rank": leg["samples_per_rank"],
+                            "path_frac_of_measured": leg["roofline"]["path"]["frac_of_measured"],
+                            "path_frac_of_8TBps_nominal": leg["roofline"]["path"]["frac_of_8TBps_nominal"],
+                            "per_kernel": leg["roofline"]["per_kernel"], "rel_l2": leg["parity"]["rel_l2_max_over_ranks"],
+                            "parity": leg["parity"],
+                            "fused_k23": None if not leg["fused_k23"] else {k: leg["fused_k23"][k] for k in ("value", "ms_per_step", "k1_ms", "k23_ms", "k23_frac")},
+                            "fused_all": None if not leg["fused_all"] else {k: leg["fused_all"][k] for k in ("value", "ms_per_step")}}
+            if key == "c4":
+                sharded[key]["halo"] = leg["halo"]
+                sharded[key]["halo_ms"] = leg["halo_ms_per_step"]
+        s5 = measure_c5(ctx, WORKLOADS["c5"], ksteps, 3, e2e=True)
+        streaming = {"workload": WORKLOADS["c5"]["name"], "value": s5["value"], "unit": "Msamples/s", "ms_per_step": s5["ms_per_step"],
+                     "tick_latency_us_device": s5["tick_latency_us"], "streams_per_rank": s5["streams_per_rank"],
+                     "rel_l2": s5["parity"]["rel_l2_max_over_ranks"], "parity": s5["parity"], "host_tick": s5.get("e2e")}
+        if rank == 0 and world == 1:
+            floop = facade_loop_figure(wl["nfft"], wl["hop"])
 
     cpu = None
     if rank == 0 and not args.no_cpu and world == 1:
-        threads = os.cpu_count() or 1
-        per, reps = 1 << 24, 24
-        v, kind, dt = cpu_roundtrip_throughput(N, H, per, threads, reps)
-        cpu = {"value": v / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
-               "sample": f"{threads} threads x {reps} x 2^24 samples, independent mono round trips, frame {N} hop {H} ({dt:.1f} s); "
-                         "Highway kernels replaced by the reference's scalar kernels (Highway not vendored)"}
+        cpu = cpu_baseline_dict(wl["nfft"], wl["hop"], 1 << 24, 24)
+        if floop and "value" in floop:
+            floop["vs_reference_one_core"] = floop["value"] / cpu["one_core"]["value"]
 
     if rank == 0:
+        e2e = r.get("e2e")
+        if e2e is not None:
+            e2e["numa_binding"] = numa
         line = {
-            "metric": "stft_istft_roundtrip_throughput", "value": value / 1e6, "unit": "Msamples/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["name"], "frame": N, "hop": H, "channels_per_rank": chans,
-                       "samples_per_rank": local_samples, "frames_per_launch": frames_per_launch,
+            "metric": "stft_istft_roundtrip_throughput", "value": r["value"], "unit": "Msamples/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+            "higher_is_better": True, "scaling": r["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["name"], "frame": r["frame"], "hop": r["hop"], "channels_per_rank": r["channels_per_rank"],
+                       "samples_per_rank": r["samples_per_rank"], "frames_per_launch": r["frames_per_launch"],
                        "cache": "inputs larger than L2 (every buffer >> 126 MB), no flush needed",
                        "generator": "counter hash uniform[-1,1), seed 0xC0FFEE"},
-            "roofline": roofline, "fused_k23": fused, "reconstruction": recon, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
+            "roofline": r["roofline"], "fused_k23": r["fused_k23"], "fused_all": r["fused_all"], "reconstruction": r["reconstruction"],
+            "sharded": sharded, "streaming": streaming, "facade_loop": floop,
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": r["gpu_launches"], "clocks": r["clocks"],
         }
+        if r.get("halo"):
+            line["halo"] = r["halo"]
         emit(line)
     if world > 1:
+        if ctx.group is not None:
+            ctx.group.close()
         dist.destroy_process_group()
 
 

@@ -11,5 +11,5 @@ from .capi import (  # noqa: F401
     CrlotError, CrlotInvalidArgument, CrlotUnsupported, Plan, FftPlan, OlaAccumulator, Stream, lib, lib_path, frame_count, ola_ring_len, window_make,
     build_norm_linear, ola_envelope, synth_uniform, HANN, HAMMING, BLACKMAN, RECT, ZERO_PAD, DROP,
     bytes_per_sample, framequeue_count, framequeue_extract, PAD_CONSTANT, PAD_REFLECT, PAD_EDGE,
-    deinterleave, interleave,
+    deinterleave, interleave, axpy, normalize_and_clear, RingBuffer, Framer,
 )

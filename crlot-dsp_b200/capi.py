@@ -630,3 +630,151 @@ class Stream:
 
     def ring_capacity(self):
         return int(lib().crlot_stream_get(self._h, 2))
+
+
+# ---- kernel-dispatch seam on device pointers (dsp::ola::axpy / axpy_windowed / normalize_and_clear) -------
+def axpy(dst, src, g, window=None, device=0):
+    """dst[i] = fma(src[i] (* window[i], rounded), g, dst[i]) on cuda float32 tensors, in place."""
+    n = dst.numel()
+    if window is None:
+        _check(lib().crlot_axpy(C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr()), C.c_float(g), C.c_size_t(n),
+                                C.c_int(device), _stream_ptr(device)))
+    else:
+        _check(lib().crlot_axpy_windowed(C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr()), C.c_void_p(window.data_ptr()),
+                                         C.c_float(g), C.c_size_t(n), C.c_int(device), _stream_ptr(device)))
+    return dst
+
+
+def normalize_and_clear(acc, norm, eps, device=0):
+    """-> out = acc / max(norm, eps) (true division); acc is zeroed in place."""
+    torch = _torch()
+    out = torch.empty_like(acc)
+    _check(lib().crlot_normalize_and_clear(C.c_void_p(out.data_ptr()), C.c_void_p(acc.data_ptr()), C.c_void_p(norm.data_ptr()),
+                                           C.c_float(eps), C.c_size_t(acc.numel()), C.c_int(device), _stream_ptr(device)))
+    return out
+
+
+# ---- drop-in RingBuffer<float> ------------------------------------------------------------------------------
+class _Span(C.Structure):
+    _fields_ = [("off1", C.c_size_t), ("len1", C.c_size_t), ("off2", C.c_size_t), ("len2", C.c_size_t)]
+
+
+class RingBuffer:
+    """dsp::ring::RingBuffer<float> over crlot_ring_* (unified-memory cells; offsets instead of pointers)."""
+
+    def __init__(self, capacity, shadow=False, device=0):
+        self._h = C.c_void_p()
+        L = lib()
+        L.crlot_ring_data.restype = C.c_void_p
+        for f in (L.crlot_ring_capacity, L.crlot_ring_physical_capacity, L.crlot_ring_write_pos, L.crlot_ring_contiguous_offset):
+            f.restype = C.c_size_t
+        _check(L.crlot_ring_create(C.c_size_t(capacity), C.c_size_t(4), C.c_int(int(shadow)), C.c_int(device), C.byref(self._h)))
+        self.device = device
+
+    def __del__(self):
+        try:
+            if self._h.value:
+                lib().crlot_ring_destroy(self._h)
+        except Exception:
+            pass
+
+    def capacity(self):
+        return lib().crlot_ring_capacity(self._h)
+
+    def physical_capacity(self):
+        return lib().crlot_ring_physical_capacity(self._h)
+
+    def write_pos(self):
+        return lib().crlot_ring_write_pos(self._h)
+
+    def data_ptr(self):
+        return lib().crlot_ring_data(self._h)
+
+    def host_view(self):
+        """numpy view of all physical cells (unified memory: synchronise the device before touching it)."""
+        n = self.physical_capacity()
+        return np.ctypeslib.as_array((C.c_float * n).from_address(self.data_ptr()))
+
+    def split(self, start, length):
+        sp = _Span()
+        _check(lib().crlot_ring_split(self._h, C.c_size_t(start), C.c_size_t(length), C.byref(sp)))
+        return (sp.off1, sp.len1), (sp.off2, sp.len2)
+
+    def shadow_sync(self, n):
+        _check(lib().crlot_ring_shadow_sync(self._h, C.c_size_t(n)))
+
+    def contiguous_offset(self, read_pos):
+        return lib().crlot_ring_contiguous_offset(self._h, C.c_size_t(read_pos))
+
+    def write(self, src):
+        src = _f32(src)
+        n = C.c_size_t(0)
+        _check(lib().crlot_ring_write(self._h, _p(src), C.c_size_t(0 if src is None else src.size), C.byref(n)))
+        return n.value
+
+    def write_device(self, src):
+        n = C.c_size_t(0)
+        _check(lib().crlot_ring_write_device(self._h, C.c_void_p(src.data_ptr()), C.c_size_t(src.numel()), C.byref(n),
+                                             _stream_ptr(self.device)))
+        return n.value
+
+    def prefetch(self, to_device=True):
+        _check(lib().crlot_ring_prefetch(self._h, C.c_int(int(to_device)), _stream_ptr(self.device)))
+
+
+# ---- drop-in Framer state (device-resident sample store) -------------------------------------------------------
+class Framer:
+    """dsp::Framer over crlot_framer_* (set_params at construction)."""
+
+    def __init__(self, frame_size, hop_size, channels=1, boundary_mode=ZERO_PAD, device=0):
+        self._h = C.c_void_p()
+        L = lib()
+        L.crlot_framer_available.restype = C.c_size_t
+        L.crlot_framer_get.restype = C.c_size_t
+        _check(L.crlot_framer_create(C.c_size_t(frame_size), C.c_size_t(hop_size), C.c_size_t(channels), C.c_int(boundary_mode),
+                                     C.c_int(device), C.byref(self._h)))
+        self.N, self.H, self.C, self.device = frame_size, hop_size, channels, device
+
+    def __del__(self):
+        try:
+            if self._h.value:
+                lib().crlot_framer_destroy(self._h)
+        except Exception:
+            pass
+
+    def push(self, interleaved):
+        x = _f32(interleaved)
+        _check(lib().crlot_framer_push(self._h, _p(x), C.c_size_t(x.size // self.C)))
+
+    def push_device(self, planar):
+        """planar: cuda float32 [channels, n] (or [n] for one channel), on the current stream."""
+        if planar.dim() == 1:
+            planar = planar.unsqueeze(0)
+        _check(lib().crlot_framer_push_device(self._h, C.c_void_p(planar.data_ptr()), C.c_longlong(planar.stride(0)),
+                                              C.c_size_t(planar.shape[1]), _stream_ptr(self.device)))
+
+    def available_frames(self):
+        return lib().crlot_framer_available(self._h)
+
+    def drainable_frames(self):
+        return lib().crlot_framer_get(self._h, 8)
+
+    def pop(self):
+        out = np.empty(self.N * self.C, np.float32)
+        ok = C.c_int(0)
+        _check(lib().crlot_framer_pop(self._h, _p(out), C.byref(ok)))
+        return out if ok.value else None
+
+    def stft(self, plan, max_frames=-1, out=None):
+        """every poppable frame through kernel 1 of `plan` on the current stream -> complex64 [channels, F, bins]"""
+        torch = _torch()
+        F = self.drainable_frames() if max_frames < 0 else min(self.drainable_frames(), max_frames)
+        if out is None:
+            out = torch.empty((self.C, F, plan.bins), dtype=torch.complex64, device=f"cuda:{self.device}")
+        n = C.c_longlong(0)
+        _check(lib().crlot_framer_stft(self._h, plan._h, C.c_longlong(max_frames), C.c_void_p(out.data_ptr()), C.byref(n),
+                                       _stream_ptr(self.device)))
+        return out[:, :n.value]
+
+    def reset(self):
+        _check(lib().crlot_framer_reset(self._h))

@@ -8,8 +8,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <new>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/crlot_cuda.h"
@@ -149,7 +151,25 @@ struct crlot_plan_s {
   bool syn_active = false;
   DevArr<float> win_a, win_s, win_ones, env;
   DevArr<cpx> tw1, sa, pre;
+  // Work counters of the dynamically scheduled kernels (K1, fused K2+K3).  A launch zeroes its counter word on its
+  // own stream and the kernel pulls chunks from it, so launches that may overlap must not share a word: every
+  // stream that ever launches on this plan gets its own (launches on one stream are ordered, so K1 and the fused
+  // kernel of that stream share it).  kCounterWords streams are tracked; beyond that words are reused round-robin.
+  static constexpr int kCounterWords = 1024;
   DevArr<unsigned int> counter;
+  std::mutex counter_mu;
+  std::unordered_map<cudaStream_t, int> counter_of;
+  int counter_next = 0;
+  unsigned int* counter_for(cudaStream_t st) {
+    std::lock_guard<std::mutex> lk(counter_mu);
+    auto it = counter_of.find(st);
+    if (it == counter_of.end()) {
+      if (counter_of.size() >= static_cast<size_t>(kCounterWords)) counter_of.clear();
+      it = counter_of.emplace(st, counter_next).first;
+      counter_next = (counter_next + 1) % kCounterWords;
+    }
+    return counter.p + it->second;
+  }
   DevArr<float2> den_rcp;      // {max(env, eps), refined reciprocal}: division table of the fused kernel 2+3
   bool generic = false;        // any-size kernels (k_generic.cu): nfft outside the register-FFT set, or hop % 4 != 0
   int k1_scrub = 0;            // kernel-1 clean-up mode (kernels.h)
@@ -364,7 +384,7 @@ int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out) {
   CU(upload_cpx(p->tw1, T.tw1));
   CU(upload_cpx(p->sa, T.sa));
   if (!T.pre.empty()) CU(upload_cpx(p->pre, T.pre));
-  CU(p->counter.alloc(4));
+  CU(p->counter.alloc(crlot_plan_s::kCounterWords));
   p->d.analysis_window = p->d.ola_window = p->d.push_window = p->d.envelope = nullptr;  // not retained
   *out = p.release();
   return CRLOT_OK;
@@ -423,7 +443,7 @@ int crlot_stft_execute(crlot_plan_t plan, const float* d_signal, long long chan_
   k.nfft = plan->d.nfft; k.hop = plan->d.hop;
   k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
   k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p;
-  k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
+  k.counter = plan->counter_for(static_cast<cudaStream_t>(stream)); k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
   k.generic = plan->generic;
   CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
@@ -475,7 +495,7 @@ int crlot_stft_execute_framequeue(crlot_plan_t plan, const float* d_signal, long
   k.nfft = plan->d.nfft; k.hop = plan->d.hop;
   k.spec = static_cast<cpx*>(d_spec); k.spec_chan_rows = n_frames;
   k.window = plan->win_a.p; k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p;
-  k.counter = plan->counter.p; k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
+  k.counter = plan->counter_for(static_cast<cudaStream_t>(stream)); k.chunk_steps = 64; k.scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
   k.generic = plan->generic;
   CU(launch_stft_fwd(k, static_cast<cudaStream_t>(stream)));
   return CRLOT_OK;
@@ -512,13 +532,13 @@ int crlot_ola_accumulate(crlot_plan_t plan, const float* d_frames, long long fra
   return CRLOT_OK;
 }
 
-static void fill_k23(K23Params& k, crlot_plan_t plan, int counter_word) {
+static void fill_k23(K23Params& k, crlot_plan_t plan, cudaStream_t st) {
   k.nfft = plan->d.nfft; k.hop = plan->d.hop;
   k.window = plan->syn_active ? plan->win_s.p : plan->win_ones.p;
   k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
   k.gain = plan->d.gain; k.eps = plan->d.eps; k.norm = plan->env.p; k.ring_len = static_cast<long long>(plan->ring_len);
   k.den_rcp = plan->den_rcp.p;
-  k.counter = plan->counter.p + counter_word; k.chunk_blocks = 0;
+  k.counter = plan->counter_for(st); k.chunk_blocks = 0;
   k.sgain = plan->sgain; k.sgain_row_stride = plan->sgain_row_stride;
 }
 
@@ -552,7 +572,7 @@ int crlot_istft_ola_execute(crlot_plan_t plan, const void* d_spec, long long spe
                 "even offsets/strides; use crlot_istft_execute + crlot_ola_accumulate");
   DeviceGuard g(plan->d.device);
   K23Params k{};
-  fill_k23(k, plan, 2);
+  fill_k23(k, plan, static_cast<cudaStream_t>(stream));
   k.spec = static_cast<const cpx*>(d_spec); k.spec_chan_rows = spec_chan_rows; k.frames_per_chan = frames_per_chan;
   k.channels = channels; k.t_offset = t_offset; k.frame_t0 = frame_t0; k.out = d_out; k.out_chan_stride = out_chan_stride;
   k.n_out = n_out;
@@ -613,7 +633,7 @@ static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long c
     }
     plan->slot_frames = slab_frames; plan->slot_group = G; plan->slot_aos = aos;
   }
-  // kernel 1 of a slot resets its work counter on its own stream: one counter word per slot
+  // every slot launches on its own stream, hence with its own work-counter word (crlot_plan_s::counter_for)
   int it = 0;
   for (int c = 0; c < (aos ? 1 : channels); ++c) {
     const float* xin = h_in + static_cast<long long>(c) * chan_stride;
@@ -635,13 +655,13 @@ static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long c
       K1Params k1{};
       k1.sig = s.in.p; k1.chan_stride = G > 1 ? ist : 0; k1.len = s1 - s0; k1.channels = G; k1.frames = nf; k1.nfft = N; k1.hop = H;
       k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p;
-      k1.pre = plan->pre.p; k1.counter = plan->counter.p + (it & 1); k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2;
+      k1.pre = plan->pre.p; k1.counter = plan->counter_for(s.stream); k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2;
       k1.generic = plan->generic;
       CU(launch_stft_fwd(k1, s.stream));
       const long long row0 = static_cast<long long>(c) * F + k_lo;     // first spectrum row of the slab (planar mode)
       if (fused) {
         K23Params k{};
-        fill_k23(k, plan, 2 + (it & 1));
+        fill_k23(k, plan, s.stream);
         k.spec = s.spec.p; k.spec_chan_rows = nf; k.frames_per_chan = nf; k.channels = G; k.t_offset = t0;
         k.frame_t0 = s0 - t0; k.out = s.out.p; k.out_chan_stride = G > 1 ? ost : 0; k.n_out = t1 - t0;
         if (k.sgain) k.sgain += (G > 1 ? 0 : row0) * k.sgain_row_stride;

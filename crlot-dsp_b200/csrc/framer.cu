@@ -61,6 +61,12 @@ struct crlot_framer_s {
   size_t stage_floats = 0;
   // the reference's own cursors/capacity in interleaved samples (buffer_size() parity only)
   size_t ref_size = 0, ref_r = 0, ref_w = 0;
+  // Stream ordering: push()/pop() run on the legacy default stream, push_device()/stft() on the caller's, which
+  // may be non-blocking.  Every operation that touches the store first makes its stream wait for the event the
+  // previous operation recorded (order_after_last) and records its own on completion (mark_done), so that e.g. the
+  // compaction of ensure_room never overwrites samples a kernel 1 launched earlier on another stream still reads.
+  cudaEvent_t ev = nullptr;
+  bool ev_pending = false;
 };
 
 // the library-wide last-error slot lives in capi.cu
@@ -91,6 +97,16 @@ struct Dev {
 };
 
 long long round_up4(long long v) { return (v + 3) & ~3LL; }
+
+int order_after_last(crlot_framer_s* f, cudaStream_t st) {
+  if (f->ev_pending) FCU(cudaStreamWaitEvent(st, f->ev, 0));
+  return CRLOT_OK;
+}
+int mark_done(crlot_framer_s* f, cudaStream_t st) {
+  FCU(cudaEventRecord(f->ev, st));
+  f->ev_pending = true;
+  return CRLOT_OK;
+}
 
 // ref: Framer::calculate_available_frames, framer.cc:88-118 (per-channel sample units)
 size_t available_now(const crlot_framer_s* f) {
@@ -201,7 +217,8 @@ int crlot_framer_create(size_t frame_size, size_t hop_size, size_t channels, int
   Dev g(device);
   f->cap = round_up4((long long)frame_size * 2);
   cudaError_t e = cudaMalloc(&f->buf, (size_t)f->cap * channels * sizeof(float));
-  if (e != cudaSuccess) { delete f; return ffail_cuda(e, "cudaMalloc"); }
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->ev, cudaEventDisableTiming);
+  if (e != cudaSuccess) { if (f->buf) cudaFree(f->buf); delete f; return ffail_cuda(e, "cudaMalloc"); }
   ref_reset(f);
   *out = f;
   return CRLOT_OK;
@@ -210,6 +227,8 @@ int crlot_framer_create(size_t frame_size, size_t hop_size, size_t channels, int
 int crlot_framer_destroy(crlot_framer_t f) {
   if (!f) return CRLOT_OK;
   Dev g(f->device);
+  if (f->ev_pending) cudaEventSynchronize(f->ev);
+  if (f->ev) cudaEventDestroy(f->ev);
   if (f->buf) cudaFree(f->buf);
   if (f->stage) cudaFree(f->stage);
   delete f;
@@ -229,7 +248,9 @@ int crlot_framer_push(crlot_framer_t f, const float* h_interleaved, size_t frame
   if (frames == 0) return CRLOT_OK;
   Dev g(f->device);
   cudaStream_t st = nullptr;
-  int rc = ensure_room(f, (long long)frames, st);
+  int rc = order_after_last(f, st);
+  if (rc) return rc;
+  rc = ensure_room(f, (long long)frames, st);
   if (rc) return rc;
   if (f->C == 1) {
     FCU(cudaMemcpyAsync(f->buf + f->w, h_interleaved, frames * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -243,6 +264,7 @@ int crlot_framer_push(crlot_framer_t f, const float* h_interleaved, size_t frame
     FCU(cudaGetLastError());
   }
   FCU(cudaStreamSynchronize(st));     // the caller may reuse its host buffer on return, like std::copy
+  f->ev_pending = false;              // everything issued so far has completed
   f->w += (long long)frames;
   ref_push(f, frames * f->C);
   return CRLOT_OK;
@@ -255,10 +277,14 @@ int crlot_framer_push_device(crlot_framer_t f, const float* d_planar, long long 
   if (frames == 0) return CRLOT_OK;
   Dev g(f->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int rc = ensure_room(f, (long long)frames, st);
+  int rc = order_after_last(f, st);
+  if (rc) return rc;
+  rc = ensure_room(f, (long long)frames, st);
   if (rc) return rc;
   FCU(cudaMemcpy2DAsync(f->buf + f->w, f->cap * sizeof(float), d_planar, chan_stride * sizeof(float),
                         frames * sizeof(float), f->C, cudaMemcpyDeviceToDevice, st));
+  rc = mark_done(f, st);
+  if (rc) return rc;
   f->w += (long long)frames;
   ref_push(f, frames * f->C);
   return CRLOT_OK;
@@ -273,6 +299,10 @@ int crlot_framer_pop(crlot_framer_t f, float* h_out_frame, int* popped) {
   if (available_now(f) == 0) return CRLOT_OK;               // framer.cc:129-131 -> false
   Dev g(f->device);
   cudaStream_t st = nullptr;
+  {
+    const int rc0 = order_after_last(f, st);
+    if (rc0) return rc0;
+  }
   const long long avail = std::min<long long>(f->w - f->r, (long long)f->N);
   if (f->C == 1) {
     FCU(cudaMemcpyAsync(h_out_frame, f->buf + f->r, (size_t)avail * sizeof(float), cudaMemcpyDeviceToHost, st));
@@ -308,12 +338,16 @@ int crlot_framer_stft(crlot_framer_t f, crlot_plan_t plan, long long max_frames,
   if (k == 0) return CRLOT_OK;
   if (!d_spec) return ffail(CRLOT_ERR_INVALID_ARGUMENT, "null spectra buffer");
   Dev g(f->device);
+  rc = order_after_last(f, static_cast<cudaStream_t>(stream));
+  if (rc) return rc;
   if (f->r & 3) {                                           // after a clamped ZERO_PAD tail: re-base once
     rc = realign(f, static_cast<cudaStream_t>(stream));
     if (rc) return rc;
   }
   // frame j of channel c = buf[c*cap + r + j*H + (0..N)), zero at and beyond (w - r): kernel 1's contract
   rc = crlot_stft_execute(plan, f->buf + f->r, f->cap, f->w - f->r, (int)f->C, k, d_spec, stream);
+  if (rc) return rc;
+  rc = mark_done(f, static_cast<cudaStream_t>(stream));
   if (rc) return rc;
   for (long long j = 0; j < k; ++j) {                       // cursor arithmetic of k pops, O(k) integers
     f->r = std::min(f->r + (long long)f->H, f->w);

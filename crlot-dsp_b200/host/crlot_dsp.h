@@ -8,6 +8,8 @@
 //   dsp::fft::FftDomain / FftPlanDesc / IFftPlan / MakeFftPlan
 //                                                   ref: dsp/fft/api/fft_api.h:9-51
 //   dsp::OLAConfig / dsp::OLAAccumulator            ref: dsp/ola/OLAAccumulator.h:15-164
+//   dsp::ola::build_norm_linear                     ref: dsp/ola/norm_builder.h:27-28
+//   dsp::base::Span / dsp::ring::RingBuffer<T>      ref: dsp/base/span.h:11-33, dsp/ring/ring_buffer.h:25-110
 // so that code written against the reference (bench/e2e_benchmark.cc:138-186, tests/*.cc) compiles
 // against this header unchanged.  Nothing here computes on the CPU: every method forwards to the
 // C-ABI, whose compute entry points launch sm_100a kernels or fail (no fallback).
@@ -20,11 +22,19 @@
 #include <complex>
 #include <cstddef>
 #include <cstdint>
+#include <limits>
+#include <map>
 #include <memory>
+#include <mutex>
 #include <new>
 #include <stdexcept>
 #include <string>
+#include <thread>
+#include <tuple>
+#include <type_traits>
+#include <utility>
 #include <vector>
+#include <cmath>
 
 #include "../../include/crlot_cuda.h"
 
@@ -168,22 +178,65 @@ class WindowLUT {
  public:
   WindowLUT(size_t nfft, WindowType type, bool periodic = false, NormalizationType norm = NormalizationType::NONE)
       : size_(nfft), type_(type), periodic_(periodic), norm_(norm) {
+    if (nfft == 0) throw std::invalid_argument("Window size must be greater than 0");
     data_ = make(type, nfft, periodic, norm);
   }
   WindowLUT() = default;
+  WindowLUT(const WindowLUT&) = delete;
+  WindowLUT& operator=(const WindowLUT&) = delete;
 
-  const float* data() const { return data_.get(); }
+  const float* data() const {
+    if (!data_) throw std::runtime_error("Window data not initialized");      // ref: WindowLUT.cc:63-68
+    return data_.get();
+  }
   size_t size() const { return data_ ? size_ : 0; }
   WindowType type() const { return data_ ? type_ : WindowType::HANN; }
   bool periodic() const { return data_ ? periodic_ : false; }
   NormalizationType normalization() const { return data_ ? norm_ : NormalizationType::NONE; }
 
-  // The reference memoises tables process-wide behind a mutex and a generation counter
-  // (WindowLUT.cc:60-165).  A table here is a few KB built once per plan and then resident on the
-  // device, so GetWindowSafe simply builds and hands out ownership.
+  // Process-wide memo of tables behind a mutex and a generation counter, as the reference's
+  // (WindowLUT.cc:60-165): a hit hands out shared ownership of the cached table, clearCache() bumps the
+  // generation so that older entries are rebuilt on their next request while outstanding references stay valid.
   std::shared_ptr<const float> GetWindowSafe(WindowType type, size_t N, bool periodic = false,
                                              NormalizationType norm = NormalizationType::NONE) {
-    return make(type, N, periodic, norm);
+    if (N == 0) throw std::invalid_argument("Window size must be greater than 0");
+    const Key key{static_cast<int>(type), N, periodic, static_cast<int>(norm)};
+    std::lock_guard<std::mutex> lock(cache_mutex_);
+    auto it = safe_cache_.find(key);
+    if (it != safe_cache_.end() && it->second.second == generation_) return it->second.first;
+    auto p = make(type, N, periodic, norm);
+    safe_cache_[key] = {p, generation_};
+    return p;
+  }
+  // ref: WindowLUT.h:155-157 (deprecated there as well; valid until clearCache())
+  [[deprecated("Use GetWindowSafe() for thread safety")]]
+  const float* GetWindow(WindowType type, size_t N, bool periodic = false,
+                         NormalizationType norm = NormalizationType::NONE) {
+    if (N == 0) throw std::invalid_argument("Window size must be greater than 0");
+    const Key key{static_cast<int>(type), N, periodic, static_cast<int>(norm)};
+    std::lock_guard<std::mutex> lock(cache_mutex_);
+    auto it = legacy_cache_.find(key);
+    if (it != legacy_cache_.end()) return it->second.get();
+    auto p = make(type, N, periodic, norm);
+    legacy_cache_[key] = p;
+    return p.get();
+  }
+  size_t getCacheSize() const {
+    std::lock_guard<std::mutex> lock(cache_mutex_);
+    return safe_cache_.size() + legacy_cache_.size();
+  }
+  void clearCache(bool force_immediate = false) {
+    std::lock_guard<std::mutex> lock(cache_mutex_);
+    ++generation_;
+    legacy_cache_.clear();
+    if (force_immediate) safe_cache_.clear();
+    else
+      for (auto it = safe_cache_.begin(); it != safe_cache_.end();)
+        it = it->second.second < generation_ ? safe_cache_.erase(it) : std::next(it);
+  }
+  uint64_t getCurrentGeneration() const {
+    std::lock_guard<std::mutex> lock(cache_mutex_);
+    return generation_;
   }
   static WindowLUT& getInstance() {
     static WindowLUT inst;
@@ -199,6 +252,16 @@ class WindowLUT {
     for (size_t i = 0; i < N; ++i) s += static_cast<double>(window[i]) * static_cast<double>(window[i]);
     return s;
   }
+  // ref: WindowLUT.cc:195-206
+  static double calculateRMSError(const float* window1, const float* window2, size_t N) {
+    if (!window1 || !window2 || N == 0) return 0.0;
+    double s = 0.0;
+    for (size_t i = 0; i < N; ++i) {
+      const double d = static_cast<double>(window1[i]) - static_cast<double>(window2[i]);
+      s += d * d;
+    }
+    return std::sqrt(s / static_cast<double>(N));
+  }
 
  private:
   static std::shared_ptr<const float> make(WindowType type, size_t N, bool periodic, NormalizationType norm) {
@@ -206,6 +269,11 @@ class WindowLUT {
     detail::check(crlot_window_make(static_cast<int>(type), N, periodic ? 1 : 0, static_cast<int>(norm), p.get()));
     return p;
   }
+  using Key = std::tuple<int, size_t, bool, int>;
+  mutable std::mutex cache_mutex_;
+  std::map<Key, std::pair<std::shared_ptr<const float>, uint64_t>> safe_cache_;
+  std::map<Key, std::shared_ptr<const float>> legacy_cache_;
+  uint64_t generation_ = 0;
   std::shared_ptr<const float> data_;
   size_t size_ = 0;
   WindowType type_ = WindowType::HANN;
@@ -272,6 +340,116 @@ class OLAAccumulator {
   OLAConfig cfg_;
   crlot_ola_t h_ = nullptr;
 };
+
+// ------------------------------------------------------------------------------------------------
+// dsp::ola free functions: the envelope builder and the kernel-dispatch seam
+// ------------------------------------------------------------------------------------------------
+namespace ola {
+// ref: dsp/ola/norm_builder.h:27-28, norm_builder.cc:8-52 (fp32 adds in the reference's order; host table)
+inline void build_norm_linear(float* norm, const float* window, size_t ring_len, size_t frame_size, size_t hop) {
+  detail::check(crlot_build_norm_linear(norm, window, ring_len, frame_size, hop));
+}
+// B200 extension: the reference's dispatch functions (dsp/ola/kernels.h:28-53) on DEVICE pointers.
+// noexcept like the reference's: a failed launch is reported by crlot_cuda_last_error().
+inline void axpy_device(float* dst, const float* src, float g, size_t n, void* stream = nullptr) noexcept {
+  crlot_axpy(dst, src, g, n, detail::default_device(), stream);
+}
+inline void axpy_windowed_device(float* dst, const float* src, const float* win, float g, size_t n,
+                                 void* stream = nullptr) noexcept {
+  crlot_axpy_windowed(dst, src, win, g, n, detail::default_device(), stream);
+}
+inline void normalize_and_clear_device(float* out, float* acc, const float* norm, float eps, size_t n,
+                                       void* stream = nullptr) noexcept {
+  crlot_normalize_and_clear(out, acc, norm, eps, n, detail::default_device(), stream);
+}
+}  // namespace ola
+
+// ------------------------------------------------------------------------------------------------
+// base::Span, ring::RingBuffer<T>          ref: dsp/base/span.h:11-33, dsp/ring/ring_buffer.h:25-110
+// ------------------------------------------------------------------------------------------------
+namespace base {
+template <typename T>
+class Span {
+ public:
+  Span() : ptr_(nullptr), len_(0) {}
+  Span(T* ptr, size_t len) : ptr_(ptr), len_(len) {}
+  T* data() const { return ptr_; }
+  size_t size() const { return len_; }
+  bool empty() const { return len_ == 0; }
+  T& operator[](size_t index) const { return ptr_[index]; }
+  T* begin() const { return ptr_; }
+  T* end() const { return ptr_ + len_; }
+
+ private:
+  T* ptr_;
+  size_t len_;
+};
+}  // namespace base
+
+namespace ring {
+// The cells live in CUDA unified memory (crlot_ring_*): data() and the spans are valid on the host, as in the
+// reference, and on the device -- kernels launched on data() see the same cells, pages migrating on first touch.
+// Index arithmetic (split / write / shadow_sync / contiguous_read_ptr) is the C-ABI's, i.e. the reference's.
+template <typename T>
+class RingBuffer {
+ public:
+  explicit RingBuffer(size_t capacity, bool shadow = false) {
+    static_assert(std::is_trivially_copyable<T>::value, "Shadow ring requires trivially copyable T");
+    detail::check(crlot_ring_create(capacity, sizeof(T), shadow ? 1 : 0, detail::default_device(), &h_));
+    buffer_ = static_cast<T*>(crlot_ring_data(h_));
+    capacity_ = capacity;
+    shadow_ = shadow;
+  }
+  ~RingBuffer() { crlot_ring_destroy(h_); }
+  RingBuffer(const RingBuffer&) = delete;
+  RingBuffer& operator=(const RingBuffer&) = delete;
+  RingBuffer(RingBuffer&&) = delete;
+  RingBuffer& operator=(RingBuffer&&) = delete;
+
+  size_t capacity() const noexcept { return capacity_; }
+  size_t physical_capacity() const noexcept { return shadow_ ? capacity_ * 2 : capacity_; }
+  bool has_shadow() const noexcept { return shadow_; }
+  size_t write_pos() const noexcept { return crlot_ring_write_pos(h_); }
+
+  [[nodiscard]] std::pair<base::Span<T>, base::Span<T>> split(size_t start, size_t len) noexcept {
+    crlot_ring_span sp{};
+    crlot_ring_split(h_, start, len, &sp);
+    return {sp.len1 ? base::Span<T>(buffer_ + sp.off1, sp.len1) : base::Span<T>(),
+            sp.len2 ? base::Span<T>(buffer_ + sp.off2, sp.len2) : base::Span<T>()};
+  }
+  [[nodiscard]] std::pair<base::Span<const T>, base::Span<const T>> split(size_t start, size_t len) const noexcept {
+    crlot_ring_span sp{};
+    crlot_ring_split(h_, start, len, &sp);
+    return {sp.len1 ? base::Span<const T>(buffer_ + sp.off1, sp.len1) : base::Span<const T>(),
+            sp.len2 ? base::Span<const T>(buffer_ + sp.off2, sp.len2) : base::Span<const T>()};
+  }
+  void shadow_sync(size_t bytes) { detail::check(crlot_ring_shadow_sync(h_, bytes)); }
+  T* contiguous_read_ptr(size_t read_pos) noexcept { return buffer_ + crlot_ring_contiguous_offset(h_, read_pos); }
+  const T* contiguous_read_ptr(size_t read_pos) const noexcept { return buffer_ + crlot_ring_contiguous_offset(h_, read_pos); }
+  T* data() noexcept { return buffer_; }
+  const T* data() const noexcept { return buffer_; }
+  size_t write(const T* src, size_t n) {
+    size_t written = 0;
+    detail::check(crlot_ring_write(h_, src, n, &written));
+    return written;
+  }
+
+  // ---- B200 extension --------------------------------------------------------------------------
+  crlot_ring_t handle() const { return h_; }
+  size_t write_device(const T* d_src, size_t n, void* stream = nullptr) {
+    size_t written = 0;
+    detail::check(crlot_ring_write_device(h_, d_src, n, &written, stream));
+    return written;
+  }
+  void prefetch(bool to_device, void* stream = nullptr) { detail::check(crlot_ring_prefetch(h_, to_device ? 1 : 0, stream)); }
+
+ private:
+  crlot_ring_t h_ = nullptr;
+  T* buffer_ = nullptr;
+  size_t capacity_ = 0;
+  bool shadow_ = false;
+};
+}  // namespace ring
 
 // ------------------------------------------------------------------------------------------------
 // FFT plan API
@@ -388,6 +566,78 @@ class StftRoundTrip {
  private:
   crlot_plan_t plan_ = nullptr;
   int n_ = 0, h_ = 0, mode_ = CRLOT_DROP;
+};
+
+// ------------------------------------------------------------------------------------------------
+// B200 extension: one long signal time-sharded over the GPUs of a box (csrc/shard.cu).
+// One object per rank (one process per GPU, or one thread per GPU): it owns the rank's plan, its
+// [left halo | owned | right halo] input buffer, workspaces and output slice, all device-resident.
+//   ShardedRoundTrip rt(total_len, N, H, w, w, rank, world, group);
+//   rt.load_owned(host_samples_of_this_rank);   // or fill rt.owned_device_ptr() on the device
+//   rt.execute();                               // NCCL halo exchange + K1 + fused K2+K3
+//   rt.read_output(host_out);                   // output samples [t0, t1) of the whole run
+// The concatenation over ranks is bit-identical to StftRoundTrip on the whole signal.
+// ------------------------------------------------------------------------------------------------
+class ShardedRoundTrip {
+ public:
+  ShardedRoundTrip(size_t total_len, size_t frame_size, size_t hop_size, const float* analysis_window,
+                   const float* ola_window, int rank, int world, crlot_shard_group_t group,
+                   BoundaryMode mode = BoundaryMode::DROP, int device = -1, bool materialise_frames = false)
+      : group_(group), device_(device < 0 ? detail::default_device() : device) {
+    detail::check(crlot_shard_plan((long long)total_len, (int)frame_size, (int)hop_size, rank, world,
+                                   mode == BoundaryMode::DROP ? CRLOT_DROP : CRLOT_ZERO_PAD, &sh_));
+    crlot_stft_desc d{};
+    d.nfft = (int)frame_size; d.hop = (int)hop_size; d.boundary_mode = sh_.boundary_mode;
+    d.analysis_window = analysis_window; d.ola_window = ola_window; d.apply_window_inside = 1;
+    d.gain = 1.0f; d.eps = 1e-8f; d.scrub = 1; d.device = device_;
+    detail::check(crlot_stft_plan_create(&d, &plan_));
+    const size_t bins = frame_size / 2 + 1;
+    const size_t own = (size_t)(sh_.own_hi - sh_.own_lo);
+    // kernel 1 wants the buffer start 16-byte aligned (cudaMalloc gives 256); 16 floats of slack at the end
+    detail::check(crlot_buf_create((pad_ + (size_t)sh_.left_halo + own + (size_t)sh_.right_halo + 16) * sizeof(float), device_, &x_));
+    detail::check(crlot_buf_zero(x_, 0, crlot_buf_bytes(x_), nullptr));
+    detail::check(crlot_buf_create(std::max<size_t>((size_t)sh_.n_frames * bins * 2 * sizeof(float), 8), device_, &spec_));
+    if (materialise_frames)
+      detail::check(crlot_buf_create(std::max<size_t>((size_t)sh_.n_frames * frame_size * sizeof(float), 8), device_, &frames_));
+    detail::check(crlot_buf_create(std::max<size_t>((size_t)sh_.n_out * sizeof(float), 8), device_, &out_));
+  }
+  ~ShardedRoundTrip() {
+    crlot_buf_destroy(x_); crlot_buf_destroy(spec_); crlot_buf_destroy(frames_); crlot_buf_destroy(out_);
+    crlot_stft_plan_destroy(plan_);
+  }
+  ShardedRoundTrip(const ShardedRoundTrip&) = delete;
+  ShardedRoundTrip& operator=(const ShardedRoundTrip&) = delete;
+
+  const crlot_time_shard& shard() const { return sh_; }
+  float* xbuf_device_ptr() const { return static_cast<float*>(crlot_buf_device_ptr(x_)) + pad_; }
+  float* owned_device_ptr() const { return xbuf_device_ptr() + sh_.left_halo; }
+  float* output_device_ptr() const { return static_cast<float*>(crlot_buf_device_ptr(out_)); }
+  void* spectra_device_ptr() const { return crlot_buf_device_ptr(spec_); }
+  // host samples [own_lo, own_hi) of the signal
+  void load_owned(const float* host) {
+    detail::check(crlot_buf_upload(x_, (pad_ + (size_t)sh_.left_halo) * sizeof(float), host,
+                                   (size_t)(sh_.own_hi - sh_.own_lo) * sizeof(float), nullptr));
+  }
+  void execute(void* stream = nullptr) {
+    detail::check(crlot_sharded_roundtrip_execute(plan_, group_, &sh_, xbuf_device_ptr(), crlot_buf_device_ptr(spec_),
+                                                  frames_ ? static_cast<float*>(crlot_buf_device_ptr(frames_)) : nullptr,
+                                                  output_device_ptr(), stream));
+  }
+  // output samples [t0, t1) of the whole run -> host (synchronises)
+  size_t read_output(float* host, void* stream = nullptr) {
+    detail::check(crlot_buf_download(out_, 0, host, (size_t)sh_.n_out * sizeof(float), stream));
+    detail::check(crlot_cuda_stream_sync(device_, stream));
+    return (size_t)sh_.n_out;
+  }
+  crlot_plan_t plan() const { return plan_; }
+
+ private:
+  crlot_time_shard sh_{};
+  crlot_shard_group_t group_ = nullptr;
+  int device_ = 0;
+  size_t pad_ = 0;
+  crlot_plan_t plan_ = nullptr;
+  crlot_buf_t x_ = nullptr, spec_ = nullptr, frames_ = nullptr, out_ = nullptr;
 };
 
 }  // namespace dsp

@@ -1,17 +1,25 @@
 // facade_test.cc -- exercises the reference-named C++ classes of crlot_dsp.h on a B200, in the
 // shape of the reference's own gtest cases (gtest is not in this image, so plain CHECKs):
 //   tests/framer_test.cc:100-322, tests/window_lut_test.cc:85-215, tests/fft_test.cc:57-250,
-//   tests/ola_accumulator_test.cc:143-330, tests/frame_queue_test.cc:30-420, and the loop of
-//   bench/e2e_benchmark.cc:138-186.
+//   tests/ola_accumulator_test.cc:143-330, tests/frame_queue_test.cc:30-420,
+//   tests/ring_buffer_test.cc:14-234, tests/norm_builder_test.cc:13-167, tests/kernels_test.cc:67-208 (on
+//   device pointers), and the loop of bench/e2e_benchmark.cc:138-186.
 // It does not link the oracle.  Arrays it produces are written to <outdir>/*.f32 so that
 // tests/test_gpu_facades_cpp.py can compare them with the oracle on the same inputs.
 //
 //   usage: facade_test <outdir>
+#include <algorithm>
 #include <cmath>
 #include <complex>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <limits>
 #include <string>
+#include <thread>
+#include <tuple>
+#include <type_traits>
+#include <utility>
 #include <vector>
 
 #include "crlot_dsp.h"
@@ -546,7 +554,351 @@ static void test_wav_interleaved() {
   CHECK(!bad.open(g_out + "/does_not_exist.wav") && !bad.is_open() && bad.get_channels() == 0);
 }
 
+
+// ---- RingBuffer (tests/ring_buffer_test.cc:14-234; bodies as there, gtest macros replaced) --------
+#define EXPECT_EQ(a, b) CHECK((a) == (b))
+#define EXPECT_TRUE(a) CHECK(a)
+#define EXPECT_THROW(expr, extype) CHECK_THROWS(expr, extype)
+static void test_ring_buffer() {
+  using dsp::ring::RingBuffer;
+  {  // Constructor :14-18, ConstructorWithShadow :20-23
+    RingBuffer<float> rb(1024);
+    EXPECT_EQ(rb.capacity(), 1024u);
+    EXPECT_EQ(rb.write_pos(), 0u);
+    RingBuffer<float> rs(512, true);
+    EXPECT_EQ(rs.capacity(), 512u);
+    EXPECT_EQ(rs.physical_capacity(), 1024u);
+    EXPECT_TRUE(rs.has_shadow());
+  }
+  {  // SplitNoWrapAround :25-43
+    RingBuffer<int> rb(10);
+    for (size_t i = 0; i < 10; ++i) rb.data()[i] = static_cast<int>(i);
+    auto [span1, span2] = rb.split(2, 5);
+    EXPECT_EQ(span1.size(), 5u);
+    EXPECT_TRUE(span2.empty());
+    for (size_t i = 0; i < 5; ++i) EXPECT_EQ(span1[i], static_cast<int>(i + 2));
+  }
+  {  // SplitWithWrapAround :45-68
+    RingBuffer<int> rb(10);
+    for (size_t i = 0; i < 10; ++i) rb.data()[i] = static_cast<int>(i);
+    auto [span1, span2] = rb.split(7, 5);
+    EXPECT_EQ(span1.size(), 3u);
+    EXPECT_EQ(span2.size(), 2u);
+    EXPECT_EQ(span1[0], 7); EXPECT_EQ(span1[1], 8); EXPECT_EQ(span1[2], 9);
+    EXPECT_EQ(span2[0], 0); EXPECT_EQ(span2[1], 1);
+  }
+  {  // SplitEmpty :70-76
+    RingBuffer<int> rb(10);
+    auto [span1, span2] = rb.split(5, 0);
+    EXPECT_TRUE(span1.empty());
+    EXPECT_TRUE(span2.empty());
+  }
+  {  // SplitFullBuffer :78-95, SplitWrapAroundFullBuffer :97-117, SplitStartBeyondCapacity :119-137
+    RingBuffer<int> rb(5);
+    for (size_t i = 0; i < 5; ++i) rb.data()[i] = static_cast<int>(i);
+    {
+      auto [span1, span2] = rb.split(0, 5);
+      EXPECT_EQ(span1.size(), 5u);
+      EXPECT_TRUE(span2.empty());
+      for (size_t i = 0; i < 5; ++i) EXPECT_EQ(span1[i], static_cast<int>(i));
+    }
+    {
+      auto [span1, span2] = rb.split(3, 5);
+      EXPECT_EQ(span1.size(), 2u);
+      EXPECT_EQ(span2.size(), 3u);
+      EXPECT_EQ(span1[0], 3); EXPECT_EQ(span1[1], 4);
+      EXPECT_EQ(span2[0], 0); EXPECT_EQ(span2[1], 1); EXPECT_EQ(span2[2], 2);
+    }
+    {
+      auto [span1, span2] = rb.split(7, 3);     // 7 % 5 = 2
+      EXPECT_EQ(span1.size(), 3u);
+      EXPECT_TRUE(span2.empty());
+      EXPECT_EQ(span1[0], 2); EXPECT_EQ(span1[1], 3); EXPECT_EQ(span1[2], 4);
+    }
+    {  // LargeLenClamping :221-234
+      auto [span1, span2] = rb.split(0, 10);
+      EXPECT_EQ(span1.size() + span2.size(), 5u);
+      EXPECT_EQ(span1.size(), 5u);
+      EXPECT_TRUE(span2.empty());
+    }
+  }
+  {  // SplitSpansConcatenation :139-176
+    RingBuffer<int> rb(8);
+    for (size_t i = 0; i < 8; ++i) rb.data()[i] = static_cast<int>(i * 10);
+    std::vector<std::pair<size_t, size_t>> test_cases = {{0, 3}, {5, 4}, {6, 5}, {2, 8}};
+    for (const auto& [start, len] : test_cases) {
+      auto [span1, span2] = rb.split(start, len);
+      std::vector<int> concatenated;
+      for (size_t i = 0; i < span1.size(); ++i) concatenated.push_back(span1[i]);
+      for (size_t i = 0; i < span2.size(); ++i) concatenated.push_back(span2[i]);
+      EXPECT_EQ(concatenated.size(), len);
+      for (size_t i = 0; i < len; ++i) EXPECT_EQ(concatenated[i], static_cast<int>(((start + i) % 8) * 10));
+    }
+  }
+  {  // ShadowSyncStub :178-182
+    RingBuffer<float> rb(100);
+    CHECK_NOTHROW(rb.shadow_sync(50));
+  }
+  {  // ConstSplitReturnsConstSpans :184-206
+    RingBuffer<int> rb(10);
+    for (size_t i = 0; i < 10; ++i) rb.data()[i] = static_cast<int>(i);
+    const RingBuffer<int>& const_rb = rb;
+    auto [span1, span2] = const_rb.split(2, 5);
+    static_assert(std::is_same_v<decltype(span1), dsp::base::Span<const int>>);
+    static_assert(std::is_same_v<decltype(span2), dsp::base::Span<const int>>);
+    EXPECT_EQ(span1.size(), 5u);
+    EXPECT_TRUE(span2.empty());
+    for (size_t i = 0; i < 5; ++i) EXPECT_EQ(span1[i], static_cast<int>(i + 2));
+  }
+  {  // OverflowProtection :208-217, ZeroCapacityThrows :219-221, NoexceptMethods :236-244
+    RingBuffer<int> rb(10);
+    auto [span1, span2] = rb.split(0, std::numeric_limits<size_t>::max());
+    EXPECT_EQ(span1.size() + span2.size(), 10u);
+    EXPECT_THROW(RingBuffer<int>(0), std::invalid_argument);
+    static_assert(noexcept(rb.capacity()));
+    static_assert(noexcept(rb.write_pos()));
+    static_assert(noexcept(rb.data()));
+    static_assert(noexcept(std::as_const(rb).data()));
+  }
+  {  // write(): wrap + shadow mirror (ring_buffer.cc:166-205), contiguous_read_ptr (:144-163)
+    RingBuffer<float> rb(8, true);
+    std::vector<float> a = {1, 2, 3, 4, 5, 6}, b = {7, 8, 9, 10, 11};
+    EXPECT_EQ(rb.write(a.data(), a.size()), 6u);
+    EXPECT_EQ(rb.write_pos(), 6u);
+    EXPECT_EQ(rb.write(b.data(), b.size()), 5u);           // 2 in the tail, 3 wrap to the head
+    EXPECT_EQ(rb.write_pos(), 3u);
+    const float want[8] = {9, 10, 11, 4, 5, 6, 7, 8};
+    bool ok = true;
+    for (int i = 0; i < 8; ++i) ok = ok && rb.data()[i] == want[i];
+    CHECK(ok);
+    ok = true;
+    for (int i = 0; i < 3; ++i) ok = ok && rb.data()[8 + i] == want[i];    // mirrored head
+    CHECK(ok);
+    const float* c = rb.contiguous_read_ptr(6);            // window [6, 6+5) is contiguous through the mirror
+    CHECK(c == rb.data() + 6 && c[0] == 7 && c[1] == 8 && c[2] == 9 && c[3] == 10 && c[4] == 11);
+    EXPECT_EQ(rb.write(nullptr, 4), 0u);
+    EXPECT_EQ(rb.write(a.data(), 0), 0u);
+    RingBuffer<float> plain(8);
+    CHECK(plain.contiguous_read_ptr(13) == plain.data() + 5);
+    // the cells are device memory too: the device-pointer seam functions operate on data() directly
+    std::vector<float> ones(8, 1.0f);
+    plain.write(ones.data(), 8);
+    RingBuffer<float> src(8), nrm(8), out(8);
+    for (int i = 0; i < 8; ++i) { src.data()[i] = float(i); nrm.data()[i] = i < 4 ? 2.0f : 0.0f; }
+    dsp::ola::axpy_device(plain.data(), src.data(), 0.5f, 8);                  // 1 + i/2
+    dsp::ola::normalize_and_clear_device(out.data(), plain.data(), nrm.data(), 0.25f, 8);
+    CHECK(crlot_cuda_stream_sync(0, nullptr) == CRLOT_OK);
+    ok = true;
+    for (int i = 0; i < 8; ++i) ok = ok && out.data()[i] == (1.0f + 0.5f * i) / (i < 4 ? 2.0f : 0.25f) && plain.data()[i] == 0.0f;
+    CHECK(ok);
+  }
+}
+
+// ---- build_norm_linear (tests/norm_builder_test.cc:13-167) ----------------------------------------
+static void build_norm_scalar(float* norm, const float* window, size_t ring_len, int frame_size, int hop) {   // :17-47
+  std::fill(norm, norm + ring_len, 0.0f);
+  for (size_t ring_pos = 0; ring_pos < ring_len; ++ring_pos) {
+    float overlap_sum = 0.0f;
+    int min_offset = -static_cast<int>(std::ceil(static_cast<double>(frame_size) / hop));
+    int max_offset = static_cast<int>(std::ceil(static_cast<double>(ring_len + frame_size - 1) / hop));
+    for (int frame_offset = min_offset; frame_offset <= max_offset; ++frame_offset) {
+      int64_t frame_start = static_cast<int64_t>(frame_offset) * hop;
+      for (int t = 0; t < frame_size; ++t) {
+        int64_t sample_pos = frame_start + t;
+        size_t mapped_pos = static_cast<size_t>(sample_pos % static_cast<int64_t>(ring_len));
+        if (sample_pos < 0) {
+          mapped_pos = ring_len - (static_cast<size_t>(-sample_pos) % ring_len);
+          if (mapped_pos == ring_len) mapped_pos = 0;
+        }
+        if (mapped_pos == ring_pos) overlap_sum += window[t];
+      }
+    }
+    norm[ring_pos] = std::max(overlap_sum, 1e-8f);
+  }
+}
+static void test_norm_builder() {
+  using dsp::ola::build_norm_linear;
+  std::vector<std::tuple<int, int, size_t>> cases = {{256, 64, 1024}, {128, 32, 512}, {512, 128, 2048}, {64, 16, 256}, {1024, 256, 4096}};
+  for (auto [frame_size, hop, ring_len] : cases) {      // BasicAccuracy :50-74, ParameterCombinations :77-110
+    std::vector<float> window(frame_size);
+    for (int i = 0; i < frame_size; ++i) window[i] = 0.5f * (1.0f - std::cos(2.0f * M_PI * i / (frame_size - 1)));
+    std::vector<float> norm_linear(ring_len), norm_scalar(ring_len);
+    build_norm_linear(norm_linear.data(), window.data(), ring_len, frame_size, hop);
+    build_norm_scalar(norm_scalar.data(), window.data(), ring_len, frame_size, hop);
+    double max_error = 0.0;
+    for (size_t i = 0; i < ring_len; ++i) max_error = std::max(max_error, (double)std::abs(norm_linear[i] - norm_scalar[i]));
+    CHECK(max_error < 1e-5);
+  }
+  {  // EdgeCases :113-131 (rectangular window)
+    std::vector<float> window(128, 1.0f), a(256), b(256);
+    build_norm_linear(a.data(), window.data(), 256, 128, 32);
+    build_norm_scalar(b.data(), window.data(), 256, 128, 32);
+    bool ok = true;
+    for (size_t i = 0; i < 256; ++i) ok = ok && std::abs(a[i] - b[i]) <= 1e-5f;
+    CHECK(ok);
+  }
+  {  // MinimumValueGuarantee :134-152
+    std::vector<float> window(256, 1e-10f), norm(1024);
+    build_norm_linear(norm.data(), window.data(), 1024, 256, 256);
+    bool ok = true;
+    for (float v : norm) ok = ok && v >= 1e-10f;
+    CHECK(ok);
+  }
+  // WindowLUT extras the reference's callers use (WindowLUT.h:146-199)
+  auto& lut = WindowLUT::getInstance();
+  lut.clearCache(true);
+  auto p1 = lut.GetWindowSafe(WindowType::HANN, 256);
+  auto p2 = lut.GetWindowSafe(WindowType::HANN, 256);
+  CHECK(p1.get() == p2.get() && lut.getCacheSize() == 1);
+  const uint64_t g0 = lut.getCurrentGeneration();
+  lut.clearCache();
+  CHECK(lut.getCurrentGeneration() == g0 + 1 && p1.get()[128] > 0.99f);     // outstanding references stay valid
+  auto p3 = lut.GetWindowSafe(WindowType::HANN, 256, true);
+  CHECK(WindowLUT::calculateRMSError(p1.get(), p1.get(), 256) == 0.0);
+  CHECK(WindowLUT::calculateRMSError(p1.get(), p3.get(), 256) > 0.0);
+  CHECK(WindowLUT::calculateRMSError(nullptr, p3.get(), 256) == 0.0);
+#pragma GCC diagnostic push
+#pragma GCC diagnostic ignored "-Wdeprecated-declarations"
+  const float* legacy = lut.GetWindow(WindowType::HAMMING, 64);
+  CHECK(legacy == lut.GetWindow(WindowType::HAMMING, 64) && std::abs(legacy[0] - 0.08f) < 1e-6f);
+  CHECK_THROWS(lut.GetWindow(WindowType::HANN, 0), std::invalid_argument);
+#pragma GCC diagnostic pop
+  CHECK_THROWS(lut.GetWindowSafe(WindowType::HANN, 0), std::invalid_argument);
+  CHECK_THROWS(WindowLUT(0, WindowType::HANN), std::invalid_argument);
+  CHECK_THROWS(WindowLUT::getInstance().data(), std::runtime_error);
+}
+
+// ---- time-sharded round trip through the C-ABI: world 1, and world 2 (one thread per GPU) when two are visible
+static void test_sharded(int ndev) {
+  const size_t N = 1024, H = 256;
+  const size_t S = 2 * crlot_ola_ring_len(N, H) + 3 * H;
+  WindowLUT hann(N, WindowType::HANN);
+  for (int world : {1, 2, 4}) {
+    const size_t total = world * S;
+    const auto x = noise(total, 77u + world);
+    StftRoundTrip whole(N, H, hann.data(), hann.data(), BoundaryMode::DROP);
+    std::vector<float> want(whole.output_len_for(total));
+    whole.process(x.data(), total, total, 1, want.data(), want.size());
+    // (a) logical ranks on ONE device, halos filled by slicing: needs no communicator
+    std::vector<float> got(want.size(), -1.0f);
+    for (int r = 0; r < world; ++r) {
+      crlot_time_shard sh{};
+      CHECK(crlot_shard_plan((long long)total, (int)N, (int)H, r, world, CRLOT_DROP, &sh) == CRLOT_OK);
+      crlot_buf_t xb = nullptr, sp = nullptr, ob = nullptr;
+      const size_t L = (size_t)(sh.in_hi - sh.in_lo);
+      CHECK(crlot_buf_create((L + 16) * 4, 0, &xb) == CRLOT_OK);
+      CHECK(crlot_buf_create((size_t)sh.n_frames * (N / 2 + 1) * 8, 0, &sp) == CRLOT_OK);
+      CHECK(crlot_buf_create((size_t)sh.n_out * 4, 0, &ob) == CRLOT_OK);
+      CHECK(crlot_buf_upload(xb, 0, x.data() + sh.in_lo, L * 4, nullptr) == CRLOT_OK);
+      crlot_time_shard solo = sh;            // same offsets, no neighbours to talk to
+      solo.world = 1; solo.rank = 0;
+      CHECK(crlot_sharded_roundtrip_execute(whole.plan(), nullptr, &solo, (float*)crlot_buf_device_ptr(xb), crlot_buf_device_ptr(sp),
+                                            nullptr, (float*)crlot_buf_device_ptr(ob), nullptr) == CRLOT_OK);
+      CHECK(crlot_buf_download(ob, 0, got.data() + sh.t0, (size_t)sh.n_out * 4, nullptr) == CRLOT_OK);
+      CHECK(crlot_cuda_stream_sync(0, nullptr) == CRLOT_OK);
+      crlot_buf_destroy(xb); crlot_buf_destroy(sp); crlot_buf_destroy(ob);
+    }
+    CHECK(std::memcmp(got.data(), want.data(), want.size() * 4) == 0);          // bit-identical to the unsharded call
+    if (world == 1) dump("shard_in", x.data(), x.size()), dump("shard_out", want.data(), want.size());
+    // (b) real ranks: one thread per GPU, NCCL halo exchange (ncclCommInitAll)
+    if (world > 1 && ndev >= world) {
+      std::vector<int> devs(world);
+      for (int i = 0; i < world; ++i) devs[i] = i;
+      std::vector<crlot_shard_group_t> groups(world, nullptr);
+      const int rc = crlot_shard_group_create_all(world, devs.data(), groups.data());
+      CHECK(rc == CRLOT_OK);
+      if (rc != CRLOT_OK) { std::printf("  group: %s\n", crlot_cuda_last_error()); continue; }
+      std::vector<float> multi(want.size(), -1.0f);
+      std::vector<int> bad(world, 0);
+      std::vector<std::thread> th;
+      for (int r = 0; r < world; ++r)
+        th.emplace_back([&, r] {
+          try {
+            ShardedRoundTrip rt(total, N, H, hann.data(), hann.data(), r, world, groups[r], BoundaryMode::DROP, devs[r]);
+            rt.load_owned(x.data() + rt.shard().own_lo);
+            crlot_cuda_stream_sync(devs[r], nullptr);
+            rt.execute();
+            rt.read_output(multi.data() + rt.shard().t0);
+          } catch (const std::exception& e) { std::printf("  rank %d: %s\n", r, e.what()); bad[r] = 1; }
+        });
+      for (auto& t : th) t.join();
+      for (int r = 0; r < world; ++r) CHECK(!bad[r]);
+      CHECK(std::memcmp(multi.data(), want.data(), want.size() * 4) == 0);
+      for (auto g : groups) crlot_shard_group_destroy(g);
+      std::printf("sharded world %d over NCCL: ok\n", world);
+    }
+  }
+}
+
+// ---- facade_test --loop <samples> <N> <H>: the reference's per-frame loop, timed (bench.py "facade_loop") ----
+// bench/e2e_benchmark.cc:149-176 driven in the streaming order of bench/ola_benchmark.cc:150-157, every call a
+// host-pointer call on the drop-in classes.  Prints one JSON line.
+#include <chrono>
+static int run_loop(size_t len, size_t N, size_t H) {
+  const auto x = noise(len, 1234u);
+  WindowLUT hann(N, WindowType::HANN);
+  const float* w = hann.data();
+  auto run = [&](std::vector<float>& y) -> double {
+    Framer framer;
+    framer.set_params(N, H, 1, BoundaryMode::DROP);
+    FftPlanDesc desc{FftDomain::Real, (int)N, false, 1, 1, 1};
+    auto plan = MakeFftPlan(desc);
+    OLAConfig cfg{};
+    cfg.sample_rate = 48000; cfg.frame_size = N; cfg.hop_size = H; cfg.channels = 1; cfg.eps = 1e-8f; cfg.apply_window_inside = true;
+    OLAAccumulator ola(cfg);
+    ola.set_window(w, (int)N);
+    std::vector<float> frame(N), proc(N);
+    std::vector<std::complex<float>> spec(N / 2 + 1);
+    const auto t0 = std::chrono::steady_clock::now();
+    framer.push(x.data(), len);
+    size_t k = 0, pos = 0;
+    float* outp[1];
+    while (framer.pop(frame.data())) {
+      for (size_t i = 0; i < N; ++i) proc[i] = frame[i] * w[i];
+      plan->forward(proc.data(), spec.data());
+      plan->inverse(spec.data(), proc.data());
+      ola.push_frame_AoS(proc.data(), nullptr, k * H, 0, N, 1.0f);
+      outp[0] = y.data() + pos;
+      pos += ola.produce(outp, H);
+      ++k;
+    }
+    if (k > 0 && N > H) { outp[0] = y.data() + pos; pos += ola.produce(outp, N - H); }
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    y.resize(pos);
+    return dt;
+  };
+  std::vector<float> y(len + N), y2(len + N);
+  run(y2);                                   // warm-up pass (plans, staging buffers, first-touch)
+  y2.assign(len + N, 0.0f);
+  const double dt = run(y);
+  // whole-signal call on the same input: the per-frame route must give the same samples bit for bit
+  StftRoundTrip rt(N, H, w, w, BoundaryMode::DROP);
+  std::vector<float> whole(rt.output_len_for(len));
+  rt.process(x.data(), len, len, 1, whole.data(), whole.size());
+  bool same = whole.size() == y.size();
+  size_t diff = 0;
+  double num = 0.0, den = 0.0;
+  for (size_t i = 0; same && i < y.size(); ++i) {
+    if (std::memcmp(&y[i], &whole[i], 4) != 0) ++diff;
+    num += (double)(y[i] - whole[i]) * (y[i] - whole[i]); den += (double)whole[i] * whole[i];
+  }
+  std::printf("{\"value\": %.6f, \"unit\": \"Msamples/s\", \"samples\": %zu, \"frame\": %zu, \"hop\": %zu, \"frames\": %zu, "
+              "\"seconds\": %.6f, \"us_per_frame\": %.3f, \"rel_l2_vs_whole_signal_call\": %.3e, \"bit_mismatches_vs_whole_signal_call\": %zu, "
+              "\"api\": \"dsp::Framer::pop -> window -> IFftPlan::forward -> IFftPlan::inverse -> OLAAccumulator::push_frame_AoS -> produce, "
+              "host pointers at every call (bench/e2e_benchmark.cc:149-176 order)\"}\n",
+              len / dt / 1e6, len, N, H, (len - N) / H + 1, dt, dt / ((len - N) / H + 1) * 1e6, den > 0 ? std::sqrt(num / den) : 0.0, diff);
+  return same ? 0 : 1;
+}
+
 int main(int argc, char** argv) {
+  if (argc > 1 && std::string(argv[1]) == "--loop") {
+    int nd = 0;
+    if (crlot_cuda_device_count(&nd) != CRLOT_OK || nd == 0) { std::printf("no CUDA device\n"); return 2; }
+    try {
+      return run_loop(argc > 2 ? std::strtoull(argv[2], nullptr, 10) : (1u << 22), argc > 3 ? std::atoi(argv[3]) : 2048,
+                      argc > 4 ? std::atoi(argv[4]) : 512);
+    } catch (const std::exception& e) { std::printf("unexpected exception: %s\n", e.what()); return 1; }
+  }
   g_out = argc > 1 ? argv[1] : ".";
   int ndev = 0;
   if (crlot_cuda_device_count(&ndev) != CRLOT_OK || ndev == 0) {
@@ -562,6 +914,9 @@ int main(int argc, char** argv) {
     test_framer_stft();
     test_framequeue();
     test_wav_interleaved();
+    test_ring_buffer();
+    test_norm_builder();
+    test_sharded(ndev);
   } catch (const std::exception& e) {
     std::printf("unexpected exception: %s\n", e.what());
     return 1;

@@ -348,6 +348,98 @@ int crlot_ola_reset(crlot_ola_t ola);
 size_t crlot_ola_get(crlot_ola_t ola, int what);
 float crlot_ola_meter_peak(crlot_ola_t ola);
 
+/* ---- kernel-dispatch seam on device pointers (SURVEY 8b seam 2) ----------------------------------- */
+/* replaces dsp::ola::axpy / axpy_windowed / normalize_and_clear   ref: dsp/ola/kernels.h:28-53,
+ *   dsp/ola/kernels.cc:18-36,42-52 (the functions the reference forwards to kernels_hwy.cc)
+ * Same element-wise arithmetic on device arrays of n floats, bit-exact with the scalar reference:
+ *   axpy:                dst[i] = fma(src[i], g, dst[i])
+ *   axpy_windowed:       dst[i] = fma(fl(src[i]*win[i]), g, dst[i])      (two roundings, kernels.cc:24-28)
+ *   normalize_and_clear: out[i] = acc[i] / max(norm[i], eps); acc[i] = 0  (true division, kernels.cc:30-36) */
+int crlot_axpy(float* d_dst, const float* d_src, float g, size_t n, int device, void* stream);
+int crlot_axpy_windowed(float* d_dst, const float* d_src, const float* d_win, float g, size_t n, int device, void* stream);
+int crlot_normalize_and_clear(float* d_out, float* d_acc, const float* d_norm, float eps, size_t n, int device,
+                              void* stream);
+
+/* ---- drop-in RingBuffer<T> (unified-memory cells, reference index arithmetic) --------------------- */
+/* replaces dsp::ring::RingBuffer<T>   ref: dsp/ring/ring_buffer.h:25-110, dsp/ring/ring_buffer.cc:15-205
+ * The (1 + shadow) * capacity cells of elem_bytes each live in CUDA unified memory: crlot_ring_data()
+ * is valid on the host (the reference's data()[i] / Span element access keep working) AND on the device
+ * (kernels index the same pointer; pages migrate to HBM on first device touch, crlot_ring_prefetch moves
+ * them eagerly).  split() is the reference's arithmetic -- len == 0 -> two empty spans, overflow guard,
+ * len = min(len, capacity), start %= capacity, one or two spans (ring_buffer.cc:44-85) -- returning
+ * element OFFSETS from data().  write() appends at the internal write position, wraps and mirrors the
+ * head like the reference (ring_buffer.cc:166-205; n is clamped to capacity, where the reference would
+ * overrun).  shadow_sync(n) copies cells [0, min(n, capacity)) to [capacity, ...) (ring_buffer.cc:132-141);
+ * contiguous_offset is contiguous_read_ptr's rule: shadow ? read_pos : read_pos % capacity (:144-163).
+ * capacity == 0 fails with CRLOT_ERR_INVALID_ARGUMENT and the reference's message (ring_buffer.cc:21-23). */
+typedef struct crlot_ring_s* crlot_ring_t;
+typedef struct crlot_ring_span { size_t off1, len1, off2, len2; } crlot_ring_span;
+int crlot_ring_create(size_t capacity, size_t elem_bytes, int shadow, int device, crlot_ring_t* out);
+int crlot_ring_destroy(crlot_ring_t r);
+void* crlot_ring_data(crlot_ring_t r);
+size_t crlot_ring_capacity(crlot_ring_t r);
+size_t crlot_ring_physical_capacity(crlot_ring_t r);
+size_t crlot_ring_write_pos(crlot_ring_t r);
+int crlot_ring_has_shadow(crlot_ring_t r);
+int crlot_ring_split(crlot_ring_t r, size_t start, size_t len, crlot_ring_span* out);
+int crlot_ring_shadow_sync(crlot_ring_t r, size_t n_elems);
+size_t crlot_ring_contiguous_offset(crlot_ring_t r, size_t read_pos);
+/* write(src, n): returns the elements written through *written (0 for a null source or n == 0) */
+int crlot_ring_write(crlot_ring_t r, const void* h_src, size_t n, size_t* written);
+int crlot_ring_write_device(crlot_ring_t r, const void* d_src, size_t n, size_t* written, void* stream);
+/* migrate the cells to the device (to_device != 0) or back to the host ahead of use */
+int crlot_ring_prefetch(crlot_ring_t r, int to_device, void* stream);
+
+/* ---- multi-GPU partitioning (csrc/shard.cu) ------------------------------------------ */
+/* Channels / streams never interact (ref: dsp/ola/OLAAccumulator.cc:76-111): contiguous blocks, no
+ * data-path communication. */
+int crlot_channel_shard(long long channels, int rank, int world, long long* first, long long* count);
+
+/* One long signal split by OUTPUT/time range.  Rank r owns outputs [t0, t1) = [r*S, (r+1)*S) clipped to
+ * the run's output length, S = total_len / world (a multiple of hop).  Frame k depends only on
+ * x[k*hop, k*hop+nfft) (ref: dsp/frame/framer.cc:128-182), out[t] only on frames with k*hop in
+ * (t-nfft, t] (ref: dsp/ola/OLAAccumulator.cc:75-111,194-209): the rank needs left_halo samples from
+ * rank-1 and right_halo from rank+1 (each about nfft-hop) and recomputes the frames that start in its left
+ * halo, so its outputs are bit-identical to the one-GPU run.  Its device buffer is laid out
+ * [left_halo | owned S samples | right_halo] = input samples [in_lo, in_hi). */
+typedef struct crlot_time_shard {
+  int rank, world, nfft, hop, boundary_mode;
+  long long total_len;
+  long long t0, t1, n_out;            /* owned output range, n_out = t1 - t0                                  */
+  long long k_lo, n_frames;           /* global index of local frame 0; frames computed locally              */
+  long long n_owned_frames;           /* of those, the frames that start inside the owned input range        */
+  long long in_lo, in_hi;             /* input samples needed                                                 */
+  long long own_lo, own_hi;           /* input samples held / generated by this rank                         */
+  long long left_halo, right_halo;    /* samples received from rank-1 / rank+1                               */
+  long long send_left, send_right;    /* samples sent to rank-1 (its right halo) / rank+1 (its left halo)    */
+  long long frame_t0;                 /* local output index of local frame 0's first sample (<= 0)           */
+} crlot_time_shard;
+int crlot_shard_plan(long long total_len, int nfft, int hop, int rank, int world, int boundary_mode,
+                     crlot_time_shard* out);
+
+/* One NCCL communicator per rank (one process per GPU, or one thread per GPU of one process).  NCCL is
+ * bound at run time (libnccl.so.2; CRLOT_NCCL_LIB overrides the name); world == 1 needs none.
+ *   multi-process: rank 0 calls crlot_shard_group_unique_id, ships the 128 bytes to the others by any
+ *                  means (MPI, torch.distributed, a file), every rank calls crlot_shard_group_create;
+ *   one process:   crlot_shard_group_create_all(n, devices, groups[n])  (ncclCommInitAll);
+ *   existing comm: crlot_shard_group_wrap borrows a caller-owned ncclComm_t. */
+#define CRLOT_NCCL_UNIQUE_ID_BYTES 128
+typedef struct crlot_shard_group_s* crlot_shard_group_t;
+int crlot_shard_group_unique_id(void* id_out_128);
+int crlot_shard_group_create(int world, int rank, const void* id_128, int device, crlot_shard_group_t* out);
+int crlot_shard_group_create_all(int n_dev, const int* devices, crlot_shard_group_t* out_groups);
+int crlot_shard_group_wrap(void* nccl_comm, int world, int rank, int device, crlot_shard_group_t* out);
+int crlot_shard_group_destroy(crlot_shard_group_t g);
+int crlot_shard_group_info(crlot_shard_group_t g, int* world, int* rank, int* device);
+/* Fills the halo regions of d_xbuf from the neighbours: ncclSend/ncclRecv pairs of send_* / *_halo floats
+ * inside ONE ncclGroupStart/End, enqueued on `stream` (asynchronous; 12 KiB per direction at config 4). */
+int crlot_halo_exchange(crlot_shard_group_t g, const crlot_time_shard* shard, float* d_xbuf, void* stream);
+/* halo exchange + kernel 1 over the haloed buffer + (kernel 2, kernel 3 | fused 2+3 when d_frames is NULL)
+ * at the shard's envelope phase (t0) and frame offset (frame_t0), all on `stream`.  d_spec
+ * [n_frames][bins], d_frames [n_frames][nfft] or NULL, d_out [n_out].  group may be NULL when world == 1. */
+int crlot_sharded_roundtrip_execute(crlot_plan_t plan, crlot_shard_group_t group, const crlot_time_shard* shard,
+                                    float* d_xbuf, void* d_spec, float* d_frames, float* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

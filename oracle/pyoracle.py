@@ -268,6 +268,17 @@ class Oracle(_Common):
                                    C.c_long(n), _ptr(out))
         return out
 
+    def slice_roundtrip(self, seed, channel, t_from, n, nfft, hop, window, ring_len, mode=DROP):
+        """Slice oracle: the round trip of the synthetic signal (seed, channel) restricted to
+        absolute output samples [a, a+n), a = the first multiple of ring_len at or after t_from, plus nfft.
+        A fresh accumulator started at a sample offset that is a multiple of ring_len (hence of hop) sees
+        the same envelope phase and, after its first nfft samples, the same frames in the same order as the
+        full run -- so the values returned are the full run's.  Returns (a, expected[n])."""
+        base = -(-t_from // ring_len) * ring_len
+        x = self.synth_uniform(seed, channel, base, n + 3 * nfft)
+        out = self.roundtrip(x, nfft, hop, window, mode, taps=False)["out"]
+        return base + nfft, out[nfft:nfft + n].copy()
+
     def synth_tones(self, i0, n):
         out = np.empty(n, np.float32)
         self.lib.orc_synth_tones.restype = None
@@ -287,15 +298,32 @@ class Ref(_Common):
     _p = "ref_"
 
     @staticmethod
-    def path(strict=False):
-        return os.path.join(_HERE, "_ref", "libcrlot_ref_strict.so" if strict else "libcrlot_ref.so")
+    def path(strict=False, isa="v3"):
+        name = "libcrlot_ref_strict.so" if strict else ("libcrlot_ref_v4.so" if isa == "v4" else "libcrlot_ref.so")
+        return os.path.join(_HERE, "_ref", name)
 
     @classmethod
-    def available(cls, strict=False):
-        return os.path.exists(cls.path(strict))
+    def available(cls, strict=False, isa="v3"):
+        return os.path.exists(cls.path(strict, isa))
 
-    def __init__(self, strict=False):
-        self.lib = C.CDLL(self.path(strict))
+    @classmethod
+    def best_isa(cls):
+        """'v4' (AVX-512 F/BW/CD/DQ/VL build) when this host's cpuid has those features and the build exists,
+        else 'v3' (AVX2+FMA): what -march=native would pick between the two shipped builds."""
+        try:
+            flags = set()
+            for ln in open("/proc/cpuinfo"):
+                if ln.startswith("flags"):
+                    flags = set(ln.split(":", 1)[1].split())
+                    break
+            v4 = {"avx512f", "avx512bw", "avx512cd", "avx512dq", "avx512vl"} <= flags
+        except OSError:
+            v4 = False
+        return "v4" if v4 and cls.available(isa="v4") else "v3"
+
+    def __init__(self, strict=False, isa="v3"):
+        self.isa = "v3-strict" if strict else isa
+        self.lib = C.CDLL(self.path(strict, isa))
 
     def ring_len(self, frame, hop):
         f = self.lib.ref_ola_ring_size

@@ -31,7 +31,8 @@ def _worker(rank, world, port, total_len, nfft, hop, q):
         sharding.halo_exchange(xbuf, sh)
         local = xbuf.numpy()
         # what the halo exchange must have delivered
-        assert np.array_equal(local, orc.synth_uniform(7, 0, sh.in_lo, sh.in_hi - sh.in_lo))
+        need = sh.in_hi - sh.in_lo            # (the last rank's owned tail beyond the last DROP frame is not needed)
+        assert np.array_equal(local[:need], orc.synth_uniform(7, 0, sh.in_lo, need))
         # local "kernels": frames -> window -> rfft -> irfft -> gather OLA at the right envelope phase
         frames = np.stack([local[k * hop:k * hop + nfft] for k in range(sh.n_frames)]) * w
         ifr = orc.irfft_many(orc.rfft_many(frames.astype(np.float32), nfft), nfft)
@@ -47,13 +48,16 @@ def _worker(rank, world, port, total_len, nfft, hop, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,nfft,hop", [(2, 1024, 256), (2, 4096, 1024), (4, 256, 64)])
+@pytest.mark.parametrize("world,nfft,hop", [(2, 1024, 256), (2, 4096, 1024), (4, 256, 64), (2, 256, 256), (3, 1000, 300)])
 def test_time_sharded_path_equals_unsharded(world, nfft, hop):
     import torch.multiprocessing as mp
-    total_len = world * 24 * hop * (nfft // hop)
+    total_len = world * 24 * hop * -(-nfft // hop)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + (os.getpid() + nfft) % 2000
+    import socket
+    with socket.socket() as sk:                   # a free port per case: consecutive cases must not collide
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
     procs = [ctx.Process(target=_worker, args=(r, world, port, total_len, nfft, hop, q)) for r in range(world)]
     for p in procs:
         p.start()
@@ -78,6 +82,19 @@ def test_shard_arithmetic():
     assert sum(s.n_owned_frames for s in shards) == 8388605
     assert all(s.frame_t0 == (-3072 if s.rank else 0) for s in shards)
     assert [s.t0 for s in shards] == [r << 30 for r in range(8)]
+    assert all(s.send_left == (3072 if s.rank else 0) and s.send_right == (3072 if s.rank < 7 else 0) for s in shards)
+    # hop == nfft: no overlap, no halos, nothing to send in either direction (sends and receives stay symmetric)
+    flat = [sharding.make_time_shard(8 * 4096, 512, 512, r, 4) for r in range(4)]
+    assert all(s.left_halo == s.right_halo == s.send_left == s.send_right == 0 for s in flat)
+    # a signal shorter than one frame: every shard is empty, with empty halos
+    empty = [sharding.make_time_shard(4 * 64, 1024, 64, r, 4) for r in range(4)]
+    assert all(s.n_frames == 0 and s.n_out == 0 and s.left_halo == 0 and s.right_halo == 0 for s in empty)
+    # halo larger than a neighbour's owned span is refused, not silently mis-sliced
+    import crlot_dsp_b200 as dsp
+    with pytest.raises(dsp.CrlotInvalidArgument):
+        sharding.make_time_shard(4 * 256, 1024, 256, 1, 4)
+    with pytest.raises(dsp.CrlotInvalidArgument):
+        sharding.make_time_shard(1000, 256, 64, 0, 3)          # does not split evenly
     # channel blocks
     assert [sharding.channel_shard(256, r, 8) for r in range(8)] == [(32 * r, 32) for r in range(8)]
     blocks = [sharding.channel_shard(10, r, 4) for r in range(4)]
