@@ -178,7 +178,8 @@ struct crlot_plan_s {
   long long sgain_row_stride = 0;
   unsigned int tiny2 = 0;
   std::vector<float> env_host;
-  HostSlot slot[2];
+  static constexpr int kHostSlots = 3;   // H2D / kernels / D2H of a slab are serial on its stream: three slabs in flight keep both copy engines busy
+  HostSlot slot[kHostSlots];
   long long slot_frames = 0;   // capacity of the host-path workspace, in frames
   int slot_group = 0;          // ... and in channels per slab (interleaved host path)
   bool slot_aos = false;
@@ -639,7 +640,7 @@ static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long c
     const float* xin = h_in + static_cast<long long>(c) * chan_stride;
     float* yout = h_out + static_cast<long long>(c) * out_chan_stride;
     for (long long t0 = 0; t0 < n_out; t0 += slab_hops * H, ++it) {
-      HostSlot& s = plan->slot[it & 1];
+      HostSlot& s = plan->slot[it % crlot_plan_s::kHostSlots];
       const long long t1 = std::min(n_out, t0 + slab_hops * H);
       long long k_lo = t0 - N + 1 <= 0 ? 0 : (t0 - N + 1 + H - 1) / H;
       long long k_hi = std::min(F - 1, (t1 - 1) / H);

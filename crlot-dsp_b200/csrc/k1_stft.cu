@@ -16,6 +16,8 @@
 //    in-register passes with one shared-memory transposition in between (warpfft.cuh), the
 //    real split uses warp shuffles, and the spectrum is stored straight from registers as
 //    contiguous 8-byte-per-lane rows.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "warpfft.cuh"
@@ -33,13 +35,37 @@ __host__ __device__ inline int next_pow2(int v) {
   return r;
 }
 
-template <int NFFT>
+// TM = the per-lane window and inter-pass twiddle constants live in tensor memory (no shared-memory tables)
+template <int NFFT, bool TM>
 struct K1Smem {
   using X = GeoX<NFFT>;
-  static constexpr int kTableBytes = NFFT * 4 + X::C * 8;
+  static constexpr int kTableBytes = TM ? 0 : NFFT * 4 + X::C * 8;
+  // TMEM columns: window (2B) + twiddles (2B), rounded up to a power of two >= 32
+  static constexpr int kTmCols = 4 * X::B <= 32 ? 32 : 4 * X::B <= 64 ? 64 : 128;
   __host__ __device__ static int per_warp_bytes(int rcap) { return rcap * 4 + X::XCPX * 8 + 16; }
   __host__ __device__ static int total(int rcap, int nwarps) { return kTableBytes + nwarps * per_warp_bytes(rcap); }
 };
+
+// inter-pass twiddle from tensor memory: chunks of 8 factors, the next chunk in flight while this one multiplies
+template <class X, bool INV> __device__ __forceinline__ void twiddle1_tmem(cpx (&v)[32], uint32_t ttw, cpx (&t0)[8]) {
+  constexpr int NCH = X::B / 8;
+  cpx tb[2][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) tb[0][i] = t0[i];
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    tmem_wait_ld8(tb[c & 1]);
+    if (c + 1 < NCH) tmem_ld8(ttw + 16 * (c + 1), tb[(c + 1) & 1]);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int ob = 8 * c + i;
+      if (ob == 0) continue;
+#pragma unroll
+      for (int j = 0; j < X::M1; ++j)
+        v[j * X::B + ob] = INV ? cmulc(v[j * X::B + ob], tb[c & 1][i]) : cmul(v[j * X::B + ob], tb[c & 1][i]);
+    }
+  }
+}
 
 // Where a frame's samples come from: position q of the (virtually padded) stream of a channel is
 // sample q - pad of the signal; positions outside [pad, pad + len) take FrameQueue's padding value
@@ -88,28 +114,64 @@ __device__ __forceinline__ void ring_fill(float* ring, int mask, const SigView& 
 //            non-zero |window|, set by the host).  Only the registers holding the newest hop are
 //            screened (2 integer ops + half a packed FMA per sample); when a warp sees a suspect
 //            it applies rule 1 to whole frames until the suspect has left the ring.
-template <int NFFT, int SCRUB>
+template <int NFFT, int SCRUB, bool TM>
 __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Params p, const int rcap) {
   using X = GeoX<NFFT>;
+  using SM = K1Smem<NFFT, TM>;
   constexpr int C = X::C, G = X::G, A = X::A, B = X::B;
+  constexpr int NCH = B / 8;                              // chunks of 8 per-lane constants (16 TMEM columns)
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint32_t s_tmem_base;
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wb = reinterpret_cast<unsigned char*>(s_tw1 + C) + warp * K1Smem<NFFT>::per_warp_bytes(rcap);
+  unsigned char* wb = smem_raw + SM::kTableBytes + warp * SM::per_warp_bytes(rcap);
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + rcap);
   const uint32_t bar = smem_u32(ex + X::XCPX);
   const int mask = rcap - 1;
+  const int a_lane = lane % A;
 
-  for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  if (!TM) {
+    for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+    for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  }
   const SplitLane<X::M2> SL = make_split_fwd<X>(lane);   // lane factors of the real split (no table)
   if (lane == 0) {
     mbar_init(bar, 1);
     fence_mbar_init();
   }
+  // Tensor memory holds what is constant per LANE for the whole kernel: the window samples of the lane's pass-1
+  // points (a + A*b, b < B: columns [0, 2B)) and its inter-pass twiddles W_C^(a*ob) (columns [2B, 4B)).  Lane t of
+  // every warp has a = t % A, and warps w, w+4, w+8 share TMEM lanes 32*(w%4)..+31, so warps 0..3 write the
+  // constants once and all twelve read them: 16 KB per frame that no longer crosses the shared-memory pipe.
+  uint32_t twin = 0, ttw = 0;
+  if (TM) {
+    if (warp == 0) tmem_alloc<SM::kTmCols>(&s_tmem_base);
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    twin = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    ttw = twin + 2 * B;
+    if (warp < 4) {
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        cpx w8[8], t8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int b = 8 * c + i;
+          w8[i] = *reinterpret_cast<const cpx*>(p.window + 2 * a_lane + 2 * A * b);
+          t8[i] = p.tw1[b * A + a_lane];
+        }
+        tmem_st8(twin + 16 * c, w8);
+        tmem_st8(ttw + 16 * c, t8);
+      }
+      tmem_wait_st();
+    }
+    tmem_fence_before_sync();
+  }
   __syncthreads();
+  if (TM) tmem_fence_after_sync();
 
   const int H = p.hop;
   const int S = (G - 1) * H + NFFT;                     // samples spanned by the G frames of one step
@@ -126,7 +188,6 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
     const int i1 = lane + 32 * j;
     in_off[j] = (i1 / A) * H + 2 * (i1 % A);
   }
-  const int a_lane = lane % A;
 
   for (;;) {
     unsigned long long q = 0;
@@ -146,6 +207,8 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
     ring_fill(ring, mask, sig, pos, S, bar, lane);
 
     for (int s = 0; s < nsteps; ++s) {
+      cpx wb8[2][8];                         // window constants, 8 at a time; the next chunk loads while this one multiplies
+      if (TM) tmem_ld8(twin, wb8[0]);        // in flight across the barrier wait
       mbar_wait(bar, parity);
       parity ^= 1u;
       __syncwarp();
@@ -154,24 +217,41 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
       unsigned int wmin = 0xffffffffu;       // min over screened samples of 2*|bits| - 2 (0 maps to max)
       cpx nf = mk(0.f, 0.f);                 // sum of 0*x: becomes NaN iff a screened sample is NaN/Inf
 #pragma unroll
-      for (int j = 0; j < X::M1; ++j) {
-        // frames of this item across lanes: g in [32j/A, (31+32j)/A]; newest hop of frame g
-        // starts at point (3-g)*C/4 (nfft == 4*hop), i.e. register b >= (3-g)*B/4
-        const int g_hi = (31 + 32 * j) / A;
-        const int newb = g_hi >= 3 ? 0 : (3 - g_hi) * B / 4;
+      for (int c = 0; c < NCH; ++c) {
+        cpx x8[X::M1][8];
 #pragma unroll
-        for (int b = 0; b < B; ++b) {
-          const int ridx = static_cast<int>((pos + in_off[j] + 2 * A * b) & mask);
-          const cpx x = *reinterpret_cast<const cpx*>(ring + ridx);
-          const cpx w = *reinterpret_cast<const cpx*>(s_win + 2 * a_lane + 2 * A * b);
-          cpx pw = mul2(x, w);                 // one rounding per sample, as frame[i]*window[i]
-          if (SCRUB == 1) pw = mk(scrub(pw.x), scrub(pw.y));
-          if (SCRUB == 2 && b >= newb) {
-            const unsigned int u0 = __float_as_uint(x.x), u1 = __float_as_uint(x.y);
-            wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));   // sign bit leaves by wrap-around
-            nf = fma2(x, mk(0.f, 0.f), nf);
+        for (int j = 0; j < X::M1; ++j)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int ridx = static_cast<int>((pos + in_off[j] + 2 * A * (8 * c + i)) & mask);
+            x8[j][i] = *reinterpret_cast<const cpx*>(ring + ridx);
           }
-          v[j * B + b] = pw;
+        if (TM) {
+          tmem_wait_ld8(wb8[c & 1]);
+          if (c + 1 < NCH) tmem_ld8(twin + 16 * (c + 1), wb8[(c + 1) & 1]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) wb8[c & 1][i] = *reinterpret_cast<const cpx*>(s_win + 2 * a_lane + 2 * A * (8 * c + i));
+        }
+#pragma unroll
+        for (int j = 0; j < X::M1; ++j) {
+          // frames of this item across lanes: g in [32j/A, (31+32j)/A]; newest hop of frame g
+          // starts at point (3-g)*C/4 (nfft == 4*hop), i.e. register b >= (3-g)*B/4
+          const int g_hi = (31 + 32 * j) / A;
+          const int newb = g_hi >= 3 ? 0 : (3 - g_hi) * B / 4;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int b = 8 * c + i;
+            const cpx x = x8[j][i];
+            cpx pw = mul2(x, wb8[c & 1][i]);     // one rounding per sample, as frame[i]*window[i]
+            if (SCRUB == 1) pw = mk(scrub(pw.x), scrub(pw.y));
+            if (SCRUB == 2 && b >= newb) {
+              const unsigned int u0 = __float_as_uint(x.x), u1 = __float_as_uint(x.y);
+              wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));   // sign bit leaves by wrap-around
+              nf = fma2(x, mk(0.f, 0.f), nf);
+            }
+            v[j * B + b] = pw;
+          }
         }
       }
       if (SCRUB == 2) {
@@ -186,8 +266,11 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
       __syncwarp();
       if (s + 1 < nsteps) ring_fill(ring, mask, sig, pos + S, G * H, bar, lane);
 
+      cpx t0[8];
+      if (TM) tmem_ld8(ttw, t0);             // first twiddle chunk in flight during pass 1
       pass1<X, false>(v);
-      twiddle1<X, false>(v, lane, s_tw1);
+      if (TM) twiddle1_tmem<X, false>(v, ttw, t0);
+      else twiddle1<X, false>(v, lane, s_tw1);
       xchg_write<X>(v, lane, ex);
       __syncwarp();
       xchg_read<X>(v, lane, ex);
@@ -213,36 +296,74 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
       spec += static_cast<long long>(G) * (C + 1);
     }
   }
+  if (TM) {
+    tmem_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<SM::kTmCols>(s_tmem_base);
+  }
 }
 
 // ---- N = 4096: one warp per frame, 64 complex registers per lane (warpfft4096.cuh) --------------
 // Same pipeline as above with G = 1: private 4096-float ring (the frame itself; the hop that has
 // just been read into registers is the one the next bulk copy overwrites), two-round exchange so
-// that eight warps fit the 227 KB of shared memory, in-lane real split (no shuffles, no table).
+// that the warps fit the 227 KB of shared memory, in-lane real split (no shuffles, no table).
+// The per-lane window (64 complex = 128 TMEM columns) and inter-pass twiddles (128 columns) live in
+// tensor memory as in the kernel above: no shared-memory tables, and one tcgen05.ld per 8 constants
+// instead of 8 LDS.64 with their address arithmetic.
 constexpr int kK1Warps4096 = 8;
 
-template <int SCRUB>
+template <int SCRUB, bool TM>
 __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(const K1Params p) {
   constexpr int NFFT = 4096, C = 2048, RCAP = 4096, mask = RCAP - 1;
   constexpr int kPerWarp = RCAP * 4 + Geo4096::FX_ROUND_CPX * 8 + 16;
+  constexpr int kTable = TM ? 0 : NFFT * 4 + C * 8;
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint32_t s_tmem_base;
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw = reinterpret_cast<cpx*>(s_win + NFFT);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wb = reinterpret_cast<unsigned char*>(s_tw + C) + warp * kPerWarp;
+  unsigned char* wb = smem_raw + kTable + warp * kPerWarp;
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + RCAP);
   const uint32_t bar = smem_u32(ex + Geo4096::FX_ROUND_CPX);
 
-  for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw[i] = p.tw1[i];
+  if (!TM) {
+    for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+    for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw[i] = p.tw1[i];
+  }
   const SplitLane4096 SL = make_split_4096<false>(lane);
   const Coop4096 CO = make_coop_4096<false>(lane);
   if (lane == 0) {
     mbar_init(bar, 1);
     fence_mbar_init();
   }
+  uint32_t twin = 0, ttw = 0;
+  if (TM) {
+    if (warp == 0) tmem_alloc<256>(&s_tmem_base);
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    twin = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    ttw = twin + 128;
+    if (warp < 4) {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        cpx w8[8], t8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int b = 8 * c + i;
+          w8[i] = *reinterpret_cast<const cpx*>(p.window + 2 * lane + 64 * b);
+          t8[i] = p.tw1[b * 32 + lane];
+        }
+        tmem_st8(twin + 16 * c, w8);
+        tmem_st8(ttw + 16 * c, t8);
+      }
+      tmem_wait_st();
+    }
+    tmem_fence_before_sync();
+  }
   __syncthreads();
+  if (TM) tmem_fence_after_sync();
 
   const int H = p.hop;
   const long long frames_per_chunk = p.chunk_steps;
@@ -268,6 +389,8 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
     ring_fill(ring, mask, sig, pos, NFFT, bar, lane);
 
     for (int s = 0; s < nsteps; ++s) {
+      cpx wb8[8];
+      if (TM) tmem_ld8(twin, wb8);           // in flight across the barrier wait
       mbar_wait(bar, parity);
       parity ^= 1u;
       __syncwarp();
@@ -276,18 +399,36 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
       unsigned int wmin = 0xffffffffu;
       cpx nf = mk(0.f, 0.f);
 #pragma unroll
-      for (int b = 0; b < 64; ++b) {
-        const int ridx = static_cast<int>((pos + 2 * lane + 64 * b) & mask);
-        const cpx x = *reinterpret_cast<const cpx*>(ring + ridx);
-        const cpx w = *reinterpret_cast<const cpx*>(s_win + 2 * lane + 64 * b);
-        cpx pw = mul2(x, w);                   // one rounding per sample, as frame[i]*window[i]
-        if (SCRUB == 1) pw = mk(scrub(pw.x), scrub(pw.y));
-        if (SCRUB == 2 && b >= 48) {           // the newest hop (nfft == 4*hop): samples >= 3072
-          const unsigned int u0 = __float_as_uint(x.x), u1 = __float_as_uint(x.y);
-          wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));
-          nf = fma2(x, mk(0.f, 0.f), nf);
+      for (int ch = 0; ch < 8; ++ch) {
+        cpx x8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int ridx = static_cast<int>((pos + 2 * lane + 64 * (8 * ch + i)) & mask);
+          x8[i] = *reinterpret_cast<const cpx*>(ring + ridx);
         }
-        v[b] = pw;
+        if (TM) {
+          tmem_wait_ld8(wb8);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) wb8[i] = *reinterpret_cast<const cpx*>(s_win + 2 * lane + 64 * (8 * ch + i));
+        }
+        cpx pw8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) pw8[i] = mul2(x8[i], wb8[i]);   // one rounding per sample, as frame[i]*window[i]
+        if (TM && ch + 1 < 8) tmem_ld8(twin + 16 * (ch + 1), wb8);   // next chunk in flight during the ring reads
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int b = 8 * ch + i;
+          const cpx x = x8[i];
+          cpx pw = pw8[i];
+          if (SCRUB == 1) pw = mk(scrub(pw.x), scrub(pw.y));
+          if (SCRUB == 2 && b >= 48) {           // the newest hop (nfft == 4*hop): samples >= 3072
+            const unsigned int u0 = __float_as_uint(x.x), u1 = __float_as_uint(x.y);
+            wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));
+            nf = fma2(x, mk(0.f, 0.f), nf);
+          }
+          v[b] = pw;
+        }
       }
       if (SCRUB == 2) {
         const bool suspect = (wmin < p.tiny2) || (nf.x != 0.0f) || (nf.y != 0.0f);
@@ -302,7 +443,19 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
       if (s + 1 < nsteps) ring_fill(ring, mask, sig, pos + NFFT, H, bar, lane);
 
       fwd4096_pass1(v);
-      fwd4096_twiddle(v, lane, s_tw);
+      if (TM) {                                // all 64 values are live here: one chunk of 8 factors at a time
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) {
+          cpx tb[8];
+          tmem_ld8(ttw + 16 * ch, tb);
+          tmem_wait_ld8(tb);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (8 * ch + i > 0) v[8 * ch + i] = cmul(v[8 * ch + i], tb[i]);
+        }
+      } else {
+        fwd4096_twiddle(v, lane, s_tw);
+      }
       fwd4096_xwrite<0>(v, lane, ex);
       __syncwarp();
       fwd4096_xread<0>(v, lane, ex);
@@ -337,12 +490,19 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
       spec += C + 1;
     }
   }
+  if (TM) {
+    tmem_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<256>(s_tmem_base);
+  }
 }
 
 static cudaError_t launch_k1_4096(const K1Params& p, cudaStream_t st) {
-  const int smem = 4096 * 4 + 2048 * 8 + kK1Warps4096 * (4096 * 4 + Geo4096::FX_ROUND_CPX * 8 + 16);
+  static const bool tm = getenv("CRLOT_K1_NO_TMEM") == nullptr;
+  const int smem = (tm ? 0 : 4096 * 4 + 2048 * 8) + kK1Warps4096 * (4096 * 4 + Geo4096::FX_ROUND_CPX * 8 + 16);
   const int mode = !p.scrub ? 0 : (p.scrub == 2 && 4096 == 4 * p.hop) ? 2 : 1;
-  auto kern = mode == 0 ? stft_fwd_kernel_4096<0> : mode == 1 ? stft_fwd_kernel_4096<1> : stft_fwd_kernel_4096<2>;
+  auto kern = tm ? (mode == 0 ? stft_fwd_kernel_4096<0, true> : mode == 1 ? stft_fwd_kernel_4096<1, true> : stft_fwd_kernel_4096<2, true>)
+                 : (mode == 0 ? stft_fwd_kernel_4096<0, false> : mode == 1 ? stft_fwd_kernel_4096<1, false> : stft_fwd_kernel_4096<2, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
@@ -359,11 +519,14 @@ cudaError_t launch_k1(const K1Params& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
   const int S = (X::G - 1) * p.hop + NFFT;
   const int rcap = next_pow2(S);
-  const int smem = K1Smem<NFFT>::total(rcap, kK1Warps);
+  // CRLOT_K1_NO_TMEM=1 keeps the window / twiddle tables in shared memory (A/B timing and the bit-identity test)
+  static const bool tm = getenv("CRLOT_K1_NO_TMEM") == nullptr;
+  const int smem = tm ? K1Smem<NFFT, true>::total(rcap, kK1Warps) : K1Smem<NFFT, false>::total(rcap, kK1Warps);
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
   // screening mode needs nfft == 4*hop and a finite threshold; otherwise the per-sample rule
   const int mode = !p.scrub ? 0 : (p.scrub == 2 && NFFT == 4 * p.hop) ? 2 : 1;
-  auto kern = mode == 0 ? stft_fwd_kernel<NFFT, 0> : mode == 1 ? stft_fwd_kernel<NFFT, 1> : stft_fwd_kernel<NFFT, 2>;
+  auto kern = tm ? (mode == 0 ? stft_fwd_kernel<NFFT, 0, true> : mode == 1 ? stft_fwd_kernel<NFFT, 1, true> : stft_fwd_kernel<NFFT, 2, true>)
+                 : (mode == 0 ? stft_fwd_kernel<NFFT, 0, false> : mode == 1 ? stft_fwd_kernel<NFFT, 1, false> : stft_fwd_kernel<NFFT, 2, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
