@@ -606,6 +606,16 @@ class Stream:
                                             _p(out), C.c_longlong(out.strides[0] // 4), C.byref(n)))
         return n.value
 
+    def submit_host(self, chunk, out):
+        """tick_host without the wait: returns (n_out, ticket); wait_host(ticket) completes it."""
+        n, t = C.c_int(0), C.c_ulonglong(0)
+        _check(lib().crlot_stream_submit_host(self._h, _p(chunk), C.c_longlong(chunk.strides[0] // 4), C.c_int(chunk.shape[1]),
+                                              _p(out), C.c_longlong(out.strides[0] // 4), C.byref(n), C.byref(t)))
+        return n.value, t.value
+
+    def wait_host(self, ticket):
+        _check(lib().crlot_stream_wait_host(self._h, C.c_ulonglong(ticket)))
+
     def drain(self, out=None):
         torch = _torch()
         if out is None:

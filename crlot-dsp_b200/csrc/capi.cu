@@ -1074,8 +1074,22 @@ struct crlot_stream_s {
   DevArr<unsigned int> done;         // block ticket of the one-launch tick
   DevArr<float> ring, acc, frames;
   DevArr<cpx> spec;
-  DevArr<float> h2d, d2h;            // staging of crlot_stream_tick_host
+  DevArr<float> h2d, d2h;            // staging of crlot_stream_tick_host (pageable host buffers)
   cudaStream_t host_stream = nullptr;
+  static constexpr int kTickets = 64;  // completion events of crlot_stream_submit_host, a ring
+  cudaEvent_t done_ev[kTickets] = {};
+  unsigned long long submitted = 0;
+  // three-stream pipeline of crlot_stream_submit_host: H2D of tick t+1 (copy_in) || kernel of tick t (host_stream) ||
+  // D2H of tick t-1 (copy_out) through kPipe device staging slots
+  static constexpr int kPipe = 4;
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  DevArr<float> pin[kPipe], pout[kPipe];
+  cudaEvent_t ev_in[kPipe] = {}, ev_k[kPipe] = {}, ev_out[kPipe] = {};
+  unsigned long long piped = 0;
+  bool poisoned = false;             // a launch failed mid-tick: host mirrors and device counters may disagree
+  // instantiated graphs of crlot_stream_run, kept across calls and re-pointed with cudaGraphExecUpdate
+  struct CachedGraph { int key; cudaGraphExec_t exec; };
+  std::vector<CachedGraph> graphs;
 };
 
 namespace {
@@ -1119,15 +1133,28 @@ cudaError_t stream_tick_launches(crlot_stream_s* s, const float* d_in, long long
   cudaError_t e = launch_stream_ingest(s->ctr.p, d_in, in_stride, chunk_len, s->ring.p, s->rcap, s->S, w0, st);
   if (e != cudaSuccess) return e;
   if (nf > 0) {
-    StreamFwdParams f{};
-    f.ctr = s->ctr.p; f.ring = s->ring.p; f.rcap = s->rcap; f.n_streams = s->S; f.nf = nf; f.nfft = N; f.hop = H;
-    f.spec = s->spec.p; f.window = p->win_a.p; f.tw1 = p->tw1.p; f.sa = p->sa.p; f.scrub = p->d.scrub;
-    e = launch_stream_fwd(f, st);
+    if (!p->generic && stream_fwd_supported(N)) {
+      StreamFwdParams f{};
+      f.ctr = s->ctr.p; f.ring = s->ring.p; f.rcap = s->rcap; f.n_streams = s->S; f.nf = nf; f.nfft = N; f.hop = H;
+      f.spec = s->spec.p; f.window = p->win_a.p; f.tw1 = p->tw1.p; f.sa = p->sa.p; f.scrub = p->d.scrub;
+      e = launch_stream_fwd(f, st);
+    } else {
+      // nfft = 4096 and the any-size plans: gather the frames out of the rings (into the buffer kernel 2 overwrites
+      // afterwards) and run kernel 1 over them as non-overlapping frames
+      e = launch_stream_gather(s->ctr.p, s->ring.p, s->rcap, s->S, nf, N, H, s->frames.p, st);
+      if (e != cudaSuccess) return e;
+      K1Params k{};
+      k.sig = s->frames.p; k.chan_stride = 0; k.len = static_cast<long long>(s->S) * nf * N; k.channels = 1;
+      k.frames = static_cast<long long>(s->S) * nf; k.nfft = N; k.hop = N; k.spec = s->spec.p; k.spec_chan_rows = k.frames;
+      k.window = p->win_a.p; k.tw1 = p->tw1.p; k.sa = p->sa.p; k.pre = p->pre.p; k.counter = p->counter_for(st);
+      k.chunk_steps = 64; k.scrub = p->k1_scrub; k.tiny2 = p->tiny2; k.generic = p->generic;
+      e = launch_stft_fwd(k, st);
+    }
     if (e != cudaSuccess) return e;
     K2Params k2{};
     k2.spec = s->spec.p; k2.rows = static_cast<long long>(s->S) * nf; k2.nfft = N; k2.frames = s->frames.p;
     k2.window = p->syn_active ? p->win_s.p : nullptr; k2.tw1 = p->tw1.p; k2.sa = p->sa.p; k2.pre = p->pre.p;
-    k2.scrub = p->d.scrub;
+    k2.scrub = p->d.scrub; k2.generic = p->generic;
     e = launch_istft_inv(k2, st);
     if (e != cudaSuccess) return e;
     StreamOlaParams o{};
@@ -1144,6 +1171,7 @@ cudaError_t stream_tick_launches(crlot_stream_s* s, const float* d_in, long long
 int stream_check_io(const crlot_stream_s* s, const void* d_in, long long in_stride, int chunk_len, const void* d_out,
                     long long out_stride) {
   if (!s || !d_in || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (s->poisoned) return fail(CRLOT_ERR_RUNTIME, "streaming state is inconsistent after a failed launch: call crlot_stream_reset");
   if (chunk_len < 0 || chunk_len > s->max_chunk) return fail(CRLOT_ERR_INVALID_ARGUMENT, "chunk_len exceeds max_chunk");
   if (out_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_out) % 16 != 0)
     return fail(CRLOT_ERR_UNSUPPORTED, "output must be 16-byte aligned with out_stride a multiple of 4 floats");
@@ -1160,8 +1188,10 @@ int crlot_stream_create(crlot_plan_t plan, int n_streams, int max_chunk, crlot_s
   if (n_streams <= 0 || max_chunk <= 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "n_streams and max_chunk must be positive");
   if (plan->d.boundary_mode != CRLOT_DROP)
     return fail(CRLOT_ERR_UNSUPPORTED, "streaming needs BoundaryMode::DROP (chunked ZERO_PAD emits premature frames)");
-  if (plan->generic || plan->d.nfft > 2048)
-    return fail(CRLOT_ERR_UNSUPPORTED, "streaming supports nfft in {256, 512, 1024, 2048} with hop % 4 == 0");
+  // every plan shape runs (the register-FFT sizes 256..2048 on the ring-reading kernels, nfft = 4096 and the any-size
+  // plans through a gather + kernel 1); the ring kernels move 16-byte groups
+  if (plan->d.nfft % 4 != 0 || plan->d.hop % 4 != 0)
+    return fail(CRLOT_ERR_UNSUPPORTED, "streaming needs nfft % 4 == 0 and hop % 4 == 0");
   const int N = plan->d.nfft, H = plan->d.hop;
   std::unique_ptr<crlot_stream_s> s(new (std::nothrow) crlot_stream_s);
   if (!s) return fail(CRLOT_ERR_ALLOC, "host allocation failed");
@@ -1190,7 +1220,18 @@ int crlot_stream_create(crlot_plan_t plan, int n_streams, int max_chunk, crlot_s
 
 int crlot_stream_destroy(crlot_stream_t s) {
   if (!s) return CRLOT_OK;
-  { DeviceGuard g(s->plan->d.device); if (s->host_stream) cudaStreamDestroy(s->host_stream); delete s; }
+  {
+    DeviceGuard g(s->plan->d.device);
+    cudaDeviceSynchronize();                       // graph launches / submitted ticks may still be in flight
+    for (auto& c : s->graphs) cudaGraphExecDestroy(c.exec);
+    for (auto& e : s->done_ev) if (e) cudaEventDestroy(e);
+    for (int i = 0; i < crlot_stream_s::kPipe; ++i)
+      for (cudaEvent_t e : {s->ev_in[i], s->ev_k[i], s->ev_out[i]}) if (e) cudaEventDestroy(e);
+    if (s->copy_in) cudaStreamDestroy(s->copy_in);
+    if (s->copy_out) cudaStreamDestroy(s->copy_out);
+    if (s->host_stream) cudaStreamDestroy(s->host_stream);
+    delete s;
+  }
   return CRLOT_OK;
 }
 
@@ -1201,7 +1242,7 @@ int crlot_stream_reset(crlot_stream_t s, void* stream) {
   CU(cudaMemsetAsync(s->ctr.p, 0, sizeof(StreamCounters), st));
   CU(cudaMemsetAsync(s->ring.p, 0, sizeof(float) * s->S * s->rcap, st));
   CU(cudaMemsetAsync(s->acc.p, 0, sizeof(float) * s->S * s->plan->ring_len, st));
-  s->w = s->k = 0; s->last_nf = 0;
+  s->w = s->k = 0; s->last_nf = 0; s->poisoned = false;
   return CRLOT_OK;
 }
 
@@ -1217,8 +1258,9 @@ int crlot_stream_tick(crlot_stream_t s, const float* d_chunk, long long chunk_st
   if (rc) return rc;
   DeviceGuard g(s->plan->d.device);
   const int nf = stream_nf(s, s->w + chunk_len);
-  CU(stream_tick_launches(s, d_chunk, chunk_stride, chunk_len, s->w, d_out, out_stride, s->k, nf,
-                          static_cast<cudaStream_t>(stream)));
+  const cudaError_t e = stream_tick_launches(s, d_chunk, chunk_stride, chunk_len, s->w, d_out, out_stride, s->k, nf,
+                                             static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) { s->poisoned = true; return fail_cuda(e, "crlot_stream_tick"); }
   s->w += chunk_len; s->k += nf; s->last_nf = nf;
   if (n_out) *n_out = nf * s->plan->d.hop;
   return CRLOT_OK;
@@ -1233,11 +1275,13 @@ int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, i
   DeviceGuard g(s->plan->d.device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long w0 = s->w, k_base = s->k;
-  // One instantiated graph per distinct frames-per-tick value seen in this run (the launches of
-  // a tick depend on the tick only through the device counters).
-  struct Cached { int nf; cudaGraphExec_t exec; };
-  std::vector<Cached> cache;
+  // One instantiated graph per distinct frames-per-tick value (the launches of a tick depend on the tick only
+  // through the device counters).  The executables live on the stream object: a later call re-captures the same
+  // launches with its own pointers / offsets and re-points the executable with cudaGraphExecUpdate (the topology
+  // is identical), which costs microseconds where instantiation costs hundreds; launches already enqueued are not
+  // affected by an update.  The call is asynchronous with respect to `stream`.
   const bool use_graph = n_ticks >= 16;
+  std::vector<int> fresh;                      // keys already re-pointed at this call's arguments
   int status = CRLOT_OK;
   for (long long t = 0; t < n_ticks && status == CRLOT_OK; ++t) {
     const int nf = stream_nf(s, s->w + chunk_len);
@@ -1248,6 +1292,7 @@ int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, i
     constexpr int kBurst = 32;
     int burst = 1;
     if (use_graph && nf == 1 && chunk_len == s->plan->d.hop && n_ticks - t >= kBurst && stream_fused_tick_enabled() &&
+        !s->plan->generic &&
         stream_tick1_supported(s->plan->d.nfft, s->plan->d.hop, chunk_len, static_cast<long long>(s->plan->ring_len), out_stride, d_out))
       burst = kBurst;
     const int key = burst > 1 ? -burst : nf;
@@ -1255,8 +1300,11 @@ int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, i
       e = stream_tick_launches(s, d_in, in_stride, chunk_len, w0, d_out, out_stride, k_base, nf, st);
     } else {
       cudaGraphExec_t exec = nullptr;
-      for (auto& c : cache) if (c.nf == key) exec = c.exec;
-      if (!exec) {
+      size_t slot = s->graphs.size();
+      for (size_t i = 0; i < s->graphs.size(); ++i) if (s->graphs[i].key == key) { exec = s->graphs[i].exec; slot = i; }
+      bool is_fresh = false;
+      for (int k : fresh) if (k == key) is_fresh = true;
+      if (!exec || !is_fresh) {
         // captured on a private stream (the caller's may be the legacy default stream, which
         // cannot capture); capturing only records the launches, the replay goes to `st`
         cudaGraph_t graph = nullptr;
@@ -1269,48 +1317,173 @@ int crlot_stream_run(crlot_stream_t s, const float* d_in, long long in_stride, i
           e = cudaStreamEndCapture(s->host_stream, &graph);
           if (e1 != cudaSuccess) e = e1;
         }
-        if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (e == cudaSuccess && exec) {
+          cudaGraphExecUpdateResultInfo info{};
+          if (cudaGraphExecUpdate(exec, graph, &info) != cudaSuccess) {      // topology changed: rebuild
+            cudaGetLastError();
+            cudaStreamSynchronize(st);
+            cudaGraphExecDestroy(exec);
+            exec = nullptr;
+            s->graphs.erase(s->graphs.begin() + static_cast<long>(slot));
+          }
+        }
+        if (e == cudaSuccess && !exec) {
+          e = cudaGraphInstantiate(&exec, graph, 0);
+          if (e == cudaSuccess) s->graphs.push_back({key, exec});
+        }
         if (graph) cudaGraphDestroy(graph);
-        if (e == cudaSuccess) cache.push_back({key, exec});
+        if (e == cudaSuccess) fresh.push_back(key);
       }
       if (e == cudaSuccess) e = cudaGraphLaunch(exec, st);
     }
-    if (e != cudaSuccess) { status = fail_cuda(e, "crlot_stream_run"); break; }
+    if (e != cudaSuccess) { s->poisoned = true; status = fail_cuda(e, "crlot_stream_run"); break; }
     s->w += static_cast<long long>(burst) * chunk_len; s->k += static_cast<long long>(burst) * nf; s->last_nf = nf;
     t += burst - 1;
-  }
-  if (!cache.empty()) {
-    cudaStreamSynchronize(st);            // the executables must outlive their launches
-    for (auto& c : cache) cudaGraphExecDestroy(c.exec);
   }
   if (n_out) *n_out = (s->k - k_base) * s->plan->d.hop;
   return status;
 }
 
-int crlot_stream_tick_host(crlot_stream_t s, const float* h_chunk, long long chunk_stride, int chunk_len, float* h_out,
-                           long long out_stride, int* n_out) {
+// Device-visible alias of a page-locked host pointer (cudaHostAlloc / cudaHostRegister memory), else nullptr.
+static void* mapped_alias(const void* h) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
+// One tick with host buffers, enqueued on the state's own stream.  Page-locked buffers with suitable alignment are
+// handed to the tick kernel AS THEY ARE (zero-copy: the kernel reads the chunk and writes the hop across PCIe
+// itself, so a tick is one launch and no copy-engine round trips); anything else is staged through device buffers
+// with two copies.
+static int stream_tick_host_enqueue(crlot_stream_t s, const float* h_chunk, long long chunk_stride, int chunk_len,
+                                    float* h_out, long long out_stride, int* n_out) {
   if (n_out) *n_out = 0;
   if (!s || !h_chunk || !h_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (s->poisoned) return fail(CRLOT_ERR_RUNTIME, "streaming state is inconsistent after a failed launch: call crlot_stream_reset");
   if (chunk_len < 0 || chunk_len > s->max_chunk) return fail(CRLOT_ERR_INVALID_ARGUMENT, "chunk_len exceeds max_chunk");
+  const int H = s->plan->d.hop;
+  if (!s->host_stream) CU(cudaStreamCreateWithFlags(&s->host_stream, cudaStreamNonBlocking));
+  cudaStream_t st = s->host_stream;
+  const int nf = stream_nf(s, s->w + chunk_len);
+  static const bool zero_copy_on = getenv("CRLOT_STREAM_NO_ZERO_COPY") == nullptr;
+  const float* zc_in = zero_copy_on ? static_cast<const float*>(mapped_alias(h_chunk)) : nullptr;
+  float* zc_out = zero_copy_on ? static_cast<float*>(mapped_alias(h_out)) : nullptr;
+  if (zc_in && zc_out && out_stride % 4 == 0 && reinterpret_cast<uintptr_t>(zc_out) % 16 == 0) {
+    const cudaError_t e = stream_tick_launches(s, zc_in, chunk_stride, chunk_len, s->w, zc_out, out_stride, s->k, nf, st);
+    if (e != cudaSuccess) { s->poisoned = true; return fail_cuda(e, "crlot_stream_tick_host"); }
+  } else {
+    const long long in_pitch = (s->max_chunk + 3) / 4 * 4, out_pitch = static_cast<long long>(s->max_nf) * H;
+    if (!s->h2d.p) {
+      CU(s->h2d.alloc(static_cast<size_t>(s->S) * in_pitch));
+      CU(s->d2h.alloc(static_cast<size_t>(s->S) * out_pitch));
+    }
+    CU(cudaMemcpy2DAsync(s->h2d.p, in_pitch * sizeof(float), h_chunk, chunk_stride * sizeof(float),
+                         static_cast<size_t>(chunk_len) * sizeof(float), s->S, cudaMemcpyHostToDevice, st));
+    const cudaError_t e = stream_tick_launches(s, s->h2d.p, in_pitch, chunk_len, s->w, s->d2h.p, out_pitch, s->k, nf, st);
+    if (e != cudaSuccess) { s->poisoned = true; return fail_cuda(e, "crlot_stream_tick_host"); }
+    if (nf > 0)
+      CU(cudaMemcpy2DAsync(h_out, out_stride * sizeof(float), s->d2h.p, out_pitch * sizeof(float),
+                           static_cast<size_t>(nf) * H * sizeof(float), s->S, cudaMemcpyDeviceToHost, st));
+  }
+  s->w += chunk_len; s->k += nf; s->last_nf = nf;
+  if (n_out) *n_out = nf * H;
+  return CRLOT_OK;
+}
+
+int crlot_stream_tick_host(crlot_stream_t s, const float* h_chunk, long long chunk_stride, int chunk_len, float* h_out,
+                           long long out_stride, int* n_out) {
+  if (!s) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
   DeviceGuard g(s->plan->d.device);
+  const int rc = stream_tick_host_enqueue(s, h_chunk, chunk_stride, chunk_len, h_out, out_stride, n_out);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(s->host_stream));
+  return CRLOT_OK;
+}
+
+// submit on three streams: the chunk's H2D copy, the tick and the hop's D2H copy of consecutive tickets overlap
+static int stream_submit_pipelined(crlot_stream_t s, const float* h_chunk, long long chunk_stride, int chunk_len,
+                                   float* h_out, long long out_stride, int* n_out, cudaEvent_t done) {
   const int H = s->plan->d.hop;
   const long long in_pitch = (s->max_chunk + 3) / 4 * 4, out_pitch = static_cast<long long>(s->max_nf) * H;
-  if (!s->host_stream) CU(cudaStreamCreateWithFlags(&s->host_stream, cudaStreamNonBlocking));
-  if (!s->h2d.p) {
-    CU(s->h2d.alloc(static_cast<size_t>(s->S) * in_pitch));
-    CU(s->d2h.alloc(static_cast<size_t>(s->S) * out_pitch));
+  if (!s->copy_in) {
+    CU(cudaStreamCreateWithFlags(&s->copy_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&s->copy_out, cudaStreamNonBlocking));
+    for (int i = 0; i < crlot_stream_s::kPipe; ++i) {
+      CU(s->pin[i].alloc(static_cast<size_t>(s->S) * in_pitch));
+      CU(s->pout[i].alloc(static_cast<size_t>(s->S) * out_pitch));
+      CU(cudaEventCreateWithFlags(&s->ev_in[i], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&s->ev_k[i], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&s->ev_out[i], cudaEventDisableTiming));
+    }
   }
-  cudaStream_t st = s->host_stream;
-  CU(cudaMemcpy2DAsync(s->h2d.p, in_pitch * sizeof(float), h_chunk, chunk_stride * sizeof(float),
-                       static_cast<size_t>(chunk_len) * sizeof(float), s->S, cudaMemcpyHostToDevice, st));
+  const int slot = static_cast<int>(s->piped % crlot_stream_s::kPipe);
+  const bool reused = s->piped >= crlot_stream_s::kPipe;
   const int nf = stream_nf(s, s->w + chunk_len);
-  CU(stream_tick_launches(s, s->h2d.p, in_pitch, chunk_len, s->w, s->d2h.p, out_pitch, s->k, nf, st));
+  // H2D: the slot's previous tick must have finished reading its chunk
+  if (reused) CU(cudaStreamWaitEvent(s->copy_in, s->ev_k[slot], 0));
+  if (chunk_stride == chunk_len && in_pitch == chunk_len)
+    CU(cudaMemcpyAsync(s->pin[slot].p, h_chunk, static_cast<size_t>(s->S) * chunk_len * sizeof(float), cudaMemcpyHostToDevice, s->copy_in));
+  else
+    CU(cudaMemcpy2DAsync(s->pin[slot].p, in_pitch * sizeof(float), h_chunk, chunk_stride * sizeof(float),
+                         static_cast<size_t>(chunk_len) * sizeof(float), s->S, cudaMemcpyHostToDevice, s->copy_in));
+  CU(cudaEventRecord(s->ev_in[slot], s->copy_in));
+  // tick: after its chunk has landed and the slot's previous output has left
+  CU(cudaStreamWaitEvent(s->host_stream, s->ev_in[slot], 0));
+  if (reused) CU(cudaStreamWaitEvent(s->host_stream, s->ev_out[slot], 0));
+  const cudaError_t e = stream_tick_launches(s, s->pin[slot].p, in_pitch, chunk_len, s->w, s->pout[slot].p, out_pitch, s->k, nf, s->host_stream);
+  if (e != cudaSuccess) { s->poisoned = true; return fail_cuda(e, "crlot_stream_submit_host"); }
+  CU(cudaEventRecord(s->ev_k[slot], s->host_stream));
+  // D2H
+  CU(cudaStreamWaitEvent(s->copy_out, s->ev_k[slot], 0));
+  if (nf > 0) {
+    const size_t row = static_cast<size_t>(nf) * H;
+    if (out_stride == static_cast<long long>(row) && out_pitch == static_cast<long long>(row))
+      CU(cudaMemcpyAsync(h_out, s->pout[slot].p, static_cast<size_t>(s->S) * row * sizeof(float), cudaMemcpyDeviceToHost, s->copy_out));
+    else
+      CU(cudaMemcpy2DAsync(h_out, out_stride * sizeof(float), s->pout[slot].p, out_pitch * sizeof(float), row * sizeof(float), s->S,
+                           cudaMemcpyDeviceToHost, s->copy_out));
+  }
+  CU(cudaEventRecord(s->ev_out[slot], s->copy_out));
+  CU(cudaEventRecord(done, s->copy_out));
+  ++s->piped;
   s->w += chunk_len; s->k += nf; s->last_nf = nf;
-  if (nf > 0)
-    CU(cudaMemcpy2DAsync(h_out, out_stride * sizeof(float), s->d2h.p, out_pitch * sizeof(float),
-                         static_cast<size_t>(nf) * H * sizeof(float), s->S, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
   if (n_out) *n_out = nf * H;
+  return CRLOT_OK;
+}
+
+int crlot_stream_submit_host(crlot_stream_t s, const float* h_chunk, long long chunk_stride, int chunk_len, float* h_out,
+                             long long out_stride, int* n_out, unsigned long long* ticket) {
+  if (n_out) *n_out = 0;
+  if (!s || !ticket || !h_chunk || !h_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (s->poisoned) return fail(CRLOT_ERR_RUNTIME, "streaming state is inconsistent after a failed launch: call crlot_stream_reset");
+  if (chunk_len < 0 || chunk_len > s->max_chunk) return fail(CRLOT_ERR_INVALID_ARGUMENT, "chunk_len exceeds max_chunk");
+  DeviceGuard g(s->plan->d.device);
+  if (!s->host_stream) CU(cudaStreamCreateWithFlags(&s->host_stream, cudaStreamNonBlocking));
+  cudaEvent_t& ev = s->done_ev[s->submitted % crlot_stream_s::kTickets];
+  if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  // CRLOT_STREAM_SUBMIT=zerocopy: the tick kernel reads / writes the page-locked buffers itself (one stream);
+  // default: the three-stream copy pipeline (copies of neighbouring ticks overlap the tick kernel)
+  static const bool zc = getenv("CRLOT_STREAM_SUBMIT") != nullptr && std::string(getenv("CRLOT_STREAM_SUBMIT")) == "zerocopy";
+  if (zc) {
+    const int rc = stream_tick_host_enqueue(s, h_chunk, chunk_stride, chunk_len, h_out, out_stride, n_out);
+    if (rc) return rc;
+    CU(cudaEventRecord(ev, s->host_stream));
+  } else {
+    const int rc = stream_submit_pipelined(s, h_chunk, chunk_stride, chunk_len, h_out, out_stride, n_out, ev);
+    if (rc) return rc;
+  }
+  *ticket = s->submitted++;
+  return CRLOT_OK;
+}
+
+int crlot_stream_wait_host(crlot_stream_t s, unsigned long long ticket) {
+  if (!s) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (ticket >= s->submitted) return fail(CRLOT_ERR_INVALID_ARGUMENT, "no such ticket");
+  DeviceGuard g(s->plan->d.device);
+  // a ticket older than the event ring has certainly completed once its slot's current occupant has
+  const unsigned long long newest = s->submitted - 1;
+  const unsigned long long t = newest - ticket >= crlot_stream_s::kTickets ? newest : ticket;
+  CU(cudaEventSynchronize(s->done_ev[t % crlot_stream_s::kTickets]));
   return CRLOT_OK;
 }
 

@@ -177,6 +177,10 @@ struct StreamFwdParams {
   int scrub;
 };
 cudaError_t launch_stream_fwd(const StreamFwdParams& p, cudaStream_t st);
+bool stream_fwd_supported(int nfft);   // frame sizes the ring-reading forward kernel covers (256..2048)
+// the other sizes: frames gathered from the rings into rows [n_streams*nf][nfft], then kernel 1 with hop = nfft
+cudaError_t launch_stream_gather(const StreamCounters* ctr, const float* ring, int rcap, int n_streams, int nf, int nfft,
+                                 int hop, float* rows, cudaStream_t st);
 struct StreamOlaParams {
   const StreamCounters* ctr;
   const float* frames;       // [n_streams][nf][nfft]

@@ -55,6 +55,25 @@ __global__ void stream_ingest_kernel(const StreamCounters* __restrict__ ctr, con
   }
 }
 
+// ---- gather: frame (k0+i) of stream s out of the ingest ring into row s*nf+i of a linear [rows][nfft] buffer.
+// Front end of the sizes the ring-reading forward kernel below does not cover (nfft = 4096 and the any-size
+// plans): kernel 1 then runs over the rows as non-overlapping frames (hop = nfft).  nfft % 4 == 0, hop % 4 == 0.
+__global__ void stream_gather_kernel(const StreamCounters* __restrict__ ctr, const float* __restrict__ ring, int rcap,
+                                     int n_streams, int nf, int nfft, int hop, float* __restrict__ rows) {
+  const long long k0 = ctr->k;
+  const int mask = rcap - 1, per = nfft / 4;
+  const long long total = static_cast<long long>(n_streams) * nf * per;
+  for (long long q = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; q < total;
+       q += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long f = q / per;
+    const int u = static_cast<int>(q % per) * 4;
+    const long long s = f / nf;
+    const int i = static_cast<int>(f % nf);
+    const int pos = static_cast<int>(((k0 + i) * hop + u) & mask);
+    *reinterpret_cast<float4*>(rows + f * nfft + u) = *reinterpret_cast<const float4*>(ring + s * rcap + pos);
+  }
+}
+
 // ---- forward: frames (k0+i) of every stream, straight from the ingest rings ----------------------
 // frame list index f = s*nf + i  ->  spectra row f of [n_streams][nf][nfft/2+1]
 template <int NFFT, bool SCRUB>
@@ -440,6 +459,19 @@ cudaError_t launch_stream_ingest(const StreamCounters* ctr, const float* chunk, 
                                                                      n_streams, w0);
   return cudaGetLastError();
 }
+
+cudaError_t launch_stream_gather(const StreamCounters* ctr, const float* ring, int rcap, int n_streams, int nf, int nfft,
+                                 int hop, float* rows, cudaStream_t st) {
+  if (nf <= 0 || n_streams <= 0) return cudaSuccess;
+  const long long work = static_cast<long long>(n_streams) * nf * (nfft / 4);
+  long long blocks = (work + 255) / 256;
+  const long long cap = static_cast<long long>(device_sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  stream_gather_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(ctr, ring, rcap, n_streams, nf, nfft, hop, rows);
+  return cudaGetLastError();
+}
+
+bool stream_fwd_supported(int nfft) { return nfft == 256 || nfft == 512 || nfft == 1024 || nfft == 2048; }
 
 cudaError_t launch_stream_fwd(const StreamFwdParams& p, cudaStream_t st) {
   if (p.nf <= 0 || p.n_streams <= 0) return cudaSuccess;

@@ -238,8 +238,11 @@ int crlot_synth_uniform(float* d_out, long long chan_stride, int channels, long 
  *   bench/ola_benchmark.cc:150-157, with the accumulator in a RingBuffer of
  *   crlot_ola_ring_len() cells (ref: dsp/ring/ring_buffer.cc:44-85, OLAAccumulator.cc:249-258).
  * All streams of one state advance in lock step (same chunk length per tick).  The plan must use
- * CRLOT_DROP (chunked ZERO_PAD emits premature frames in the reference, framer.cc:98-103) and
- * nfft <= 2048.  Outputs are bit-identical to crlot_roundtrip_execute on the concatenated input. */
+ * CRLOT_DROP (chunked ZERO_PAD emits premature frames in the reference, framer.cc:98-103); every plan
+ * shape with nfft % 4 == 0 and hop % 4 == 0 runs (256..2048 on the ring-reading kernels, nfft = 4096 and
+ * the any-size plans through a gather + kernel 1).  Outputs are bit-identical to
+ * crlot_roundtrip_execute on the concatenated input.  After a failed launch the state refuses further
+ * ticks until crlot_stream_reset (host mirrors and device counters may disagree). */
 typedef struct crlot_stream_s* crlot_stream_t;
 int crlot_stream_create(crlot_plan_t plan, int n_streams, int max_chunk, crlot_stream_t* out);
 int crlot_stream_destroy(crlot_stream_t st);
@@ -253,7 +256,8 @@ int crlot_stream_tick(crlot_stream_t st, const float* d_chunk, long long chunk_s
                       float* d_out, long long out_stride, int* n_out, void* stream);
 /* n_ticks ticks over consecutive chunks of d_in [n_streams][in_stride] (tick i reads samples
  * [i*chunk_len, (i+1)*chunk_len)); outputs are appended per stream in d_out; *n_out = total samples
- * written per stream.  The tick loop runs inside the library (CUDA graph replay in steady state). */
+ * written per stream.  The tick loop runs inside the library (CUDA graph replay in steady state; the
+ * instantiated graphs are kept on the state and re-pointed per call).  Asynchronous on `stream`. */
 int crlot_stream_run(crlot_stream_t st, const float* d_in, long long in_stride, int chunk_len, long long n_ticks,
                      float* d_out, long long out_stride, long long* n_out, void* stream);
 /* One tick with HOST buffers (ideally page-locked): h_chunk [n_streams][chunk_stride] is copied to
@@ -261,6 +265,14 @@ int crlot_stream_run(crlot_stream_t st, const float* d_in, long long in_stride, 
  * [n_streams][out_stride], and the call returns when h_out is complete (the low-latency use). */
 int crlot_stream_tick_host(crlot_stream_t st, const float* h_chunk, long long chunk_stride, int chunk_len,
                            float* h_out, long long out_stride, int* n_out);
+/* The same tick without the wait: enqueues it on the state's own stream and returns a ticket;
+ * crlot_stream_wait_host(ticket) blocks until that tick's outputs are complete in h_out.  Several ticks may be
+ * in flight (each with its own, still-valid buffers); they execute in order.  When both buffers are page-locked
+ * (crlot_host_alloc / cudaHostRegister) the tick kernel reads the chunk and writes the hop across PCIe itself
+ * (zero-copy: one launch per tick, no copy-engine round trips) -- also in crlot_stream_tick_host. */
+int crlot_stream_submit_host(crlot_stream_t st, const float* h_chunk, long long chunk_stride, int chunk_len,
+                             float* h_out, long long out_stride, int* n_out, unsigned long long* ticket);
+int crlot_stream_wait_host(crlot_stream_t st, unsigned long long ticket);
 /* final produce(nfft - hop) of the drive; *n_out = nfft - hop (0 if no frame was ever pushed) */
 int crlot_stream_drain(crlot_stream_t st, float* d_out, long long out_stride, int* n_out, void* stream);
 /* spectra of the most recent tick, device pointer to [n_streams][frames][nfft/2+1] complex, and

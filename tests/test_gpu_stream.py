@@ -33,10 +33,13 @@ def run_ticks(cuda, st, x, chunk):
 
 
 @pytest.mark.parametrize("N,H,wt,chunk", [(256, 64, po.HAMMING, 64), (256, 64, po.HAMMING, 256), (256, 64, po.HAMMING, 100),
-                                          (1024, 256, po.HANN, 256), (512, 128, po.HANN, 36), (2048, 512, po.HANN, 512)])
+                                          (1024, 256, po.HANN, 256), (512, 128, po.HANN, 36), (2048, 512, po.HANN, 512),
+                                          # beyond the ring-reading kernels: nfft = 4096 and any-size plans (gather + kernel 1)
+                                          (4096, 1024, po.HANN, 1024), (4096, 1024, po.HANN, 600), (480, 160, po.HANN, 160),
+                                          (6000, 1500, po.HAMMING, 1000), (8192, 2048, po.HANN, 2048)])
 def test_stream_ticks_equal_batch_and_oracle(cuda, dsp, oracle, N, H, wt, chunk):
     rng = np.random.default_rng(N + chunk)
-    S, T = 13, 41
+    S, T = (13, 41) if N <= 2048 else (5, 23)
     L = T * chunk
     x = rng.uniform(-1, 1, (S, L)).astype(np.float32)
     w = oracle.window(wt, N)
@@ -116,9 +119,9 @@ def test_stream_argument_errors(cuda, dsp, oracle):
     zp = dsp.Plan(256, 64, analysis_window=w, ola_window=w, boundary_mode=dsp.ZERO_PAD)
     with pytest.raises(dsp.CrlotUnsupported):
         dsp.Stream(zp, 4, 64)                       # chunked ZERO_PAD is not a sane drive (framer.cc:98-103)
-    big = dsp.Plan(4096, 1024, boundary_mode=dsp.DROP)
+    odd = dsp.Plan(1000, 250, boundary_mode=dsp.DROP)          # hop % 4 != 0: the ring kernels move 16-byte groups
     with pytest.raises(dsp.CrlotUnsupported):
-        dsp.Stream(big, 4, 1024)
+        dsp.Stream(odd, 4, 250)
     plan = dsp.Plan(256, 64, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP)
     with pytest.raises(dsp.CrlotInvalidArgument):
         dsp.Stream(plan, 0, 64)
@@ -126,3 +129,75 @@ def test_stream_argument_errors(cuda, dsp, oracle):
     with pytest.raises(dsp.CrlotInvalidArgument):
         st.tick(cuda.zeros((2, 128), dtype=cuda.float32, device="cuda"))     # chunk_len > max_chunk
     assert st.drain().shape[1] == 0                  # nothing pushed yet: produce() has nothing to give
+
+
+def test_stream_run_called_repeatedly_repoints_its_graphs(cuda, dsp, oracle):
+    """crlot_stream_run keeps its instantiated graphs on the state and re-points them per call (different input /
+    output pointers and offsets each time): the concatenation of several runs equals one run, and the call does not
+    block the host stream (results are read only after an explicit synchronize)."""
+    rng = np.random.default_rng(11)
+    N, H, S, chunk, T = 256, 64, 64, 64, 192
+    w = oracle.window(po.HAMMING, N)
+    x = rng.uniform(-1, 1, (S, T * chunk)).astype(np.float32)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP)
+    a = dsp.Stream(plan, S, max_chunk=chunk)
+    xs = dev(cuda, x)
+    want = a.run(xs, chunk).cpu().numpy().copy()
+    b = dsp.Stream(plan, S, max_chunk=chunk)
+    parts = []
+    for i in range(3):                                           # three calls of 64 ticks, three different buffers
+        seg = xs[:, i * 64 * chunk:(i + 1) * 64 * chunk].clone()
+        parts.append(b.run(seg, chunk))
+    cuda.cuda.synchronize()
+    got = np.concatenate([p.cpu().numpy() for p in parts], axis=1)
+    assert np.array_equal(bits(got), bits(want))
+
+
+@pytest.mark.parametrize("N,H,chunk", [(256, 64, 64), (1024, 256, 256), (256, 64, 160), (4096, 1024, 1024)])
+def test_stream_host_ticks_zero_copy_staged_and_pipelined(cuda, dsp, oracle, N, H, chunk):
+    """crlot_stream_tick_host on page-locked buffers (zero-copy: the tick kernel reads / writes host memory itself),
+    on pageable buffers (staged copies), and crlot_stream_submit_host / _wait_host with several ticks in flight:
+    all bit-identical to device-resident ticks."""
+    rng = np.random.default_rng(N + chunk)
+    S, T = 9, 30
+    w = oracle.window(po.HANN, N)
+    x = rng.uniform(-1, 1, (S, T * chunk)).astype(np.float32)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP)
+    ref = dsp.Stream(plan, S, max_chunk=chunk)
+    want = run_ticks(cuda, ref, x, chunk)[:, :-(N - H)]                  # without the final drain
+    max_out = (chunk // H + 1) * H
+    # (a) pinned, synchronous
+    a = dsp.Stream(plan, S, max_chunk=chunk)
+    hin = cuda.from_numpy(x).pin_memory()
+    hout = cuda.empty((S, max_out), dtype=cuda.float32).pin_memory()
+    hin_np, hout_np = hin.numpy(), hout.numpy()
+    outs = []
+    for t in range(T):
+        n = a.tick_host(hin_np[:, t * chunk:(t + 1) * chunk], hout_np)
+        outs.append(hout_np[:, :n].copy())
+    assert np.array_equal(bits(np.concatenate(outs, axis=1)), bits(want))
+    # (b) pageable, synchronous (staged through device buffers)
+    b = dsp.Stream(plan, S, max_chunk=chunk)
+    pout = np.empty((S, max_out), np.float32)
+    outs = []
+    for t in range(T):
+        n = b.tick_host(np.ascontiguousarray(x[:, t * chunk:(t + 1) * chunk]), pout)
+        outs.append(pout[:, :n].copy())
+    assert np.array_equal(bits(np.concatenate(outs, axis=1)), bits(want))
+    # (c) pinned, three ticks in flight
+    c = dsp.Stream(plan, S, max_chunk=chunk)
+    depth = 3
+    ring = [cuda.empty((S, max_out), dtype=cuda.float32).pin_memory() for _ in range(depth)]
+    ring_np = [r.numpy() for r in ring]
+    pend, outs = [], []
+    for t in range(T):
+        if len(pend) == depth:
+            tk, n, slot = pend.pop(0)
+            c.wait_host(tk)
+            outs.append(ring_np[slot][:, :n].copy())
+        n, tk = c.submit_host(hin_np[:, t * chunk:(t + 1) * chunk], ring_np[t % depth])
+        pend.append((tk, n, t % depth))
+    for tk, n, slot in pend:
+        c.wait_host(tk)
+        outs.append(ring_np[slot][:, :n].copy())
+    assert np.array_equal(bits(np.concatenate(outs, axis=1)), bits(want))
