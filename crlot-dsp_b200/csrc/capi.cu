@@ -67,6 +67,40 @@ template <class T> struct DevArr {
   }
 };
 
+// page-locked host staging (true asynchronous copies, no driver bounce buffer)
+template <class T> struct PinnedArr {
+  T* p = nullptr;
+  size_t n = 0;
+  ~PinnedArr() { if (p) cudaFreeHost(p); }
+  cudaError_t resize(size_t count) {
+    if (p) { cudaFreeHost(p); p = nullptr; }
+    n = count;
+    return count ? cudaHostAlloc(reinterpret_cast<void**>(&p), count * sizeof(T), cudaHostAllocDefault) : cudaSuccess;
+  }
+  T* data() { return p; }
+  T& operator[](size_t i) { return p[i]; }
+};
+
+// "This host array is the unmodified output of my previous call and still lives on the device": the per-frame
+// drop-in loop (bench/e2e_benchmark.cc:152-166) hands each call's output array straight to the next call --
+// forward -> inverse -> push_frame_AoS.  A facade object records (caller's pointer, bytes, its device buffer, its
+// page-locked copy of what it delivered); the next call finds the entry by pointer, checks with one memcmp against
+// the page-locked copy that the caller has not touched the data, and then reads the device buffer instead of
+// uploading the same bytes again.  Entries die with their owner.
+struct Resident { const void* host; size_t bytes; const void* dev; const void* pinned; int device; const void* owner; };
+thread_local Resident g_resident[2] = {};
+void resident_publish(int slot, const void* host, size_t bytes, const void* dev, const void* pinned, int device, const void* owner) {
+  g_resident[slot] = Resident{host, bytes, dev, pinned, device, owner};
+}
+const void* resident_lookup(const void* host, size_t bytes, int device) {
+  for (const Resident& r : g_resident)
+    if (r.host == host && r.dev && r.device == device && r.bytes >= bytes && std::memcmp(r.pinned, host, bytes) == 0) return r.dev;
+  return nullptr;
+}
+void resident_forget(const void* owner) {
+  for (Resident& r : g_resident) if (r.owner == owner) r = Resident{};
+}
+
 }  // namespace
 
 struct crlot_buf_s {
@@ -742,8 +776,7 @@ struct crlot_fft_s {
   crlot_plan_t plan = nullptr;
   DevArr<float> d_time;
   DevArr<cpx> d_freq;
-  std::vector<float> h_time;
-  std::vector<float> h_freq;
+  PinnedArr<float> h_time, h_freq;   // page-locked staging: copies are asynchronous, one synchronize per call
 };
 
 extern "C" {
@@ -769,14 +802,15 @@ int crlot_fft_plan_create(int nfft, int in_place, int batch, int stride_in, int 
   DeviceGuard g(device);
   cudaError_t e = f->d_time.alloc(static_cast<size_t>(batch) * nfft);
   if (e == cudaSuccess) e = f->d_freq.alloc(static_cast<size_t>(batch) * (nfft / 2 + 1));
-  if (e != cudaSuccess) { crlot_stft_plan_destroy(f->plan); return fail_cuda(e, "cudaMalloc"); }
-  f->h_time.resize(static_cast<size_t>(batch) * nfft);
-  f->h_freq.resize(static_cast<size_t>(batch) * (nfft / 2 + 1) * 2);
+  if (e == cudaSuccess) e = f->h_time.resize(static_cast<size_t>(batch) * nfft);
+  if (e == cudaSuccess) e = f->h_freq.resize(static_cast<size_t>(batch) * (nfft / 2 + 1) * 2);
+  if (e != cudaSuccess) { crlot_stft_plan_destroy(f->plan); return fail_cuda(e, "cudaHostAlloc"); }
   *out = f.release();
   return CRLOT_OK;
 }
 int crlot_fft_plan_destroy(crlot_fft_t f) {
   if (!f) return CRLOT_OK;
+  resident_forget(f);
   if (f->plan) crlot_stft_plan_destroy(f->plan);
   { DeviceGuard g(f->device); delete f; }
   return CRLOT_OK;
@@ -801,8 +835,8 @@ int crlot_fft_plan_create_complex(int nfft, int in_place, int batch, int stride_
   cudaError_t e = upload_cpx(f->ctw, T.tw1);
   if (e == cudaSuccess) e = f->d_cin.alloc(static_cast<size_t>(batch) * nfft);
   if (e == cudaSuccess) e = f->d_cout.alloc(static_cast<size_t>(batch) * nfft);
+  if (e == cudaSuccess) e = f->h_freq.resize(static_cast<size_t>(batch) * nfft * 2);
   if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc");
-  f->h_freq.resize(static_cast<size_t>(batch) * nfft * 2);
   *out = f.release();
   return CRLOT_OK;
 }
@@ -856,25 +890,43 @@ int crlot_fft_inverse_complex(crlot_fft_t f, const float* h_in_ri, float* h_out_
 }
 
 // forward: batch b reads in + b*si*n with element stride si; writes out + b*so*(n/2+1) with
-// element stride so (ref: kissfft_adapter.cc:97-98,103,118)
+// element stride so (ref: kissfft_adapter.cc:97-98,103,118).  One launch for the whole batch; copies through
+// page-locked staging on the default stream, ONE synchronize at the end.
 int crlot_fft_forward(crlot_fft_t f, const float* h_in, float* h_out_ri, int batch) {
   if (!f || !h_in || !h_out_ri) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
   if (f->complex_domain) return fail(CRLOT_ERR_RUNTIME, "Real FFT not supported for Complex domain plan");
   if (batch < 1 || batch > f->batch) return fail(CRLOT_ERR_RUNTIME, "Invalid batch size");
   const int n = f->nfft, nb = n / 2 + 1;
-  for (int b = 0; b < batch; ++b)
-    for (int i = 0; i < n; ++i) f->h_time[static_cast<size_t>(b) * n + i] = h_in[static_cast<long long>(b) * f->si * n + static_cast<long long>(i) * f->si];
   DeviceGuard g(f->device);
-  CU(cudaMemcpy(f->d_time.p, f->h_time.data(), sizeof(float) * batch * n, cudaMemcpyHostToDevice));
+  const size_t in_bytes = sizeof(float) * batch * n, out_bytes = sizeof(float) * 2 * batch * nb;
+  const void* dev_in = f->si == 1 ? resident_lookup(h_in, in_bytes, f->device) : nullptr;   // an earlier call's output?
+  if (dev_in) {
+    if (dev_in != f->d_time.p) {       // another object's buffer: our page-locked mirror no longer matches d_time
+      CU(cudaMemcpyAsync(f->d_time.p, dev_in, in_bytes, cudaMemcpyDeviceToDevice, nullptr));
+      resident_forget(f);
+    }
+  } else {
+    if (f->si == 1) std::memcpy(f->h_time.data(), h_in, in_bytes);
+    else
+      for (int b = 0; b < batch; ++b)
+        for (int i = 0; i < n; ++i) f->h_time[static_cast<size_t>(b) * n + i] = h_in[static_cast<long long>(b) * f->si * n + static_cast<long long>(i) * f->si];
+    CU(cudaMemcpyAsync(f->d_time.p, f->h_time.data(), in_bytes, cudaMemcpyHostToDevice, nullptr));
+  }
   int rc = crlot_stft_execute(f->plan, f->d_time.p, 0, static_cast<long long>(batch) * n, 1, batch, f->d_freq.p, nullptr);
   if (rc) return rc;
-  CU(cudaMemcpy(f->h_freq.data(), f->d_freq.p, sizeof(float) * 2 * batch * nb, cudaMemcpyDeviceToHost));
-  for (int b = 0; b < batch; ++b)
-    for (int i = 0; i < nb; ++i) {
-      const long long o = 2 * (static_cast<long long>(b) * f->so * nb + static_cast<long long>(i) * f->so);
-      h_out_ri[o] = f->h_freq[2 * (static_cast<size_t>(b) * nb + i)];
-      h_out_ri[o + 1] = f->h_freq[2 * (static_cast<size_t>(b) * nb + i) + 1];
-    }
+  CU(cudaMemcpyAsync(f->h_freq.data(), f->d_freq.p, out_bytes, cudaMemcpyDeviceToHost, nullptr));
+  CU(cudaStreamSynchronize(nullptr));
+  if (f->so == 1) {
+    std::memcpy(h_out_ri, f->h_freq.data(), out_bytes);
+    resident_publish(0, h_out_ri, out_bytes, f->d_freq.p, f->h_freq.data(), f->device, f);
+  } else {
+    for (int b = 0; b < batch; ++b)
+      for (int i = 0; i < nb; ++i) {
+        const long long o = 2 * (static_cast<long long>(b) * f->so * nb + static_cast<long long>(i) * f->so);
+        h_out_ri[o] = f->h_freq[2 * (static_cast<size_t>(b) * nb + i)];
+        h_out_ri[o + 1] = f->h_freq[2 * (static_cast<size_t>(b) * nb + i) + 1];
+      }
+  }
   return CRLOT_OK;
 }
 // inverse: batch b reads in + b*si*(n/2+1) with element stride si; writes out + b*so*n with
@@ -884,19 +936,36 @@ int crlot_fft_inverse(crlot_fft_t f, const float* h_in_ri, float* h_out, int bat
   if (f->complex_domain) return fail(CRLOT_ERR_RUNTIME, "Real FFT not supported for Complex domain plan");
   if (batch < 1 || batch > f->batch) return fail(CRLOT_ERR_RUNTIME, "Invalid batch size");
   const int n = f->nfft, nb = n / 2 + 1;
-  for (int b = 0; b < batch; ++b)
-    for (int i = 0; i < nb; ++i) {
-      const long long s = 2 * (static_cast<long long>(b) * f->si * nb + static_cast<long long>(i) * f->si);
-      f->h_freq[2 * (static_cast<size_t>(b) * nb + i)] = h_in_ri[s];
-      f->h_freq[2 * (static_cast<size_t>(b) * nb + i) + 1] = h_in_ri[s + 1];
-    }
   DeviceGuard g(f->device);
-  CU(cudaMemcpy(f->d_freq.p, f->h_freq.data(), sizeof(float) * 2 * batch * nb, cudaMemcpyHostToDevice));
+  const size_t in_bytes = sizeof(float) * 2 * batch * nb, out_bytes = sizeof(float) * batch * n;
+  const void* dev_in = f->si == 1 ? resident_lookup(h_in_ri, in_bytes, f->device) : nullptr;   // untouched forward() output?
+  if (dev_in) {
+    if (dev_in != f->d_freq.p) {
+      CU(cudaMemcpyAsync(f->d_freq.p, dev_in, in_bytes, cudaMemcpyDeviceToDevice, nullptr));
+      resident_forget(f);
+    }
+  } else {
+    if (f->si == 1) std::memcpy(f->h_freq.data(), h_in_ri, in_bytes);
+    else
+      for (int b = 0; b < batch; ++b)
+        for (int i = 0; i < nb; ++i) {
+          const long long q = 2 * (static_cast<long long>(b) * f->si * nb + static_cast<long long>(i) * f->si);
+          f->h_freq[2 * (static_cast<size_t>(b) * nb + i)] = h_in_ri[q];
+          f->h_freq[2 * (static_cast<size_t>(b) * nb + i) + 1] = h_in_ri[q + 1];
+        }
+    CU(cudaMemcpyAsync(f->d_freq.p, f->h_freq.data(), in_bytes, cudaMemcpyHostToDevice, nullptr));
+  }
   int rc = crlot_istft_execute(f->plan, f->d_freq.p, batch, f->d_time.p, 0, nullptr);
   if (rc) return rc;
-  CU(cudaMemcpy(f->h_time.data(), f->d_time.p, sizeof(float) * batch * n, cudaMemcpyDeviceToHost));
-  for (int b = 0; b < batch; ++b)
-    for (int i = 0; i < n; ++i) h_out[static_cast<long long>(b) * f->so * n + static_cast<long long>(i) * f->so] = f->h_time[static_cast<size_t>(b) * n + i];
+  CU(cudaMemcpyAsync(f->h_time.data(), f->d_time.p, out_bytes, cudaMemcpyDeviceToHost, nullptr));
+  CU(cudaStreamSynchronize(nullptr));
+  if (f->so == 1) {
+    std::memcpy(h_out, f->h_time.data(), out_bytes);
+    resident_publish(1, h_out, out_bytes, f->d_time.p, f->h_time.data(), f->device, f);
+  } else {
+    for (int b = 0; b < batch; ++b)
+      for (int i = 0; i < n; ++i) h_out[static_cast<long long>(b) * f->so * n + static_cast<long long>(i) * f->so] = f->h_time[static_cast<size_t>(b) * n + i];
+  }
   return CRLOT_OK;
 }
 
@@ -913,7 +982,9 @@ struct crlot_ola_s {
   size_t read_pos = 0, produced = 0;
   float peak = 0.0f;
   DevArr<float> ring, norm, win, call_win, stage;
-  std::vector<float> h_stage, h_norm, h_win;
+  PinnedArr<float> h_stage;           // page-locked staging of frames in / samples out
+  bool stage_busy = false;            // an asynchronous upload from h_stage may still be in flight
+  std::vector<float> h_norm, h_win;
   void rebuild_norm() {   // ref: OLAAccumulator::initialize_normalization
     h_norm.resize(ring_len);
     envelope_impl(h_norm.data(), has_window ? h_win.data() : nullptr, ring_len, N, H, inside, eps);
@@ -941,7 +1012,7 @@ int crlot_ola_create(int sample_rate, size_t frame_size, size_t hop_size, size_t
   CU(o->win.alloc(frame_size));
   CU(o->call_win.alloc(frame_size));
   CU(o->stage.alloc(std::max(o->ring_len, frame_size) * channels));
-  o->h_stage.resize(std::max(o->ring_len, frame_size) * channels);
+  CU(o->h_stage.resize(std::max(o->ring_len, frame_size) * channels));
   *out = o.release();
   return CRLOT_OK;
 }
@@ -963,23 +1034,36 @@ int crlot_ola_set_window(crlot_ola_t o, const float* w, int wlen) {
   return CRLOT_OK;
 }
 
-static int ola_add_staged(crlot_ola_t o, const float* window, size_t start, size_t off, size_t size, float gain) {
-  // h_stage holds [C][size] planar samples already offset by `off`
+// Frames are accumulated ASYNCHRONOUSLY (nothing comes back to the host): the upload from the page-locked stage and
+// the ring kernel are enqueued on the default stream and the call returns; the next call that rewrites the stage,
+// and produce(), order themselves behind them.  d_src != nullptr: the samples are already on the device (the
+// caller handed over an untouched IFftPlan::inverse output, see Resident above) -- no upload at all.
+static int ola_wait_stage(crlot_ola_t o) {
+  if (o->stage_busy) { CU(cudaStreamSynchronize(nullptr)); o->stage_busy = false; }
+  return CRLOT_OK;
+}
+static int ola_add_staged(crlot_ola_t o, const float* window, size_t start, size_t off, size_t size, float gain,
+                          const float* d_src) {
+  // h_stage (or d_src) holds [C][size] planar samples already offset by `off`
   const bool use = o->inside ? o->has_window : (window != nullptr);
   const float* dwin = nullptr;
   if (use) {
     if (o->inside) dwin = o->win.p + off;
     else {
-      CU(cudaMemcpy(o->call_win.p, window + off, sizeof(float) * size, cudaMemcpyHostToDevice));
+      CU(cudaMemcpyAsync(o->call_win.p, window + off, sizeof(float) * size, cudaMemcpyHostToDevice, nullptr));
+      CU(cudaStreamSynchronize(nullptr));        // `window` is the caller's (pageable) memory
       dwin = o->call_win.p;
     }
   }
   const size_t n = std::min(size, o->ring_len);    // RingBuffer::split clamps to capacity
-  CU(cudaMemcpy(o->stage.p, o->h_stage.data(), sizeof(float) * size * o->C, cudaMemcpyHostToDevice));
-  CU(launch_ring_axpy(o->ring.p, static_cast<long long>(o->ring_len), static_cast<int>(o->C), o->stage.p,
+  if (!d_src) {
+    CU(cudaMemcpyAsync(o->stage.p, o->h_stage.data(), sizeof(float) * size * o->C, cudaMemcpyHostToDevice, nullptr));
+    o->stage_busy = true;
+    d_src = o->stage.p;
+  }
+  CU(launch_ring_axpy(o->ring.p, static_cast<long long>(o->ring_len), static_cast<int>(o->C), d_src,
                       static_cast<long long>(size), dwin, gain, static_cast<long long>(start % o->ring_len),
                       static_cast<int>(n), nullptr));
-  CU(cudaStreamSynchronize(nullptr));
   o->produced = std::max(o->produced, start + size);
   return CRLOT_OK;
 }
@@ -990,12 +1074,17 @@ int crlot_ola_add_frame_soa(crlot_ola_t o, const float* const* ch_frames, const 
   if (!ch_frames) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Channel frames pointer cannot be null");
   if (size == 0 || start_off >= o->N) return CRLOT_OK;
   if (start_off + size > o->N) size = o->N - start_off;
-  for (size_t c = 0; c < o->C; ++c) {
+  for (size_t c = 0; c < o->C; ++c)
     if (!ch_frames[c]) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Channel frame pointer cannot be null");
-    std::copy(ch_frames[c] + start_off, ch_frames[c] + start_off + size, o->h_stage.begin() + c * size);
-  }
   DeviceGuard g(o->device);
-  return ola_add_staged(o, window, start_sample, start_off, size, gain);
+  if (o->C == 1) {
+    const void* dev = resident_lookup(ch_frames[0], sizeof(float) * o->N, o->device);
+    if (dev) return ola_add_staged(o, window, start_sample, start_off, size, gain, static_cast<const float*>(dev) + start_off);
+  }
+  int rc = ola_wait_stage(o);
+  if (rc) return rc;
+  for (size_t c = 0; c < o->C; ++c) std::memcpy(o->h_stage.data() + c * size, ch_frames[c] + start_off, sizeof(float) * size);
+  return ola_add_staged(o, window, start_sample, start_off, size, gain, nullptr);
 }
 int crlot_ola_push_frame_aos(crlot_ola_t o, const float* interleaved, const float* window, size_t start_sample,
                              size_t start_off, size_t size, float gain) {
@@ -1003,13 +1092,19 @@ int crlot_ola_push_frame_aos(crlot_ola_t o, const float* interleaved, const floa
   if (!interleaved) return fail(CRLOT_ERR_INVALID_ARGUMENT, "Interleaved input pointer cannot be null");
   if (size == 0 || start_off >= o->N) return CRLOT_OK;
   if (start_off + size > o->N) size = o->N - start_off;
-  const float* src = interleaved + start_off * o->C;      // ref: aos_to_soa.cc:13-17
-  for (size_t c = 0; c < o->C; ++c)
-    for (size_t i = 0; i < size; ++i) o->h_stage[c * size + i] = src[i * o->C + c];
   DeviceGuard g(o->device);
   // the reference re-enters add_frame_SoA with start_off = 0 on the de-interleaved scratch, so the
   // window (stored or per-call) is indexed from 0 there (OLAAccumulator.cc:159)
-  return ola_add_staged(o, window, start_sample, 0, size, gain);
+  if (o->C == 1) {                                          // one channel: interleaved == planar
+    const void* dev = resident_lookup(interleaved, sizeof(float) * o->N, o->device);
+    if (dev) return ola_add_staged(o, window, start_sample, 0, size, gain, static_cast<const float*>(dev) + start_off);
+  }
+  int rc = ola_wait_stage(o);
+  if (rc) return rc;
+  const float* src = interleaved + start_off * o->C;      // ref: aos_to_soa.cc:13-17
+  for (size_t c = 0; c < o->C; ++c)
+    for (size_t i = 0; i < size; ++i) o->h_stage[c * size + i] = src[i * o->C + c];
+  return ola_add_staged(o, window, start_sample, 0, size, gain, nullptr);
 }
 int crlot_ola_produce(crlot_ola_t o, float* const* ch_out, size_t n, size_t* produced_out) {
   if (produced_out) *produced_out = 0;
@@ -1026,8 +1121,10 @@ int crlot_ola_produce(crlot_ola_t o, float* const* ch_out, size_t n, size_t* pro
   CU(launch_ring_produce(o->ring.p, static_cast<long long>(o->ring_len), static_cast<int>(o->C), o->norm.p, o->eps,
                          static_cast<long long>(o->read_pos % o->ring_len), static_cast<int>(m), o->stage.p,
                          static_cast<long long>(m), nullptr));
-  CU(cudaMemcpy(o->h_stage.data(), o->stage.p, sizeof(float) * m * o->C, cudaMemcpyDeviceToHost));
-  for (size_t c = 0; c < o->C; ++c) std::copy(o->h_stage.begin() + c * m, o->h_stage.begin() + (c + 1) * m, ch_out[c]);
+  CU(cudaMemcpyAsync(o->h_stage.data(), o->stage.p, sizeof(float) * m * o->C, cudaMemcpyDeviceToHost, nullptr));
+  CU(cudaStreamSynchronize(nullptr));
+  o->stage_busy = false;
+  for (size_t c = 0; c < o->C; ++c) std::memcpy(ch_out[c], o->h_stage.data() + c * m, sizeof(float) * m);
   o->read_pos = (o->read_pos + n) % o->ring_len;
   for (size_t i = 0; i < m; ++i) o->peak = std::max(o->peak, std::fabs(ch_out[0][i]));
   if (produced_out) *produced_out = n;

@@ -67,6 +67,12 @@ struct crlot_framer_s {
   // compaction of ensure_room never overwrites samples a kernel 1 launched earlier on another stream still reads.
   cudaEvent_t ev = nullptr;
   bool ev_pending = false;
+  // pop() read-ahead (one channel): the per-frame drop-in loop pops frame after frame, each only hop samples
+  // further on.  One D2H copy brings kAheadHops hops of the store into page-locked host memory and the following
+  // pops are served from it (the samples of [lo, hi) of the device store, which only ever grows behind w).
+  static constexpr long long kAheadHops = 64;
+  float* ahead = nullptr;
+  long long ahead_cap = 0, ahead_lo = 0, ahead_hi = 0;   // store indices covered; empty when lo == hi
 };
 
 // the library-wide last-error slot lives in capi.cu
@@ -143,6 +149,7 @@ int ensure_room(crlot_framer_s* f, long long add, cudaStream_t st) {
       FCU(cudaMemcpy2DAsync(f->buf, f->cap * sizeof(float), f->buf + r4, f->cap * sizeof(float),
                             keep * sizeof(float), f->C, cudaMemcpyDeviceToDevice, st));
     f->r -= r4; f->w -= r4;
+    f->ahead_lo = f->ahead_hi = 0;
     return CRLOT_OK;
   }
   long long ncap = std::max<long long>(need, 2 * f->cap);
@@ -158,6 +165,7 @@ int ensure_room(crlot_framer_s* f, long long add, cudaStream_t st) {
   if (f->buf) cudaFree(f->buf);
   f->buf = nb; f->cap = ncap;
   f->r -= r4; f->w -= r4;
+  f->ahead_lo = f->ahead_hi = 0;
   return CRLOT_OK;
 }
 
@@ -175,6 +183,7 @@ int realign(crlot_framer_s* f, cudaStream_t st) {
   cudaFree(f->buf);
   f->buf = nb;
   f->w = keep; f->r = 0;
+  f->ahead_lo = f->ahead_hi = 0;
   return CRLOT_OK;
 }
 
@@ -231,6 +240,7 @@ int crlot_framer_destroy(crlot_framer_t f) {
   if (f->ev) cudaEventDestroy(f->ev);
   if (f->buf) cudaFree(f->buf);
   if (f->stage) cudaFree(f->stage);
+  if (f->ahead) cudaFreeHost(f->ahead);
   delete f;
   return CRLOT_OK;
 }
@@ -238,6 +248,7 @@ int crlot_framer_destroy(crlot_framer_t f) {
 int crlot_framer_reset(crlot_framer_t f) {
   if (!f) return ffail(CRLOT_ERR_INVALID_ARGUMENT, "null framer");
   f->r = f->w = 0;
+  f->ahead_lo = f->ahead_hi = 0;
   ref_reset(f);
   return CRLOT_OK;
 }
@@ -305,8 +316,18 @@ int crlot_framer_pop(crlot_framer_t f, float* h_out_frame, int* popped) {
   }
   const long long avail = std::min<long long>(f->w - f->r, (long long)f->N);
   if (f->C == 1) {
-    FCU(cudaMemcpyAsync(h_out_frame, f->buf + f->r, (size_t)avail * sizeof(float), cudaMemcpyDeviceToHost, st));
-    FCU(cudaStreamSynchronize(st));
+    if (f->r < f->ahead_lo || f->r + avail > f->ahead_hi) {       // not covered by the read-ahead: refill it
+      const long long want = std::min<long long>(f->w - f->r, (long long)f->N + crlot_framer_s::kAheadHops * (long long)f->H);
+      if (!f->ahead) {
+        const long long cap = (long long)f->N + crlot_framer_s::kAheadHops * (long long)f->H;
+        FCU(cudaHostAlloc((void**)&f->ahead, (size_t)cap * sizeof(float), cudaHostAllocDefault));
+        f->ahead_cap = cap;
+      }
+      FCU(cudaMemcpyAsync(f->ahead, f->buf + f->r, (size_t)want * sizeof(float), cudaMemcpyDeviceToHost, st));
+      FCU(cudaStreamSynchronize(st));
+      f->ahead_lo = f->r; f->ahead_hi = f->r + want;
+    }
+    std::copy(f->ahead + (f->r - f->ahead_lo), f->ahead + (f->r - f->ahead_lo) + avail, h_out_frame);
     std::fill(h_out_frame + avail, h_out_frame + f->N, 0.0f);    // ZERO_PAD tail, framer.cc:157-159
   } else {
     int rc = ensure_stage(f, f->N * f->C);

@@ -175,5 +175,6 @@ def test_error_behaviour(cuda, dsp):
         dsp.FftPlan(16386)
     with pytest.raises(dsp.CrlotUnsupported):
         dsp.FftPlan(8193, complex_domain=True)
+    dsp.Stream(dsp.Plan(480, 160, boundary_mode=po.DROP), 4, 160)          # any-size plans stream too (gather + kernel 1)
     with pytest.raises(dsp.CrlotUnsupported):
-        dsp.Stream(dsp.Plan(480, 160, boundary_mode=po.DROP), 4, 160)
+        dsp.Stream(dsp.Plan(1000, 250, boundary_mode=po.DROP), 4, 250)     # ... unless hop % 4 != 0
