@@ -11,6 +11,8 @@
 // segments, the mirror bins come from one warp shuffle per value, frames are written straight
 // from registers.  Warp-steps are interleaved over the grid so neighbouring warps stream
 // neighbouring rows.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "warpfft.cuh"
@@ -116,20 +118,26 @@ constexpr int kK2Warps4096 = 8;
 constexpr int kK2Stage4096 = 2048 * 8;                       // bytes staged per row
 constexpr int kK2PerWarp4096 = kK2Stage4096 + Geo4096::FX_ROUND_CPX * 8 + 16;
 
-template <bool WIN, bool SCRUB>
+// TM: the per-lane inter-pass twiddles (2 x 32 complex, columns [0, 128)) and synthesis-window samples (64 complex,
+// columns [128, 256)) live in tensor memory instead of shared-memory tables (see k1_stft.cu).
+template <bool WIN, bool SCRUB, bool TM>
 __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(const K2Params p) {
   constexpr int NFFT = 4096, C = 2048;
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint32_t s_tmem_base;
   float* s_win = reinterpret_cast<float*>(smem_raw);
-  cpx* s_twi = reinterpret_cast<cpx*>(s_win + (WIN ? NFFT : 0));
+  cpx* s_twi = reinterpret_cast<cpx*>(s_win + (WIN && !TM ? NFFT : 0));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wb = reinterpret_cast<unsigned char*>(s_twi + C) + warp * kK2PerWarp4096;
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_twi + (TM ? 0 : C)) + warp * kK2PerWarp4096;
   cpx* stage = reinterpret_cast<cpx*>(wb);
   cpx* ex = stage + C;
   const uint32_t bar = smem_u32(ex + Geo4096::FX_ROUND_CPX);
-  if (WIN)
-    for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_twi[i] = p.pre[i];
+  const int a1 = Geo4096::row1(lane);
+  if (!TM) {
+    if (WIN)
+      for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i];
+    for (int i = threadIdx.x; i < C; i += blockDim.x) s_twi[i] = p.pre[i];
+  }
   const SplitLane4096 SL = make_split_4096<true>(lane);
   const Coop4096 CO = make_coop_4096<true>(lane);
   cpx dc = mk(0.f, 0.f);
@@ -137,10 +145,35 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
     mbar_init(bar, 1);
     fence_mbar_init();
   }
+  uint32_t ttw = 0, twin = 0;
+  if (TM) {
+    if (warp == 0) tmem_alloc<256>(&s_tmem_base);
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    ttw = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    twin = ttw + 128;
+    if (warp < 4) {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        cpx t8[8], w8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = 8 * c + i;                         // register r of the pass-1 view: ob = r & 31, column a0 / a1
+          t8[i] = p.pre[(r & 31) * 64 + (r < 32 ? lane : a1)];
+          w8[i] = WIN ? *reinterpret_cast<const cpx*>(p.window + 2 * (lane + 32 * r)) : mk(1.f, 1.f);
+        }
+        tmem_st8(ttw + 16 * c, t8);
+        tmem_st8(twin + 16 * c, w8);
+      }
+      tmem_wait_st();
+    }
+    tmem_fence_before_sync();
+  }
   __syncthreads();
+  if (TM) tmem_fence_after_sync();
   const long long stride = static_cast<long long>(gridDim.x) * kK2Warps4096;
   const float scale = 2.0f / static_cast<float>(NFFT);    // the split hands over halved values
-  const int a1 = Geo4096::row1(lane);
   uint32_t phase = 0;
   long long rowi = static_cast<long long>(blockIdx.x) * kK2Warps4096 + warp;
   // off = 1 when the row starts 8 bytes past a 16-byte boundary: stage[i] = bin i + off
@@ -207,7 +240,19 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
 
     if (lane != 0) split4096_general<true>(v, SL.q, SL.qr);
     inv4096_pass1(v);
-    inv4096_twiddle(v, lane, s_twi);
+    if (TM) {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        cpx t8[8];
+        tmem_ld8(ttw + 16 * c, t8);
+        tmem_wait_ld8(t8);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (((8 * c + i) & 31) != 0) v[8 * c + i] = cmulc(v[8 * c + i], t8[i]);
+      }
+    } else {
+      inv4096_twiddle(v, lane, s_twi);
+    }
     inv4096_xwrite<0>(v, lane, ex);
     __syncwarp();
     inv4096_xread<0>(v, lane, ex);
@@ -219,29 +264,49 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
     inv4096_pass2(v);
     float* dst = p.frames + rowi * NFFT;
 #pragma unroll
-    for (int oa = 0; oa < 64; ++oa) {
-      const int n = lane + 32 * oa;
-      float y0 = v[oa].x * scale, y1 = v[oa].y * scale;
-      if (SCRUB) {
-        y0 = scrub(y0);
-        y1 = scrub(y1);
+    for (int c = 0; c < 8; ++c) {
+      cpx w8[8];
+      if (TM && WIN) {
+        tmem_ld8(twin + 16 * c, w8);
+        tmem_wait_ld8(w8);
       }
-      if (WIN) {
-        const float2 w = *reinterpret_cast<const float2*>(s_win + 2 * n);
-        y0 = __fmul_rn(y0, w.x);
-        y1 = __fmul_rn(y1, w.y);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int oa = 8 * c + i;
+        const int n = lane + 32 * oa;
+        float y0 = v[oa].x * scale, y1 = v[oa].y * scale;
+        if (SCRUB) {
+          y0 = scrub(y0);
+          y1 = scrub(y1);
+        }
+        if (WIN) {
+          const float2 w = TM ? make_float2(w8[i].x, w8[i].y) : *reinterpret_cast<const float2*>(s_win + 2 * n);
+          y0 = __fmul_rn(y0, w.x);
+          y1 = __fmul_rn(y1, w.y);
+        }
+        stg_stream(reinterpret_cast<cpx*>(dst + 2 * n), mk(y0, y1));
       }
-      stg_stream(reinterpret_cast<cpx*>(dst + 2 * n), mk(y0, y1));
     }
+  }
+  if (TM) {
+    tmem_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<256>(s_tmem_base);
   }
 }
 
 static cudaError_t launch_k2_4096(const K2Params& p, cudaStream_t st) {
   const bool win = p.window != nullptr;
-  const int smem = (win ? 4096 * 4 : 0) + 2048 * 8 + kK2Warps4096 * kK2PerWarp4096;
+  static const bool tm = getenv("CRLOT_K2_NO_TMEM") == nullptr;   // A/B switch: tables in shared memory instead
+  const int smem = (tm ? 0 : (win ? 4096 * 4 : 0) + 2048 * 8) + kK2Warps4096 * kK2PerWarp4096;
   void (*kern)(const K2Params) = nullptr;
-  if (win) kern = p.scrub ? istft_inv_kernel_4096<true, true> : istft_inv_kernel_4096<true, false>;
-  else     kern = p.scrub ? istft_inv_kernel_4096<false, true> : istft_inv_kernel_4096<false, false>;
+  if (tm) {
+    if (win) kern = p.scrub ? istft_inv_kernel_4096<true, true, true> : istft_inv_kernel_4096<true, false, true>;
+    else     kern = p.scrub ? istft_inv_kernel_4096<false, true, true> : istft_inv_kernel_4096<false, false, true>;
+  } else {
+    if (win) kern = p.scrub ? istft_inv_kernel_4096<true, true, false> : istft_inv_kernel_4096<true, false, false>;
+    else     kern = p.scrub ? istft_inv_kernel_4096<false, true, false> : istft_inv_kernel_4096<false, false, false>;
+  }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   const long long want_blocks = (p.rows + kK2Warps4096 - 1) / kK2Warps4096;
