@@ -348,6 +348,29 @@ class Plan:
                                              C.c_longlong(out.stride(0) if ch > 1 else 0), _stream_ptr(self.device)))
         return out, spec
 
+    def roundtrip_fused_all_supported(self, t_offset=0, frame_t0=0):
+        return bool(lib().crlot_roundtrip_fused_supported(self._h, C.c_void_p(0), C.c_longlong(0), C.c_longlong(t_offset),
+                                                          C.c_longlong(frame_t0), C.c_void_p(0), C.c_longlong(0)))
+
+    def roundtrip_fused_all(self, signal, length=None, n_frames=None, t_offset=0, frame_t0=0, n_out=None, out=None):
+        """The whole round trip in one kernel (crlot_roundtrip_fused_execute): spectra never materialised."""
+        torch = _torch()
+        if signal.dim() == 1:
+            signal = signal.unsqueeze(0)
+        ch = signal.shape[0]
+        length = signal.shape[1] if length is None else length
+        F = self.n_frames(length) if n_frames is None else n_frames
+        if n_out is None:
+            n_out = (F - 1) * self.hop + self.nfft if F > 0 else 0
+        if out is None:
+            out = torch.empty((ch, n_out), dtype=torch.float32, device=signal.device)
+        _check(lib().crlot_roundtrip_fused_execute(self._h, C.c_void_p(signal.data_ptr()), C.c_longlong(signal.stride(0) if ch > 1 else 0),
+                                                   C.c_longlong(length), C.c_int(ch), C.c_longlong(F), C.c_longlong(t_offset),
+                                                   C.c_longlong(frame_t0), C.c_void_p(out.data_ptr()),
+                                                   C.c_longlong(out.stride(0) if ch > 1 else 0), C.c_longlong(n_out),
+                                                   _stream_ptr(self.device)))
+        return out
+
     def roundtrip(self, signal, spec=None, frames=None, out=None, length=None):
         """K1 -> K2 (synthesis window fused) -> K3 on device tensors; returns (out, spec, frames)."""
         torch = _torch()

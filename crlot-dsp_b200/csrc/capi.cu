@@ -615,11 +615,43 @@ int crlot_istft_ola_execute(crlot_plan_t plan, const void* d_spec, long long spe
   return CRLOT_OK;
 }
 
+// ---- fully fused round trip: K1 -> [spectral hook] -> K2+K3 in ONE kernel, spectra never materialised -----------
+int crlot_roundtrip_fused_supported(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long t_offset,
+                                    long long frame_t0, const float* d_out, long long out_chan_stride) {
+  if (!plan || !plan->k23_win_ok || plan->generic || !plan->den_rcp.p) return 0;
+  return roundtrip_fused_supported(plan->d.nfft, plan->d.hop, static_cast<long long>(plan->ring_len), t_offset, frame_t0,
+                                   out_chan_stride, d_out, plan->env.p, d_signal, chan_stride) ? 1 : 0;
+}
+
+int crlot_roundtrip_fused_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
+                                  long long n_frames, long long t_offset, long long frame_t0, float* d_out,
+                                  long long out_chan_stride, long long n_out, void* stream) {
+  if (!plan || !d_signal || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || n_frames < 0 || n_out < 0 || t_offset < 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (!crlot_roundtrip_fused_supported(plan, d_signal, chan_stride, t_offset, frame_t0, d_out, out_chan_stride))
+    return fail(CRLOT_ERR_UNSUPPORTED,
+                "the one-kernel round trip exists for nfft 2048 / hop 512 with even offsets and strides; "
+                "use crlot_roundtrip_execute with a spectra buffer");
+  DeviceGuard g(plan->d.device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  K23Params k{};
+  fill_k23(k, plan, st);
+  k.spec = nullptr; k.spec_chan_rows = n_frames; k.frames_per_chan = n_frames; k.channels = channels;
+  k.t_offset = t_offset; k.frame_t0 = frame_t0; k.out = d_out; k.out_chan_stride = out_chan_stride; k.n_out = n_out;
+  k.sig = d_signal; k.sig_chan_stride = chan_stride; k.sig_len = len; k.awindow = plan->win_a.p;
+  k.k1_scrub = plan->k1_scrub; k.tiny2 = plan->tiny2;
+  CU(launch_istft_ola(k, st));
+  return CRLOT_OK;
+}
+
 int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len, int channels,
                             void* d_spec, float* d_frames, float* d_out, long long out_chan_stride, void* stream) {
   if (!plan) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
   const long long F = crlot_frame_count(len, plan->d.nfft, plan->d.hop, plan->d.boundary_mode);
   if (F == 0) return CRLOT_OK;
+  if (!d_spec && !d_frames)   // neither spectra nor iFFT frames wanted: the whole round trip in one kernel
+    return crlot_roundtrip_fused_execute(plan, d_signal, chan_stride, len, channels, F, 0, 0, d_out, out_chan_stride,
+                                         (F - 1) * plan->d.hop + plan->d.nfft, stream);
   int rc = crlot_stft_execute(plan, d_signal, chan_stride, len, channels, F, d_spec, stream);
   if (rc) return rc;
   if (!d_frames)   // no materialisation of the iFFT frames requested: kernels 2+3 fused

@@ -21,6 +21,8 @@
 //   samples i >= N - hop  : first touch of their ring cells  -> plain store, no read
 //   samples in between    : read-modify-write in the ring
 // No atomics; every output sample sums its frames in ascending order: deterministic.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "warpfft.cuh"
@@ -53,24 +55,92 @@ __device__ __forceinline__ void prefetch_l2(const void* p) {
 // every sum starts from +0).  Frames that fail the screen, warm-up frames and ragged blocks take
 // the rolled path, which stages the raw iFFT output in the exchange buffer and applies the
 // reference formula sample by sample.
-template <int NFFT, int RDIV>
+// TMEM columns of a lane (TM): [0, 2B) inter-pass twiddles W_C^(a*ob) of its pass-1 items (a = lane % A),
+// [2B, 2B + 2A) the scaled synthesis-window samples of its pass-2 outputs (ob = lane % B, o = ob + B*oa).
+// FW (fully fused round trip, nfft 2048 / hop 512): additionally [kAWin, +2B) the analysis-window samples of the lane's
+// pass-1 points and, per warp of a lane quarter, 2B columns of RAW signal samples -- the lane's own points of the
+// current frame: with hop = nfft/4 = 8 register steps, sample a + A*b of frame k is sample a + A*(b-8) of frame k+1,
+// i.e. it stays in the same lane, so the three quarters of a frame that the next frame shares never leave the
+// lane's tensor memory and only the new hop is fetched from global memory (8 coalesced 8-byte loads per lane).
+template <int NFFT, bool FW = false> struct K23Tm {
+  using X = GeoX<NFFT>;
+  static constexpr int kTw = 0, kWin = 2 * X::B, kAWin = kWin + 2 * X::A, kRing = kAWin + 2 * X::B;
+  static constexpr int kUsed = FW ? kRing + 3 * 2 * X::B : kAWin;
+  static constexpr int kCols = kUsed <= 32 ? 32 : kUsed <= 64 ? 64 : kUsed <= 128 ? 128 : kUsed <= 256 ? 256 : 512;
+};
+
+// one complex sample pair sig[idx], sig[idx+1] with zeros at and beyond len (Framer's ZERO_PAD tail)
+__device__ __forceinline__ cpx ld_pair_guard(const float* sig, long long idx, long long len) {
+  if (idx + 1 < len) return ldg_stream(reinterpret_cast<const cpx*>(sig + idx));
+  return mk(idx < len ? __ldg(sig + idx) : 0.0f, 0.0f);
+}
+
+template <int NFFT, int RDIV, bool TM, bool FW = false>
 __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23Params p, const int acap) {
   using X = GeoX<NFFT>;
+  using T = K23Tm<NFFT, FW>;
+  static_assert(!FW || (TM && NFFT == 2048 && RDIV == 4), "the fully fused kernel exists for nfft 2048 / hop 512");
   constexpr int C = X::C, G = X::G, A = X::A, B = X::B;
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint32_t s_tmem_base;
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned char* wb = reinterpret_cast<unsigned char*>(s_tw1 + C) + warp * (acap * 4 + X::XCPX * 8);
+  unsigned char* wb = reinterpret_cast<unsigned char*>(s_tw1 + (TM ? 0 : C)) + warp * (acap * 4 + X::XCPX * 8);
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + acap);
   const int mask = acap - 1;
   const float scale = 2.0f / static_cast<float>(NFFT);             // inv_split hands over halved values
 
+  // the natural-order window table stays in shared memory for the rolled path (warm-up / ragged / screened frames)
   for (int i = threadIdx.x; i < NFFT; i += blockDim.x) s_win[i] = p.window[i] * scale;
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
+  if (!TM)
+    for (int i = threadIdx.x; i < C; i += blockDim.x) s_tw1[i] = p.tw1[i];
   const SplitLane<X::M1> SL = make_split_inv<X>(lane);   // lane factors of the real split (no table)
+  uint32_t tmb = 0;
+  if (TM) {
+    if (warp == 0) tmem_alloc<T::kCols>(&s_tmem_base);
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    tmb = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    if (warp < 4) {
+      const int a = lane % A, ob = lane % B;
+#pragma unroll
+      for (int c = 0; c < B / 8; ++c) {
+        cpx t8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t8[i] = p.tw1[(8 * c + i) * A + a];
+        tmem_st8(tmb + T::kTw + 16 * c, t8);
+      }
+#pragma unroll
+      for (int c = 0; c < A / 8; ++c) {
+        cpx w8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float2 w = *reinterpret_cast<const float2*>(p.window + 2 * (ob + B * (8 * c + i)));
+          w8[i] = mk(w.x * scale, w.y * scale);
+        }
+        tmem_st8(tmb + T::kWin + 16 * c, w8);
+      }
+      if (FW) {
+#pragma unroll
+        for (int c = 0; c < B / 8; ++c) {
+          cpx w8[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) w8[i] = *reinterpret_cast<const cpx*>(p.awindow + 2 * a + 2 * A * (8 * c + i));
+          tmem_st8(tmb + T::kAWin + 16 * c, w8);
+        }
+      }
+      tmem_wait_st();
+    }
+    tmem_fence_before_sync();
+  }
   __syncthreads();
+  if (TM) tmem_fence_after_sync();
+  const uint32_t tring = tmb + T::kRing + 2 * B * (warp >> 2);     // FW: this warp's raw-sample columns
+  const SplitLane<X::M2> SLF = make_split_fwd<X>(lane);            // FW: lane factors of the forward split
+  const int lpf = mirror_lane<B>(lane);
 
   const int H = RDIV > 0 ? NFFT / (RDIV > 0 ? RDIV : 1) : p.hop;
   const int R = (NFFT + H - 1) / H;
@@ -97,6 +167,8 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
     const long long m0 = p.m_begin + (q % chunks_per_chan) * p.chunk_blocks;
     const long long m1 = min(m0 + p.chunk_blocks, p.m_end);
     const cpx* spec = p.spec + c * p.spec_chan_rows * (C + 1);
+    const float* sig = FW ? p.sig + c * p.sig_chan_stride : nullptr;
+    int dirty = 0;                                        // FW: frames still to be cleaned up sample by sample
     float* out = p.out + c * p.out_chan_stride;
     const float* sgain = p.sgain ? p.sgain + c * p.spec_chan_rows * p.sgain_row_stride : nullptr;
     const long long k0 = max(0ll, m0 - R + 1);
@@ -145,6 +217,90 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
       const long long left = k1 - kbase;
       cpx v[32];
       cpx nyq[X::M1];
+      if constexpr (FW) {
+        // ---- forward half: frame kbase from the signal, kernel 1's arithmetic (k1_stft.cu) ------------------
+        const int s = static_cast<int>(kbase - k0);
+        const long long f0 = kbase * H;                     // first sample of the frame
+        const bool whole = f0 + NFFT <= p.sig_len;
+        unsigned int wmin = 0xffffffffu;
+        cpx nf = mk(0.f, 0.f);
+        if (kbase + 1 < k1 && lane < 16 && f0 + NFFT + H <= p.sig_len)   // the hop the NEXT frame brings in: into L2 now
+          prefetch_l2(sig + f0 + NFFT + 32 * lane);
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          cpx x8[8], w8[8];
+          tmem_ld8(tmb + T::kAWin + 16 * ch, w8);
+          const bool fresh = s == 0 || ch == 3;             // from global memory; else carried over in tensor memory
+          if (fresh) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const long long idx = f0 + 2 * lane + 2 * A * (8 * ch + i);
+              x8[i] = whole ? ldg_stream(reinterpret_cast<const cpx*>(sig + idx)) : ld_pair_guard(sig, idx, p.sig_len);
+            }
+            // frame chunk ch sits in ring chunk (ch + s) mod 4: the chunk the oldest hop has just left
+            if (ch > 0) tmem_st8(tring + 16 * ((ch + s) & 3), x8);
+            if (p.k1_scrub == 2) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const unsigned int u0 = __float_as_uint(x8[i].x), u1 = __float_as_uint(x8[i].y);
+                wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));
+                nf = fma2(x8[i], mk(0.f, 0.f), nf);
+              }
+            }
+            tmem_wait_ld8(w8);
+          } else {
+            tmem_ld8(tring + 16 * ((ch + s) & 3), x8);
+            tmem_wait_ld8(w8);
+            tmem_wait_ld8(x8);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            cpx pw = mul2(x8[i], w8[i]);                    // one rounding per sample, as frame[i]*window[i]
+            if (p.k1_scrub == 1) pw = mk(scrub(pw.x), scrub(pw.y));
+            v[8 * ch + i] = pw;
+          }
+        }
+        tmem_wait_st();                                     // the new hop is in place before a later step reads it back
+        if (p.k1_scrub == 2) {
+          const bool suspect = (wmin < p.tiny2) || (nf.x != 0.0f) || (nf.y != 0.0f);
+          if (__any_sync(0xffffffffu, suspect)) dirty = 5;
+          if (dirty > 0 || s == 0) {                        // s == 0: every sample of the frame is new
+#pragma unroll
+            for (int r = 0; r < 32; ++r) v[r] = mk(scrub(v[r].x), scrub(v[r].y));
+            if (dirty > 0) --dirty;
+          }
+        }
+        pass1<X, false>(v);
+#pragma unroll
+        for (int cc = 0; cc < B / 8; ++cc) {
+          cpx t8[8];
+          tmem_ld8(tmb + T::kTw + 16 * cc, t8);
+          tmem_wait_ld8(t8);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (8 * cc + i > 0) v[8 * cc + i] = cmul(v[8 * cc + i], t8[i]);
+        }
+        xchg_write<X>(v, lane, ex);
+        __syncwarp();
+        xchg_read<X>(v, lane, ex);
+        __syncwarp();
+        pass2<X, false>(v);
+        {
+          cpx nyqf[X::M2], midf[X::M2];
+          auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lpf), __shfl_sync(0xffffffffu, v[r].y, lpf)); };
+          fwd_split_pairs<X>(v, lane, SLF, mirror, nyqf, midf);
+          fwd_split_finish<X>(v, lane, mirror, midf);
+          nyq[0] = lane == 0 ? nyqf[0] : mk(0.f, 0.f);
+        }
+        // The spectrum row is now in registers, register oa of lane ob = bin ob + 32*oa: exactly the layout the
+        // inverse half wants (register b of lane a = bin a + 32*b).  The spectral hook, as kernel 2 applies it on load:
+        if (sgain != nullptr) {
+          const float* gr = sgain + kbase * p.sgain_row_stride;
+#pragma unroll
+          for (int b = 0; b < B; ++b) v[b] = mul2(v[b], splat(__ldg(gr + lane + A * b)));
+          if (lane == 0) nyq[0] = mul2(nyq[0], splat(__ldg(gr + C)));
+        }
+      } else {
       load_rows(v, nyq, kbase);
       // pull the next step's rows into L2 while this one is transformed (12 warps per SM cannot
       // cover a DRAM round trip by themselves)
@@ -155,6 +311,7 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
         for (int o = 0; o < (kBytes + 4095) / 4096; ++o)
           if (o * 4096 + lane * 128 < kBytes) prefetch_l2(nxt + o * 4096 + lane * 128);
       }
+      }
       {
         cpx mid[X::M1];
         auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp)); };
@@ -162,7 +319,21 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
         inv_split_finish<X>(v, lane, mirror, mid);
       }
       pass1<X, true>(v);
-      twiddle1<X, true>(v, lane, s_tw1);
+      if (TM) {
+#pragma unroll
+        for (int c = 0; c < B / 8; ++c) {
+          cpx t8[8];
+          tmem_ld8(tmb + T::kTw + 16 * c, t8);
+          tmem_wait_ld8(t8);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (8 * c + i > 0)
+#pragma unroll
+              for (int j = 0; j < X::M1; ++j) v[j * B + 8 * c + i] = cmulc(v[j * B + 8 * c + i], t8[i]);
+        }
+      } else {
+        twiddle1<X, true>(v, lane, s_tw1);
+      }
       xchg_write<X>(v, lane, ex);
       __syncwarp();
       xchg_read<X>(v, lane, ex);
@@ -204,12 +375,25 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
           }
         }
         // f = fl(v * ws), every frame of the step at once
+        if (TM) {
 #pragma unroll
-        for (int j = 0; j < X::M2; ++j) {
-          const int ob = (lane + 32 * j) % B;
+          for (int c = 0; c < A / 8; ++c) {
+            cpx w8[8];
+            tmem_ld8(tmb + T::kWin + 16 * c, w8);
+            tmem_wait_ld8(w8);
 #pragma unroll
-          for (int oa = 0; oa < A; ++oa)
-            v[j * A + oa] = mul2(v[j * A + oa], *reinterpret_cast<const cpx*>(s_win + 2 * (ob + B * oa)));
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+              for (int j = 0; j < X::M2; ++j) v[j * A + 8 * c + i] = mul2(v[j * A + 8 * c + i], w8[i]);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < X::M2; ++j) {
+            const int ob = (lane + 32 * j) % B;
+#pragma unroll
+            for (int oa = 0; oa < A; ++oa)
+              v[j * A + oa] = mul2(v[j * A + oa], *reinterpret_cast<const cpx*>(s_win + 2 * (ob + B * oa)));
+          }
         }
         // overlap-add, one frame at a time so that every ring cell sees its frames in ascending order
 #pragma unroll
@@ -325,6 +509,11 @@ __global__ void __launch_bounds__(kK23Warps * 32, 1) istft_ola_kernel(const K23P
       }
     }
   }
+  if (TM) {
+    tmem_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<T::kCols>(s_tmem_base);
+  }
 }
 
 template <int NFFT>
@@ -332,11 +521,13 @@ cudaError_t launch_k23(const K23Params& p, cudaStream_t st) {
   using X = GeoX<NFFT>;
   const int S = (X::G - 1) * p.hop + NFFT;
   const int acap = k23_next_pow2(S);
-  const int smem = NFFT * 4 + X::C * 8 + kK23Warps * (acap * 4 + X::XCPX * 8);
+  static const bool tm_env = getenv("CRLOT_K23_NO_TMEM") == nullptr;   // A/B switch: twiddle / window tables in shared memory
+  const bool tm = tm_env || p.sig != nullptr;
+  const int smem = NFFT * 4 + (tm ? 0 : X::C * 8) + kK23Warps * (acap * 4 + X::XCPX * 8);
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
   const int rdiv = (NFFT % p.hop == 0) ? NFFT / p.hop : 0;
   void (*kern)(const K23Params, const int) = nullptr;
-#define CRLOT_K23_PICK(RD) kern = istft_ola_kernel<NFFT, RD>
+#define CRLOT_K23_PICK(RD) kern = tm ? istft_ola_kernel<NFFT, RD, true> : istft_ola_kernel<NFFT, RD, false>
   switch (rdiv) {
     case 1: CRLOT_K23_PICK(1); break;
     case 2: CRLOT_K23_PICK(2); break;
@@ -345,6 +536,14 @@ cudaError_t launch_k23(const K23Params& p, cudaStream_t st) {
     default: CRLOT_K23_PICK(0); break;
   }
 #undef CRLOT_K23_PICK
+  if (p.sig != nullptr) {                        // fully fused round trip
+    if constexpr (NFFT == 2048) {
+      if (rdiv != 4) return cudaErrorNotSupported;
+      kern = istft_ola_kernel<2048, 4, true, true>;
+    } else {
+      return cudaErrorNotSupported;
+    }
+  }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
@@ -373,6 +572,14 @@ bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offs
   if ((t_offset & 1) || (frame_t0 & 1) || (out_chan_stride & 1)) return false;
   if (reinterpret_cast<uintptr_t>(out) % 8 != 0 || reinterpret_cast<uintptr_t>(norm) % 8 != 0) return false;
   return true;
+}
+
+bool roundtrip_fused_supported(int nfft, int hop, long long ring_len, long long t_offset, long long frame_t0,
+                               long long out_chan_stride, const void* out, const void* norm, const void* sig,
+                               long long sig_chan_stride) {
+  if (nfft != 2048 || hop != 512) return false;
+  if (reinterpret_cast<uintptr_t>(sig) % 8 != 0 || (sig_chan_stride & 1)) return false;
+  return istft_ola_supported(nfft, hop, ring_len, t_offset, frame_t0, out_chan_stride, out, norm);
 }
 
 cudaError_t launch_istft_ola(K23Params p, cudaStream_t st) {

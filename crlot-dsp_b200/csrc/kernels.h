@@ -118,7 +118,20 @@ struct K23Params {
   const float* sgain;           // spectral-domain hook, as in K2Params; rows indexed like `spec`
   long long sgain_row_stride;
   long long m_begin, m_end;     // filled by the launcher: hop blocks [m_begin, m_end) cover [0, n_out)
+  // fully fused round trip (sig != nullptr): the spectrum rows are not read from `spec` but computed in the same
+  // warp from the signal -- frame k of channel c = sig[c*sig_chan_stride + k*hop + (0..nfft)), zero beyond sig_len,
+  // times awindow, forward real FFT with kernel 1's arithmetic -- and never leave the registers.
+  const float* sig;
+  long long sig_chan_stride, sig_len;
+  const float* awindow;         // device analysis window (all ones = none)
+  int k1_scrub;                 // kernel 1's clean-up mode (0 none, 1 every sample, 2 screening)
+  unsigned int tiny2;           // screening threshold of kernel 1
 };
+// nfft = 2048 with hop = 512 (the layout of the forward output registers equals the layout the inverse wants, and
+// the raw-sample carry-over in tensor memory wants nfft == 4*hop), otherwise the conditions of istft_ola_supported
+bool roundtrip_fused_supported(int nfft, int hop, long long ring_len, long long t_offset, long long frame_t0,
+                               long long out_chan_stride, const void* out, const void* norm, const void* sig,
+                               long long sig_chan_stride);
 bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offset, long long frame_t0,
                          long long out_chan_stride, const void* out, const void* norm);
 cudaError_t launch_istft_ola(K23Params p, cudaStream_t st);

@@ -178,8 +178,8 @@ int crlot_ola_accumulate(crlot_plan_t plan, const float* d_frames, long long fra
  * as crlot_ola_accumulate, bit-identical to calling the two in sequence with the synthesis window
  * fused -- but the iFFT frames stay in shared memory: per frame 8*bins bytes are read and 4*hop
  * written, instead of 8*bins + 4*nfft + 4*nfft + 4*hop.  Returns CRLOT_ERR_UNSUPPORTED outside its
- * shapes (crlot_istft_ola_supported() == 0): nfft <= 2048, hop a multiple of 64 (16 for nfft 256,
- * 32 for 512/1024), even t_offset / frame_t0 / out_chan_stride, 8-byte aligned d_out.
+ * shapes (crlot_istft_ola_supported() == 0): nfft in {256, 512, 1024, 2048, 4096}, hop a multiple of 64 (16 for
+ * nfft 256, 32 for 512/1024), even t_offset / frame_t0 / out_chan_stride, 8-byte aligned d_out.
  * replaces: IFftPlan::inverse + OLAAccumulator::push_frame_AoS + produce
  *   ref: kissfft_adapter.cc:124-168; OLAAccumulator.cc:54-122,162-221; dsp/ola/kernels.cc:18-36 */
 int crlot_istft_ola_supported(crlot_plan_t plan, long long t_offset, long long frame_t0, const float* d_out,
@@ -195,7 +195,7 @@ int crlot_selftest_division(crlot_plan_t plan, unsigned long long n, unsigned lo
                             unsigned long long* mismatches);
 
 /* The composed round trip on device buffers (K1 -> K2 -> K3 on `stream`, or K1 -> fused K2+K3 when
- * d_frames is NULL).  d_spec and d_frames
+ * d_frames is NULL, or the one-kernel round trip below when d_spec is NULL as well).  d_spec and d_frames
  * are caller-provided materialisation buffers ([channels][n_frames][bins] complex and
  * [channels][n_frames][nfft] fp32).  n_frames = crlot_frame_count(len,...); output length per
  * channel = (n_frames-1)*hop + nfft.
@@ -204,6 +204,23 @@ int crlot_selftest_division(crlot_plan_t plan, unsigned long long n, unsigned lo
 int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
                             int channels, void* d_spec, float* d_frames, float* d_out, long long out_chan_stride,
                             void* stream);
+
+/* The whole round trip in ONE kernel, for callers that need neither the spectra nor the iFFT frames (the reference's
+ * loop does nothing between forward and inverse but the optional per-bin processing,
+ *   ref: bench/e2e_benchmark.cc:158-166): each warp frames, windows and transforms a frame, applies the plan's
+ * spectral gain (crlot_stft_plan_set_spectral_gain) in registers, inverse-transforms, overlap-adds and normalises --
+ * 8 bytes of HBM traffic per sample instead of 72.  Same roundings in the same order as the three-kernel path:
+ * bit-identical output.  Frame k = d_signal[c*chan_stride + k*hop + (0..nfft)), zero at and beyond len;
+ * t_offset / frame_t0 / n_out as in crlot_ola_accumulate (time shards).  Exists for nfft 2048 / hop 512 (where the
+ * forward transform's register layout is the inverse's and the overlapping three quarters of a frame stay in the
+ * lane's tensor memory); crlot_roundtrip_fused_supported() == 0 otherwise and the call returns
+ * CRLOT_ERR_UNSUPPORTED.  crlot_roundtrip_execute(d_spec = NULL, d_frames = NULL) forwards here.
+ * replaces: Framer::pop + window + IFftPlan::forward + IFftPlan::inverse + OLAAccumulator::push_frame_AoS + produce */
+int crlot_roundtrip_fused_supported(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long t_offset,
+                                    long long frame_t0, const float* d_out, long long out_chan_stride);
+int crlot_roundtrip_fused_execute(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
+                                  int channels, long long n_frames, long long t_offset, long long frame_t0, float* d_out,
+                                  long long out_chan_stride, long long n_out, void* stream);
 
 /* Same round trip with HOST buffers: host->device and device->host copies are inside the call,
  * processed in time slabs through an internal double-buffered workspace so transfers overlap
