@@ -1,13 +1,15 @@
-# Round-1 evidence run (one B200): bench lines, ncu launch list of the bench command, one
-# `ncu --set full` capture per hot kernel at the c2 launch size.  Outputs under gpurun_out/.
+# Round-2 evidence run (one B200): bench lines, the ncu launch list of the bench command, one `ncu --set full`
+# capture per hot kernel at the c2 / c4 launch sizes (exported to raw CSV on the box; the .ncu-rep files stay there).
+# Outputs under gpurun_out/.   usage: bash tools/run_prof.sh [tag]
 set -x
-T=${1:-r1c}
+T=${1:-r2}
 python bench.py --steps 10 --warmup 3 > gpurun_out/${T}_bench_c2_n1.json 2> gpurun_out/${T}_bench_c2_n1.err
-python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/${T}_plain_c2.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_ncu_launches_c2.csv python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/${T}_ncu_launch.log 2>&1
-python tools/time_fused.py 2048 512 30 > gpurun_out/${T}_plain_full.log 2>&1 && for k in stft_fwd istft_inv ola_gather istft_ola; do ncu --set full --clock-control none --import-source on -k regex:$k -s 2 -c 1 -o gpurun_out/${T}_full_$k python tools/time_fused.py 2048 512 30 > gpurun_out/${T}_ncu_$k.log 2>&1; done
-cat gpurun_out/${T}_plain_full.log
-python bench.py --steps 5 --warmup 3 --workload c3 --no-cpu > gpurun_out/${T}_bench_c3_n1.json 2> gpurun_out/${T}_bench_c3_n1.err
-python bench.py --steps 5 --warmup 3 --workload c4 --no-cpu > gpurun_out/${T}_bench_c4_n1.json 2> gpurun_out/${T}_bench_c4_n1.err
-python bench.py --steps 5 --warmup 3 --workload c5 --no-cpu > gpurun_out/${T}_bench_c5_n1.json 2> gpurun_out/${T}_bench_c5_n1.err
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_reference.json 2> gpurun_out/${T}_bench_reference.err
-tail -c 1200 gpurun_out/${T}_bench_c2_n1.json
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_reference_n1.json 2> gpurun_out/${T}_bench_reference_n1.err
+python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-legs > gpurun_out/${T}_plain_c2.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_ncu_launches_c2.csv python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu --no-legs > gpurun_out/${T}_ncu_launch.log 2>&1
+for cfg in "2048 512" "4096 1024"; do
+  set -- $cfg
+  python tools/time_fused.py $1 $2 30 > gpurun_out/${T}_plain_full_$1.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:'stft_fwd|istft_inv|ola_gather|istft_ola' -s 8 -c 26 -f -o /tmp/${T}_full_$1 python tools/time_fused.py $1 $2 30 > gpurun_out/${T}_ncu_$1.log 2>&1
+  ncu -i /tmp/${T}_full_$1.ncu-rep --page raw --csv > gpurun_out/${T}_ncu_full_$1.raw.csv
+  cat gpurun_out/${T}_plain_full_$1.log
+done
+tail -c 600 gpurun_out/${T}_bench_c2_n1.json

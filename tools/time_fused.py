@@ -38,9 +38,14 @@ try:
     same = torch.equal(out.view(torch.int32), out2.view(torch.int32))
 except dsp.CrlotUnsupported:
     t23, same = float("nan"), None
+tall = float("nan")
+if plan.roundtrip_fused_all_supported():
+    out3 = torch.empty_like(out)
+    tall = timeit(lambda: plan.roundtrip_fused_all(x, out=out3))
+    same = same and torch.equal(out.view(torch.int32), out3.view(torch.int32))
 bins = N // 2 + 1
 gb1 = ch * F * (4 * H + 8 * bins) / 1e9
 gb23 = ch * F * (8 * bins + 4 * H) / 1e9
 print(f"N={N} H={H} L=2^{logL} ch={ch} F={F}: K1 {t1:.3f} ms ({gb1/t1*1e3:.0f} GB/s)  K2 {t2:.3f}  K3 {t3:.3f}  "
       f"K2+K3 {t2+t3:.3f}  fused {t23:.3f} ms ({gb23/t23*1e3:.0f} GB/s alg)  bit-identical {same}")
-print(f"round trip: 3-kernel {(1<<logL)*ch/(t1+t2+t3)/1e6:.1f} Gs/s   fused {(1<<logL)*ch/(t1+t23)/1e6:.1f} Gs/s")
+print(f"round trip: 3-kernel {(1<<logL)*ch/(t1+t2+t3)/1e6:.1f} Gs/s   fused {(1<<logL)*ch/(t1+t23)/1e6:.1f} Gs/s   one kernel {tall:.3f} ms = {(1<<logL)*ch/tall/1e6:.1f} Gs/s")
