@@ -663,7 +663,7 @@ int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long 
   return crlot_ola_accumulate(plan, d_frames, F, F, channels, 1, 0, 0, d_out, out_chan_stride, n_out, stream);
 }
 
-// Host-buffer round trip: time slabs through two workspace slots, one stream each, so the
+// Host-buffer round trip: time slabs through three workspace slots, one stream each, so the
 // H2D copy of slab i+1 and the D2H copy of slab i-1 overlap the kernels of slab i.
 // aos: h_in / h_out are interleaved [n][channels] (what Framer::push and WavReader hand over,
 // ref: dsp/frame/framer.cc:133-141, io/wav.cc:90-123); every slab carries all channels, is

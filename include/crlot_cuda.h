@@ -103,6 +103,13 @@ typedef struct crlot_plan_info {
   int device;
 } crlot_plan_info;
 
+/* Stream and thread rules.  Every execute entry point enqueues on the `stream` it is given and returns without
+ * synchronising (host-buffer entry points synchronise before returning).  One plan may be used from several
+ * streams / host threads at once: the dynamically scheduled kernels (K1, fused K2+K3, the one-kernel round trip)
+ * take their work counter per stream (up to 1024 streams per plan are tracked; launches on ONE stream are ordered
+ * and share a counter).  crlot_stft_plan_set_spectral_gain is plan state: change it only while no launch of that
+ * plan is being enqueued.  The stateful objects (crlot_framer_t, crlot_ola_t, crlot_stream_t, crlot_fft_t) are, like
+ * the reference's classes, for one host thread at a time; the Framer orders its own operations across streams. */
 int crlot_stft_plan_create(const crlot_stft_desc* desc, crlot_plan_t* out);
 int crlot_stft_plan_destroy(crlot_plan_t plan);
 int crlot_stft_plan_info(crlot_plan_t plan, crlot_plan_info* info);
@@ -223,7 +230,7 @@ int crlot_roundtrip_fused_execute(crlot_plan_t plan, const float* d_signal, long
                                   long long out_chan_stride, long long n_out, void* stream);
 
 /* Same round trip with HOST buffers: host->device and device->host copies are inside the call,
- * processed in time slabs through an internal double-buffered workspace so transfers overlap
+ * processed in time slabs through three internal workspace slots (one stream each) so transfers overlap
  * compute.  h_out receives (n_frames-1)*hop + nfft samples per channel; *n_out_per_chan is set.
  * h_in / h_out should be page-locked (crlot_host_alloc) for full PCIe rate. */
 int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_stride, long long len, int channels,
