@@ -549,7 +549,11 @@ cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st) {
     case 512: return launch_k1<512>(p, st);
     case 1024: return launch_k1<1024>(p, st);
     case 2048: return launch_k1<2048>(p, st);
-    case 4096: return launch_k1_4096(p, st);
+    case 4096: {
+      // CRLOT_K1_4096_V1=1: the first version (one 64-register transform per frame, 8 warps) for A/B timing
+      static const bool v1 = getenv("CRLOT_K1_4096_V1") != nullptr;
+      return v1 ? launch_k1_4096(p, st) : launch_stft_fwd_4096v2(p, st);
+    }
     default: return cudaErrorNotSupported;
   }
 }

@@ -43,6 +43,26 @@ inline FftTables make_fft_tables(int nfft) {
     t.sa[2 * k + 1] = (float)(0.5 * std::sin(ph));
   }
   if (nfft == 4096) {
+    // Tables of the two-sub-transform kernels (k1_4096v2.cu): a 4096-point frame = 2048 complex points = two
+    // 1024-point complex transforms (even / odd) + a radix-2 combine + the real split.  `sa` is not read by the
+    // register kernels of this size, so it carries them: [0,1024) tw[ob*32+a] = exp(-2 pi i a*ob/1024) (inter-pass
+    // twiddles of a 1024-point transform), [1024,2048) tc[oa*32+l] = exp(-2 pi i k/2048), k = l + 32*oa (combine),
+    // [2048,3072) qs[p*32+l] = (-i/2) exp(-i pi k/2048), k = l + 32*p (forward real split of the 2048-point result).
+    t.sa.assign(2 * 3072, 0.0f);
+    for (int ob = 0; ob < 32; ++ob)
+      for (int a = 0; a < 32; ++a) {
+        const double ph = -2.0 * pi * (double)a * (double)ob / 1024.0;
+        t.sa[2 * (ob * 32 + a)] = (float)std::cos(ph);
+        t.sa[2 * (ob * 32 + a) + 1] = (float)std::sin(ph);
+      }
+    for (int k = 0; k < 1024; ++k) {       // k = l + 32*oa is stored at index oa*32 + l = k's own digits swapped... both are k
+      const int l = k % 32, oa = k / 32;
+      const double pc = -2.0 * pi * (double)k / 2048.0, ps = pi * (double)k / 2048.0;
+      t.sa[2 * (1024 + oa * 32 + l)] = (float)std::cos(pc);
+      t.sa[2 * (1024 + oa * 32 + l) + 1] = (float)std::sin(pc);
+      t.sa[2 * (2048 + oa * 32 + l)] = (float)(-0.5 * std::sin(ps));
+      t.sa[2 * (2048 + oa * 32 + l) + 1] = (float)(-0.5 * std::cos(ps));
+    }
     t.pre.resize(2 * 2048);
     for (int ob = 0; ob < 32; ++ob)
       for (int a = 0; a < 64; ++a) {
