@@ -391,6 +391,16 @@ class Plan:
                                              C.c_longlong(out.stride(0) if ch > 1 else 0), _stream_ptr(self.device)))
         return out, spec, frames
 
+    def roundtrip_static(self, signal, out, length=None):
+        """crlot_roundtrip_execute_static: the round trip with every intermediate in the library's static device
+        scratch; nothing is allocated here or in the call -- the caller passes signal and output."""
+        ch = 1 if signal.dim() == 1 else signal.shape[0]
+        length = signal.shape[-1] if length is None else length
+        _check(lib().crlot_roundtrip_execute_static(
+            self._h, C.c_void_p(signal.data_ptr()), C.c_longlong(signal.stride(0) if ch > 1 else 0), C.c_longlong(length),
+            C.c_int(ch), C.c_void_p(out.data_ptr()), C.c_longlong(out.stride(0) if ch > 1 else 0), _stream_ptr(self.device)))
+        return out
+
     # -- host buffers (H2D / D2H inside the call) ----------------------------------------------
     def roundtrip_host(self, x, out=None):
         """x: numpy float32 [channels, L] or [L] (ideally page-locked) -> numpy [channels, n_out]."""

@@ -1652,3 +1652,99 @@ long long crlot_stream_get(crlot_stream_t s, int what) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// round trip on STATIC scratch: no allocation inside the call (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc -- code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The work counter of the dynamically scheduled kernels, the spectra and (when the
+// fused kernel 2+3 does not cover the plan) the iFFT frames live in one file-scope device array that every GPU which
+// loads the library holds until exit.  All calls share it: calls that overlap on the GPU race.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[CRLOT_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxStaticDevices = 64;
+constexpr size_t kStaticHeader = 256;       // [0, 256): work-counter words; the sections after it are 256-byte aligned
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[kMaxStaticDevices] = {};
+
+// The device address of g_static_scratch on the CURRENT device, resolved once per device.  In host code the array's
+// name is a host-side stand-in, never a device address: only cudaGetSymbolAddress yields what a kernel may be given.
+int static_scratch_for(int device, unsigned char** out) {
+  if (device < 0 || device >= kMaxStaticDevices) return fail(CRLOT_ERR_UNSUPPORTED, "device ordinal beyond the static-scratch table");
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaGetSymbolAddress(static scratch)");
+    if (!p) return fail(CRLOT_ERR_CUDA, "cudaGetSymbolAddress returned a null device address");
+    g_static_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_ptr[device];
+  return CRLOT_OK;
+}
+size_t round256(size_t b) { return (b + 255) & ~static_cast<size_t>(255); }
+}  // namespace
+
+extern "C" int crlot_roundtrip_execute_static(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
+                                              int channels, float* d_out, long long out_chan_stride, void* stream) {
+  if (!plan || !d_signal || !d_out) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (!plan->generic && (chan_stride % 4 != 0 || reinterpret_cast<uintptr_t>(d_signal) % 16 != 0))
+    return fail(CRLOT_ERR_UNSUPPORTED, "signal must be 16-byte aligned with chan_stride a multiple of 4 floats");
+  const int N = plan->d.nfft, H = plan->d.hop;
+  const long long F = crlot_frame_count(len, N, H, plan->d.boundary_mode);
+  if (F == 0) return CRLOT_OK;
+  const long long n_out = (F - 1) * H + N;
+  const bool fused = crlot_istft_ola_supported(plan, 0, 0, d_out, out_chan_stride) != 0;
+  const size_t rows = static_cast<size_t>(F) * static_cast<size_t>(channels);
+  const size_t spec_bytes = round256(rows * static_cast<size_t>(plan->bins) * sizeof(cpx));
+  const size_t frame_bytes = fused ? 0 : round256(rows * static_cast<size_t>(N) * sizeof(float));
+  const size_t need = kStaticHeader + spec_bytes + frame_bytes;
+  if (need > static_cast<size_t>(CRLOT_STATIC_SCRATCH_BYTES))
+    return fail(CRLOT_ERR_INVALID_ARGUMENT,
+                "crlot_roundtrip_execute_static: " + std::to_string(rows) + " frames need " + std::to_string(need) +
+                    " bytes of scratch, the static scratch holds CRLOT_STATIC_SCRATCH_BYTES = " +
+                    std::to_string(static_cast<size_t>(CRLOT_STATIC_SCRATCH_BYTES)) +
+                    "; split the signal or use crlot_roundtrip_execute with caller-provided buffers");
+  DeviceGuard g(plan->d.device);
+  if (!g.ok) return fail(CRLOT_ERR_CUDA, "cannot select device");
+  unsigned char* base = nullptr;
+  if (int rc = static_scratch_for(plan->d.device, &base)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(base);   // zeroed on `st` by each launcher before its kernel
+  cpx* spec = reinterpret_cast<cpx*>(base + kStaticHeader);
+  float* frames = reinterpret_cast<float*>(base + kStaticHeader + spec_bytes);
+
+  K1Params k1{};
+  k1.sig = d_signal; k1.chan_stride = chan_stride; k1.len = len; k1.channels = channels; k1.frames = F;
+  k1.nfft = N; k1.hop = H; k1.spec = spec; k1.spec_chan_rows = F;
+  k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p; k1.pre = plan->pre.p;
+  k1.counter = counter; k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2; k1.generic = plan->generic;
+  CU(launch_stft_fwd(k1, st));
+  if (fused) {
+    K23Params k{};
+    k.nfft = N; k.hop = H; k.window = plan->syn_active ? plan->win_s.p : plan->win_ones.p;
+    k.tw1 = plan->tw1.p; k.sa = plan->sa.p; k.pre = plan->pre.p; k.scrub = plan->d.scrub;
+    k.gain = plan->d.gain; k.eps = plan->d.eps; k.norm = plan->env.p; k.ring_len = static_cast<long long>(plan->ring_len);
+    k.den_rcp = plan->den_rcp.p; k.counter = counter; k.chunk_blocks = 0;
+    k.sgain = plan->sgain; k.sgain_row_stride = plan->sgain_row_stride;
+    k.spec = spec; k.spec_chan_rows = F; k.frames_per_chan = F; k.channels = channels;
+    k.t_offset = 0; k.frame_t0 = 0; k.out = d_out; k.out_chan_stride = out_chan_stride; k.n_out = n_out;
+    CU(launch_istft_ola(k, st));
+    return CRLOT_OK;
+  }
+  K2Params k2{};
+  k2.spec = spec; k2.rows = static_cast<long long>(rows); k2.nfft = N; k2.frames = frames;
+  k2.window = plan->syn_active ? plan->win_s.p : nullptr;
+  k2.tw1 = plan->tw1.p; k2.sa = plan->sa.p; k2.pre = plan->pre.p; k2.scrub = plan->d.scrub;
+  k2.sgain = plan->sgain; k2.sgain_row_stride = plan->sgain_row_stride; k2.generic = plan->generic;
+  CU(launch_istft_inv(k2, st));
+  K3Params k3{};
+  k3.frames = frames; k3.frames_chan_rows = F; k3.frames_per_chan = F; k3.channels = channels; k3.nfft = N; k3.hop = H;
+  k3.window = nullptr; k3.gain = plan->d.gain; k3.eps = plan->d.eps; k3.norm = plan->env.p;
+  k3.ring_len = static_cast<long long>(plan->ring_len); k3.t_offset = 0; k3.frame_t0 = 0;
+  k3.out = d_out; k3.out_chan_stride = out_chan_stride; k3.n_out = n_out;
+  CU(launch_ola_gather(k3, st));
+  return CRLOT_OK;
+}

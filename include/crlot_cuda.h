@@ -476,6 +476,25 @@ int crlot_halo_exchange(crlot_shard_group_t g, const crlot_time_shard* shard, fl
 int crlot_sharded_roundtrip_execute(crlot_plan_t plan, crlot_shard_group_t group, const crlot_time_shard* shard,
                                     float* d_xbuf, void* d_spec, float* d_frames, float* d_out, void* stream);
 
+/* ---- round trip on static scratch: a call that allocates nothing --------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * crlot_roundtrip_execute (d_frames = NULL semantics: K1 -> fused K2+K3, or K1 -> K2 -> K3 where the fused kernel
+ * does not cover the plan) with every intermediate -- the kernels' work counter, the spectra and, on the unfused
+ * route, the iFFT frames -- in ONE file-scope `static __device__` array of CRLOT_STATIC_SCRATCH_BYTES inside the
+ * library (each GPU that loads the library holds it until exit).  The caller passes only the signal and the output;
+ * the call itself performs no cudaMalloc / cudaFree / allocating library routine, and produces the same bits as
+ * crlot_roundtrip_execute.  Limit: 256 + round256(F*channels*bins*8) [+ round256(F*channels*nfft*4) unfused]
+ * bytes must fit, F = crlot_frame_count(len, ...) -- e.g. 4091 frames x channels at nfft 2048; beyond that the call
+ * fails with CRLOT_ERR_INVALID_ARGUMENT and a message that states both figures.  Every call shares the array, which
+ * keeps the previous call's contents (the work counter is cleared on `stream` before each kernel; everything else is
+ * written before it is read): calls that may OVERLAP on the GPU -- different streams, different plans, different
+ * host threads -- race and must be ordered by the caller.  The first call on a device resolves the array's device
+ * address (cudaGetSymbolAddress); make that call before a graph capture begins. */
+#define CRLOT_STATIC_SCRATCH_BYTES (32u << 20)
+int crlot_roundtrip_execute_static(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
+                                   int channels, float* d_out, long long out_chan_stride, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
