@@ -296,6 +296,11 @@ __global__ void __launch_bounds__(kK2Warps4096 * 32, 1) istft_inv_kernel_4096(co
 }
 
 static cudaError_t launch_k2_4096(const K2Params& p, cudaStream_t st) {
+  // Default: the two-sub-transform kernel (k2_4096v2.cu; needs 16-byte aligned frame rows for its float4 stores and a
+  // 16-byte aligned spectrum base for its bulk copies).  CRLOT_K2_4096_V1=1 selects the first version below (64
+  // registers per lane, 8 warps) for A/B timing; read per call.
+  if (getenv("CRLOT_K2_4096_V1") == nullptr && ((reinterpret_cast<uintptr_t>(p.frames) | reinterpret_cast<uintptr_t>(p.spec)) & 15) == 0)
+    return launch_istft_inv_4096v2(p, st);
   const bool win = p.window != nullptr;
   static const bool tm = getenv("CRLOT_K2_NO_TMEM") == nullptr;   // A/B switch: tables in shared memory instead
   const int smem = (tm ? 0 : (win ? 4096 * 4 : 0) + 2048 * 8) + kK2Warps4096 * kK2PerWarp4096;

@@ -56,6 +56,7 @@ struct K2Params {
 };
 cudaError_t launch_istft_inv(const K2Params& p, cudaStream_t st);
 cudaError_t launch_istft_inv_generic(const K2Params& p, cudaStream_t st);
+cudaError_t launch_istft_inv_4096v2(const K2Params& p, cudaStream_t st);   // k2_4096v2.cu: nfft 4096 as two 1024-point sub-transforms
 
 // ---- complex-domain plan: rows of n complex points, n in {128, 256, 512, 1024, 2048} --------------
 struct CfftParams {

@@ -13,6 +13,7 @@
 #include "../../crlot-dsp_b200/csrc/tables.h"
 #include "../../crlot-dsp_b200/csrc/warpfft.cuh"
 #include "../../crlot-dsp_b200/csrc/warpfft4096.cuh"
+#include "../../crlot-dsp_b200/csrc/warpfft4096v2.cuh"
 
 using namespace crlot;
 typedef std::complex<double> cd;
@@ -221,6 +222,69 @@ static int run4096() {
   return ok ? 0 : 1;
 }
 
+// N = 4096 inverse as two 1024-point sub-transforms (warpfft4096v2.cuh; k2_4096v2.cu and k23_4096.cu)
+static int run4096v2_inverse() {
+  typedef GeoX<2048> XV;
+  const int N = 4096, C = 2048;
+  FftTables T = make_fft_tables(N);
+  const cpx* sa = reinterpret_cast<const cpx*>(T.sa.data());
+  const cpx *tw = sa, *tc = sa + 1024, *qs = sa + 2048;
+  std::vector<float> x(N);
+  for (auto& s : x) s = (float)frand();
+  std::vector<cpx> Xf(C + 1);
+  for (int k = 0; k <= C; ++k) {
+    cd s = 0;
+    for (int n = 0; n < N; ++n) s += (double)x[n] * std::polar(1.0, -2.0 * M_PI * (double)n * k / N);
+    Xf[k] = mk((float)s.real(), (float)s.imag());
+  }
+  Xf[0].y = 55.0f; Xf[C].y = -9.0f;    // must be ignored
+  // every register is parked exactly once
+  int cover = 1;
+  { std::vector<int> seen(32, 0);
+    for (int c = 0; c < 4; ++c) for (int s = 0; s < 8; ++s) ++seen[v2_park_reg(c, s)];
+    for (int r = 0; r < 32; ++r) if (seen[r] != 1) cover = 0; }
+  static cpx lo[32][32], hi[32][32], ve[32][32], vo[32][32];
+  for (int l = 0; l < 32; ++l) for (int b = 0; b < 32; ++b) { lo[l][b] = Xf[l + 32 * b]; hi[l][b] = Xf[1024 + l + 32 * b]; }
+  cpx exE[32], exO[32];
+  for (int l = 0; l < 32; ++l) {       // lane l's share of lane 0's quads: four direct loads
+    const int kc = 32 * l;
+    if (l) inv4096v2_quad(Xf[kc], Xf[1024 - kc], Xf[1024 + kc], Xf[2048 - kc], qs[kc], tc[kc], exE[l], exO[l]);
+    else inv4096v2_quad0(Xf[0], Xf[1024], Xf[2048], exE[0], exO[0]);
+  }
+  for (int l = 0; l < 32; ++l) {
+    const int lp = (32 - l) & 31;
+    for (int j = 0; j < 8; ++j) for (int s = 0; s < 4; ++s) {
+      const int b = v2_chunk_reg(j, s), k = l + 32 * b;
+      cpx e, o;
+      inv4096v2_quad(lo[l][b], lo[lp][31 - b], hi[l][b], hi[lp][31 - b], qs[k], tc[k], e, o);
+      if (l == 0) { e = exE[b]; o = exO[b]; }
+      ve[l][b] = e; vo[l][b] = o;
+    }
+  }
+  std::vector<cpx> ex(XV::XCPX);
+  std::vector<double> y(N);
+  for (int h = 0; h < 2; ++h) {
+    cpx (*v)[32] = h ? vo : ve;
+    for (int l = 0; l < 32; ++l) { pass1<XV, true>(v[l]); twiddle1<XV, true>(v[l], l, tw); }
+    for (int l = 0; l < 32; ++l) xchg_write<XV>(v[l], l, ex.data());
+    for (int l = 0; l < 32; ++l) xchg_read<XV>(v[l], l, ex.data());
+    for (int l = 0; l < 32; ++l) {
+      pass2<XV, true>(v[l]);
+      for (int oa = 0; oa < 32; ++oa) {
+        const int m = l + 32 * oa;
+        y[4 * m + 2 * h] = 2.0 * v[l][oa].x / N;
+        y[4 * m + 2 * h + 1] = 2.0 * v[l][oa].y / N;
+      }
+    }
+  }
+  double err = 0, nrm = 0;
+  for (int i = 0; i < N; ++i) { err += (y[i] - x[i]) * (y[i] - x[i]); nrm += (double)x[i] * x[i]; }
+  const double inv_rel = std::sqrt(err / nrm);
+  const int ok = inv_rel < 5e-7 && cover;
+  printf("N=4096 inverse v2 (two 1024-point sub-transforms)  inv rel-L2 %.3e  registers parked once %d  %s\n", inv_rel, cover, ok ? "OK" : "FAIL");
+  return ok ? 0 : 1;
+}
+
 int main() {
   srand(1234);
   int bad = 0;
@@ -229,5 +293,6 @@ int main() {
   bad += run<1024>();
   bad += run<2048>();
   bad += run4096();
+  bad += run4096v2_inverse();
   return bad;
 }

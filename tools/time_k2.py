@@ -32,3 +32,12 @@ ts.sort()
 alg = (8.0 * plan.bins + 4.0 * N) * F
 print(f"K2 N={N} 2^{LG}: best {ts[0]:.3f} ms median {ts[len(ts)//2]:.3f} ms -> {alg / ts[len(ts)//2] / 1e6:.0f} GB/s "
       f"tmem={'off' if os.environ.get('CRLOT_K2_NO_TMEM') else 'on'} checksum {float(frames.abs().sum()):.6e}")
+
+if N == 4096 and LG <= 28:      # the two-sub-transform kernel against the first version (different roundings: tolerance, not bits)
+    os.environ["CRLOT_K2_4096_V1"] = "1"
+    f1 = torch.empty_like(frames)
+    plan.istft_frames(spec, True, out=f1)
+    torch.cuda.synchronize()
+    del os.environ["CRLOT_K2_4096_V1"]
+    d = (frames.double() - f1.double())
+    print(f"v2 vs v1: rel-L2 {float(d.norm() / f1.double().norm()):.3e} max abs {float(d.abs().max()):.3e}")
