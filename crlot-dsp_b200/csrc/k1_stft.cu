@@ -92,10 +92,11 @@ __device__ __forceinline__ void ring_fill(float* ring, int mask, const SigView& 
   if (lead > 0 || lead + nb < count) {   // only at the edges of a channel
     for (int i = lane; i < count; i += 32)
       if (i < lead || i >= lead + nb) ring[(abs0 + i) & mask] = pad_value(sv.sig, sv.len, lo + i, sv.pad_mode);
+    fence_proxy_async_smem();   // the only generic-proxy WRITES to the ring (the steady state only reads it: no fence there --
+                                // a proxy fence is a MEMBAR that also waits for the previous frame's spectrum stores)
     __syncwarp();     // the edge is in place before the barrier phase can complete
   }
-  if (lane == 0) {
-    fence_proxy_async_smem();
+  if (elect_one()) {
     mbar_arrive_expect_tx(bar, static_cast<uint32_t>(nb) * 4u);
     if (nb > 0) {
       const int r0 = static_cast<int>((abs0 + lead) & mask);
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(kK1Warps * 32, 1) stft_fwd_kernel(const K1Para
   __shared__ uint32_t s_tmem_base;
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw1 = reinterpret_cast<cpx*>(s_win + NFFT);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform by construction
   unsigned char* wb = smem_raw + SM::kTableBytes + warp * SM::per_warp_bytes(rcap);
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + rcap);
@@ -321,7 +322,7 @@ __global__ void __launch_bounds__(kK1Warps4096 * 32, 1) stft_fwd_kernel_4096(con
   __shared__ uint32_t s_tmem_base;
   float* s_win = reinterpret_cast<float*>(smem_raw);
   cpx* s_tw = reinterpret_cast<cpx*>(s_win + NFFT);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform by construction
   unsigned char* wb = smem_raw + kTable + warp * kPerWarp;
   float* ring = reinterpret_cast<float*>(wb);
   cpx* ex = reinterpret_cast<cpx*>(ring + RCAP);
