@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) stft_fwd_kernel_4096v2(const
   cpx* s_we = reinterpret_cast<cpx*>(smem_raw);          // s_we[m] = (w[4m], w[4m+1]),  s_wo[m] = (w[4m+2], w[4m+3])
   cpx* s_wo = s_we + 1024;
   cpx* s_qs = s_wo + 1024;                               // split factors, [p*32 + lane]
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform by construction
   cpx* ex = reinterpret_cast<cpx*>(smem_raw + kV2Tables + warp * kV2PerWarp);
   cpx* park = ex + XV::XCPX;
 
@@ -203,13 +203,16 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) stft_fwd_kernel_4096v2(const
       for (int h = 0; h < 2; ++h) {
         const uint32_t plane = h ? tro : tre;
         const cpx* win = h ? s_wo : s_we;
+        // all four chunks of the plane in flight at once, straight into the registers they are multiplied in (one exposed
+        // tensor-memory latency per plane instead of four)
+        cpx x8[4][8];
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) tmem_ld8(plane + 16 * (carry ? ((ch + s) & 3) : ch), x8[ch]);
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
-          cpx x8[8];
-          tmem_ld8(plane + 16 * (carry ? ((ch + s) & 3) : ch), x8);
-          tmem_wait_ld8(x8);
+          tmem_wait_ld8(x8[ch]);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[8 * ch + i] = mul2(x8[i], win[lane + 32 * (8 * ch + i)]);   // one rounding per sample
+          for (int i = 0; i < 8; ++i) v[8 * ch + i] = mul2(x8[ch][i], win[lane + 32 * (8 * ch + i)]);   // one rounding per sample
         }
         if (clean_all) {
 #pragma unroll
@@ -235,13 +238,16 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) stft_fwd_kernel_4096v2(const
         }
       }
       // ---- t = W_2048^k O[k] -------------------------------------------------------------------------------------------
+      {
+        cpx tb[2][8];                                        // the next chunk of twiddles in flight while this one multiplies
+        tmem_ld8(ttc, tb[0]);
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
-        cpx t8[8];
-        tmem_ld8(ttc + 16 * ch, t8);
-        tmem_wait_ld8(t8);
+        for (int ch = 0; ch < 4; ++ch) {
+          tmem_wait_ld8(tb[ch & 1]);
+          if (ch + 1 < 4) tmem_ld8(ttc + 16 * (ch + 1), tb[(ch + 1) & 1]);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[8 * ch + i] = cmul(v[8 * ch + i], t8[i]);
+          for (int i = 0; i < 8; ++i) v[8 * ch + i] = cmul(v[8 * ch + i], tb[ch & 1][i]);
+        }
       }
       // ---- combine + real split + store, a mirrored pair of registers at a time ----------------------------------------
       // own bin k = lane + 32*pp: Z[k] = E + t; its partner Z[2048-k] = (E - t) of the mirror lane at register 31 - pp
