@@ -274,6 +274,22 @@ class Plan:
                                                    C.c_void_p(out.data_ptr()), _stream_ptr(self.device)))
         return out
 
+    def stft_host_framequeue(self, x, center=True, pad_mode=PAD_CONSTANT, out=None):
+        """x: numpy float32 [channels, L] or [L] (ideally page-locked) -> numpy complex64 [channels, F, bins]
+        (crlot_stft_host_framequeue: FrameQueue's frames, windowed and transformed, slab by slab)."""
+        x = np.asarray(x)
+        assert x.dtype == np.float32 and x.flags.c_contiguous
+        x2 = x.reshape(1, -1) if x.ndim == 1 else x
+        ch, L = x2.shape
+        F = max(0, framequeue_count(L, self.nfft, self.hop, center))
+        if out is None:
+            out = np.empty((ch, F, self.bins), np.complex64)
+        got = C.c_longlong(0)
+        _check(lib().crlot_stft_host_framequeue(self._h, _p(x2), C.c_longlong(L), C.c_longlong(L), C.c_int(ch),
+                                                C.c_int(int(center)), C.c_int(pad_mode), _p(out), C.byref(got)))
+        assert got.value == F
+        return out
+
     def istft_frames(self, spec, fuse_synthesis_window=False, out=None):
         """spec: complex64 [..., bins] -> float32 [..., nfft] frames (1/N scaled, cleaned up)."""
         torch = _torch()

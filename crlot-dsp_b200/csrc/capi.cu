@@ -663,6 +663,23 @@ int crlot_roundtrip_execute(crlot_plan_t plan, const float* d_signal, long long 
   return crlot_ola_accumulate(plan, d_frames, F, F, channels, 1, 0, 0, d_out, out_chan_stride, n_out, stream);
 }
 
+// The three workspace slots of the host-buffer entry points (one stream each), grown on demand.
+static int ensure_host_slots(crlot_plan_t plan, long long slab_frames, int G, bool aos, bool fused, long long ist, long long ost) {
+  const int N = plan->d.nfft;
+  if (plan->slot_frames < slab_frames || plan->slot_group < G || (aos && !plan->slot_aos)) {
+    for (auto& s : plan->slot) {
+      if (!s.stream) CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+      CU(s.in.alloc(static_cast<size_t>(ist) * G));
+      CU(s.spec.alloc(static_cast<size_t>(slab_frames) * plan->bins * G));
+      if (!fused) CU(s.frames.alloc(static_cast<size_t>(slab_frames) * N * G));
+      CU(s.out.alloc(static_cast<size_t>(ost) * G));
+      if (aos) CU(s.aos.alloc(static_cast<size_t>(ist) * G));
+    }
+    plan->slot_frames = slab_frames; plan->slot_group = G; plan->slot_aos = aos;
+  }
+  return CRLOT_OK;
+}
+
 // Host-buffer round trip: time slabs through three workspace slots, one stream each, so the
 // H2D copy of slab i+1 and the D2H copy of slab i-1 overlap the kernels of slab i.
 // aos: h_in / h_out are interleaved [n][channels] (what Framer::push and WavReader hand over,
@@ -689,17 +706,7 @@ static int roundtrip_host_impl(crlot_plan_t plan, const float* h_in, long long c
   const long long ost = (slab_hops * H + N + 3) / 4 * 4;
   // slab offsets are multiples of the hop, so one eligibility test covers every slab
   const bool fused = !plan->generic && plan->k23_win_ok && istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, ost, nullptr, plan->env.p);
-  if (plan->slot_frames < slab_frames || plan->slot_group < G || (aos && !plan->slot_aos)) {
-    for (auto& s : plan->slot) {
-      if (!s.stream) CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-      CU(s.in.alloc(static_cast<size_t>(ist) * G));
-      CU(s.spec.alloc(static_cast<size_t>(slab_frames) * plan->bins * G));
-      if (!fused) CU(s.frames.alloc(static_cast<size_t>(slab_frames) * N * G));
-      CU(s.out.alloc(static_cast<size_t>(ost) * G));
-      if (aos) CU(s.aos.alloc(static_cast<size_t>(ist) * G));
-    }
-    plan->slot_frames = slab_frames; plan->slot_group = G; plan->slot_aos = aos;
-  }
+  { const int rc = ensure_host_slots(plan, slab_frames, G, aos, fused, ist, ost); if (rc) return rc; }
   // every slot launches on its own stream, hence with its own work-counter word (crlot_plan_s::counter_for)
   int it = 0;
   for (int c = 0; c < (aos ? 1 : channels); ++c) {
@@ -768,6 +775,68 @@ int crlot_roundtrip_host(crlot_plan_t plan, const float* h_in, long long chan_st
 int crlot_roundtrip_host_interleaved(crlot_plan_t plan, const float* h_in, long long len, int channels, float* h_out,
                                      long long* n_out_per_chan) {
   return roundtrip_host_impl(plan, h_in, 0, len, channels, h_out, 0, n_out_per_chan, true);
+}
+
+// FrameQueue front end from host buffers: kernel 1 over FrameQueue's frames, slab by slab through the same three
+// workspace slots (H2D of slab i+1 and D2H of the spectra of slab i-1 overlap kernel 1 of slab i).  A slab carries the
+// signal range its frames touch; the frame positions are shifted by giving kernel 1 the pad that is left at the slab's
+// first frame (centre pad minus the samples skipped -- zero for interior slabs), so interior slabs run the plain bulk-copy
+// path and only the slabs that contain a signal end compute pad positions (a reflection never reaches further than
+// nfft/2 < one slab from the end it bounces off).
+int crlot_stft_host_framequeue(crlot_plan_t plan, const float* h_signal, long long chan_stride, long long len, int channels,
+                               int center, int pad_mode, void* h_spec, long long* n_frames_out) {
+  if (!plan || !h_signal || !h_spec) return fail(CRLOT_ERR_INVALID_ARGUMENT, "null pointer");
+  if (channels <= 0 || len < 0) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (pad_mode < CRLOT_PAD_CONSTANT || pad_mode > CRLOT_PAD_EDGE) return fail(CRLOT_ERR_INVALID_ARGUMENT, "bad pad mode");
+  if (len >= (1ll << 31)) return fail(CRLOT_ERR_INVALID_ARGUMENT, "length out of range (the reference indexes with int)");
+  const int N = plan->d.nfft, H = plan->d.hop;
+  const long long F = crlot_framequeue_count(len, N, H, center);
+  if (n_frames_out) *n_frames_out = F < 0 ? 0 : F;
+  if (F <= 0) return CRLOT_OK;
+  if (!plan->generic && H % 4 != 0) return fail(CRLOT_ERR_UNSUPPORTED, "hop must be a multiple of 4");
+  DeviceGuard g(plan->d.device);
+  const long long pad = center ? N / 2 : 0;
+  // same slab geometry as the round trip, so the two entry points share their slots
+  const long long overlap = (N + H - 1) / H - 1;
+  const long long slab_hops = std::min<long long>(std::max<long long>((1ll << 24) / H, 4 * (overlap + 1)), F + overlap);
+  const long long slab_frames = slab_hops + overlap;
+  const long long ist = ((slab_frames - 1) * H + N + 3) / 4 * 4;
+  const long long ost = (slab_hops * H + N + 3) / 4 * 4;
+  const bool fused = !plan->generic && plan->k23_win_ok && istft_ola_supported(N, H, static_cast<long long>(plan->ring_len), 0, 0, ost, nullptr, plan->env.p);
+  { const int rc = ensure_host_slots(plan, slab_frames, 1, false, fused, ist, ost); if (rc) return rc; }
+  // (a signal short enough for a reflection to bounce off both ends has fewer frames than one slab holds: it goes as one
+  // slab with both true ends in it)
+  cpx* spec_out = static_cast<cpx*>(h_spec);
+  int it = 0;
+  for (int c = 0; c < channels; ++c) {
+    const float* xin = h_signal + static_cast<long long>(c) * chan_stride;
+    for (long long k_lo = 0; k_lo < F; k_lo += slab_frames, ++it) {
+      HostSlot& s = plan->slot[it % crlot_plan_s::kHostSlots];
+      const long long nf = std::min(slab_frames, F - k_lo);
+      // signal range the slab's frames touch, clipped to what exists; a slab that reaches an end keeps that end
+      long long s0 = k_lo * H - pad, s1 = (k_lo + nf - 1) * H + N - pad;
+      if (s0 < 0) s0 = 0;
+      if (s0 > len) s0 = len / 4 * 4;                                  // frames entirely inside the right pad
+      if (s1 > len) s1 = len;
+      if (pad_mode != CRLOT_PAD_CONSTANT && s1 == len) {
+        // right-pad positions mirror / repeat samples up to nfft/2 before the end: keep them in the slab
+        s0 = std::min(s0, std::max<long long>(0, (len - N) / 4 * 4));
+      }
+      if (s1 > s0)
+        CU(cudaMemcpyAsync(s.in.p, xin + s0, static_cast<size_t>(s1 - s0) * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+      K1Params k1{};
+      k1.sig = s.in.p; k1.chan_stride = 0; k1.len = s1 - s0; k1.channels = 1; k1.frames = nf; k1.nfft = N; k1.hop = H;
+      k1.pad = static_cast<int>(pad + s0 - k_lo * H); k1.pad_mode = pad_mode;
+      k1.spec = s.spec.p; k1.spec_chan_rows = nf; k1.window = plan->win_a.p; k1.tw1 = plan->tw1.p; k1.sa = plan->sa.p;
+      k1.pre = plan->pre.p; k1.counter = plan->counter_for(s.stream); k1.chunk_steps = 64; k1.scrub = plan->k1_scrub; k1.tiny2 = plan->tiny2;
+      k1.generic = plan->generic;
+      CU(launch_stft_fwd(k1, s.stream));
+      CU(cudaMemcpyAsync(spec_out + (static_cast<long long>(c) * F + k_lo) * plan->bins, s.spec.p,
+                         static_cast<size_t>(nf) * plan->bins * sizeof(cpx), cudaMemcpyDeviceToHost, s.stream));
+    }
+  }
+  for (auto& s : plan->slot) if (s.stream) CU(cudaStreamSynchronize(s.stream));
+  return CRLOT_OK;
 }
 
 int crlot_deinterleave(const float* d_interleaved, long long n, int channels, float* d_planar, long long chan_stride,

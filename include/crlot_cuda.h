@@ -162,6 +162,15 @@ int crlot_framequeue_extract(const float* d_signal, long long len, int frame, in
 int crlot_stft_execute_framequeue(crlot_plan_t plan, const float* d_signal, long long chan_stride, long long len,
                                   int channels, long long n_frames, int center, int pad_mode, void* d_spec,
                                   void* stream);
+/* The same from HOST buffers: h_signal planar [channels][chan_stride], h_spec [channels][n_frames][nfft/2+1] complex,
+ * n_frames = crlot_framequeue_count (also returned through n_frames_out).  Slabs of frames go through the plan's three
+ * host-path workspace slots (H2D, kernel 1, D2H of the spectra overlap across slabs); interior slabs run the plain
+ * path, the slabs that hold a signal end compute the pad positions.  Page-locked buffers (crlot_host_alloc) make the
+ * copies asynchronous; blocks until h_spec is complete.
+ * replaces: FrameQueue(input, len, frame, hop, center, pad_mode) + per frame window multiply + IFftPlan::forward, the
+ * frame loop of the reference's batch-framing pipeline   ref: dsp/frame/FrameQueue.cc:9-115; bench/performance_benchmark.cc:174-246 */
+int crlot_stft_host_framequeue(crlot_plan_t plan, const float* h_signal, long long chan_stride, long long len,
+                               int channels, int center, int pad_mode, void* h_spec, long long* n_frames_out);
 
 /* Kernel 2.  rows spectra -> rows frames of nfft floats, scaled by 1/nfft and cleaned up;
  * with fuse_synthesis_window != 0 each sample is additionally multiplied (one rounding) by the

@@ -105,3 +105,43 @@ def test_uncentered_equals_plain_drop_framing(cuda, dsp, oracle):
     b = plan.stft(x)
     cuda.cuda.synchronize()
     assert a.shape == b.shape and np.array_equal(bits(a.cpu().numpy()), bits(b.cpu().numpy()))
+
+
+@pytest.mark.parametrize("N,H", [(1024, 256), (2048, 512), (4096, 1024), (2048, 2048), (480, 160)])
+@pytest.mark.parametrize("mode", MODES)
+def test_host_entry_equals_device_entry(cuda, dsp, oracle, N, H, mode):
+    """crlot_stft_host_framequeue (slabs through the host-path slots) == crlot_stft_execute_framequeue on the whole
+    signal, bit for bit: short signals (one slab with both ends), both centre settings, several channels."""
+    w = oracle.window(po.HANN, N)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP)
+    rng = np.random.default_rng(3 * N + H + mode)
+    for ch, L, center in ((1, 5, True), (1, N // 2 + 3, True), (2, 5 * N + 12, True), (3, 70 * H + 41, True), (2, 9 * N + 7, False)):
+        if not center and L < N:
+            continue
+        x = rng.standard_normal((ch, L)).astype(np.float32)
+        got = plan.stft_host_framequeue(x, center, mode)
+        Lp = (L + 3) // 4 * 4
+        xd = cuda.zeros((ch, Lp), dtype=cuda.float32, device="cuda")
+        xd[:, :L] = dev(cuda, x)
+        want = plan.stft_framequeue(xd, center, mode, length=L).cpu().numpy()
+        assert got.shape == want.shape
+        assert np.array_equal(bits(got.view(np.float32)), bits(want.view(np.float32))), (ch, L, center)
+
+
+@pytest.mark.parametrize("N,H,mode", [(2048, 512, po.PAD_REFLECT), (4096, 1024, po.PAD_EDGE), (1024, 256, po.PAD_CONSTANT)])
+def test_host_entry_across_slabs(cuda, dsp, oracle, N, H, mode):
+    """A signal of several slabs (2^24 samples each): the first slab holds the left pad, interior slabs run the plain
+    path with a zero pad offset, the last one the right pad -- and a ragged length leaves a short last slab whose
+    reflection reaches back before its own first frame.  Bit-identical to the one-launch device entry."""
+    w = oracle.window(po.HANN, N)
+    plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=dsp.DROP)
+    for L in ((1 << 25) + 3 * H + 5, 2 * (1 << 24) + N // 2 - 100):
+        x = np.asarray(dsp.synth_uniform(1, L, seed=L & 0xffff).cpu().numpy())
+        got = plan.stft_host_framequeue(x, True, mode)
+        Lp = (L + 3) // 4 * 4
+        xd = cuda.zeros((1, Lp), dtype=cuda.float32, device="cuda")
+        xd[:, :L] = dev(cuda, x)
+        want = plan.stft_framequeue(xd, True, mode, length=L)
+        gd = dev(cuda, got.view(np.float32))
+        assert cuda.equal(gd.view(cuda.int32).reshape(-1), cuda.view_as_real(want).contiguous().view(cuda.int32).reshape(-1)), L
+        del xd, want, gd
