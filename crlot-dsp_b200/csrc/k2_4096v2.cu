@@ -53,41 +53,45 @@ template <bool WIN, bool SCRUB>
 __device__ __forceinline__ void sub_transform(cpx (&v)[32], const int h, int lane, cpx* ex, uint32_t ttw, uint32_t tpark,
                                               uint32_t twin, float scale) {
   if (h == 1) {                                        // finished e <-> parked o', eight registers at a time
+    cpx tb[2][8];                                      // the next parked chunk in flight while this one swaps
+    tmem_ld8(tpark, tb[0]);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      cpx t8[8], e8[8];
-      tmem_ld8(tpark + 16 * c, t8);
-      tmem_wait_ld8(t8);
+      cpx e8[8];
+      tmem_wait_ld8(tb[c & 1]);
+      if (c + 1 < 4) tmem_ld8(tpark + 16 * (c + 1), tb[(c + 1) & 1]);
 #pragma unroll
       for (int s = 0; s < 8; ++s) {
         e8[s] = v[v2_park_reg(c, s)];
-        v[v2_park_reg(c, s)] = t8[s];
+        v[v2_park_reg(c, s)] = tb[c & 1][s];
       }
       tmem_st8(tpark + 16 * c, e8);
     }
   }
   ifft1024(v, lane, ex, ttw);
+  cpx wb[2][8];                                        // window constants: the next chunk in flight while this one multiplies
+  if (WIN) tmem_ld8(twin + 64 * h, wb[0]);
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
-    cpx w8[8];
     if (WIN) {
-      tmem_ld8(twin + 64 * h + 16 * c, w8);
-      tmem_wait_ld8(w8);
+      tmem_wait_ld8(wb[c & 1]);
+      if (c + 1 < 4) tmem_ld8(twin + 64 * h + 16 * (c + 1), wb[(c + 1) & 1]);
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int oa = 8 * c + i;
       cpx y = mul2(v[oa], splat(scale));              // exact: a power of two
       if (SCRUB) y = mk(scrub(y.x), scrub(y.y));
-      if (WIN) y = mul2(y, w8[i]);                     // one rounding per sample, as std::fma(src, win, 0.0f) rounds it
+      if (WIN) y = mul2(y, wb[c & 1][i]);              // one rounding per sample, as std::fma(src, win, 0.0f) rounds it
       v[oa] = y;
     }
   }
 }
 
-// UNR: two copies of the sub-transform in the instruction stream instead of a two-trip loop (A/B: CRLOT_K2_4096_UNROLLED)
+// (Two copies of the sub-transform in the instruction stream instead of the two-trip loop were measured: the unrolled
+// kernel spills and runs 8.2 ms against 6.85 ms at that stage of the work.)
 // GAIN: the spectral-domain hook is compiled in (its loads and multiplies would otherwise ride along predicated off)
-template <bool WIN, bool SCRUB, bool UNR, bool GAIN>
+template <bool WIN, bool SCRUB, bool GAIN>
 __global__ void __launch_bounds__(kV2Warps * 32, 1) istft_inv_kernel_4096v2(const K2Params p) {
   constexpr int NFFT = 4096, C = 2048;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -278,24 +282,21 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) istft_inv_kernel_4096v2(cons
     }
 
     // ---- the two sub-transforms: ONE copy of the code, run for e' and then for o' -----------------------------------
-    if (UNR) {
-      sub_transform<WIN, SCRUB>(v, 0, lane, ex, ttw, tpark, twin, scale);
-      sub_transform<WIN, SCRUB>(v, 1, lane, ex, ttw, tpark, twin, scale);
-    } else {
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h) sub_transform<WIN, SCRUB>(v, h, lane, ex, ttw, tpark, twin, scale);
-    }
+    for (int h = 0; h < 2; ++h) sub_transform<WIN, SCRUB>(v, h, lane, ex, ttw, tpark, twin, scale);
     tmem_wait_st();
     float* dst = p.frames + rowi * NFFT;
+    cpx eb[2][8];                                          // the parked e: the next chunk in flight while this one is stored
+    tmem_ld8(tpark, eb[0]);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      cpx e8[8];
-      tmem_ld8(tpark + 16 * c, e8);
-      tmem_wait_ld8(e8);
+      tmem_wait_ld8(eb[c & 1]);
+      if (c + 1 < 4) tmem_ld8(tpark + 16 * (c + 1), eb[(c + 1) & 1]);
 #pragma unroll
       for (int s = 0; s < 8; ++s) {
         const int rg = v2_park_reg(c, s);
-        stg_stream4(reinterpret_cast<float4*>(dst + 4 * (lane + 32 * rg)), make_float4(e8[s].x, e8[s].y, v[rg].x, v[rg].y));
+        stg_stream4(reinterpret_cast<float4*>(dst + 4 * (lane + 32 * rg)),
+                    make_float4(eb[c & 1][s].x, eb[c & 1][s].y, v[rg].x, v[rg].y));
       }
     }
   }
@@ -309,13 +310,11 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) istft_inv_kernel_4096v2(cons
 cudaError_t launch_istft_inv_4096v2(const K2Params& p, cudaStream_t st) {
   const bool win = p.window != nullptr;
   void (*kern)(const K2Params) = nullptr;
-  const bool unr = getenv("CRLOT_K2_4096_UNROLLED") != nullptr;
-  const int sel = (win ? 8 : 0) | (p.scrub ? 4 : 0) | (unr ? 2 : 0) | (p.sgain != nullptr ? 1 : 0);
+  const int sel = (win ? 4 : 0) | (p.scrub ? 2 : 0) | (p.sgain != nullptr ? 1 : 0);
   switch (sel) {
-#define CRLOT_K2V2_CASE(n) case n: kern = istft_inv_kernel_4096v2<((n) & 8) != 0, ((n) & 4) != 0, ((n) & 2) != 0, ((n) & 1) != 0>; break;
-    CRLOT_K2V2_CASE(0) CRLOT_K2V2_CASE(1) CRLOT_K2V2_CASE(2) CRLOT_K2V2_CASE(3) CRLOT_K2V2_CASE(4) CRLOT_K2V2_CASE(5)
-    CRLOT_K2V2_CASE(6) CRLOT_K2V2_CASE(7) CRLOT_K2V2_CASE(8) CRLOT_K2V2_CASE(9) CRLOT_K2V2_CASE(10) CRLOT_K2V2_CASE(11)
-    CRLOT_K2V2_CASE(12) CRLOT_K2V2_CASE(13) CRLOT_K2V2_CASE(14) CRLOT_K2V2_CASE(15)
+#define CRLOT_K2V2_CASE(n) case n: kern = istft_inv_kernel_4096v2<((n) & 4) != 0, ((n) & 2) != 0, ((n) & 1) != 0>; break;
+    CRLOT_K2V2_CASE(0) CRLOT_K2V2_CASE(1) CRLOT_K2V2_CASE(2) CRLOT_K2V2_CASE(3)
+    CRLOT_K2V2_CASE(4) CRLOT_K2V2_CASE(5) CRLOT_K2V2_CASE(6) CRLOT_K2V2_CASE(7)
 #undef CRLOT_K2V2_CASE
   }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kV2Smem);
