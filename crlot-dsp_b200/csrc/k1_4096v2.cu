@@ -64,6 +64,12 @@ __device__ __forceinline__ void fft1024(cpx (&v)[32], int lane, cpx* ex, uint32_
   pass2<XV, false>(v);
 }
 
+// predicated streaming store without a compiler memory barrier (nothing in the kernel reads the spectra back)
+__device__ __forceinline__ void stg_stream_if(bool on, cpx* p, cpx v) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %3, 0;\n\t@q st.global.L1::no_allocate.v2.f32 [%0], {%1, %2};\n\t}" ::"l"(p),
+               "f"(v.x), "f"(v.y), "r"(static_cast<unsigned int>(on)));
+}
+
 // X[q] = s/2 + f, X[2048-q] = conj(s/2 - f) with s = z + conj m, f = q * (z - conj m), q = (-i/2) exp(-i pi q/2048)
 __device__ __forceinline__ void split_fwd(cpx z, cpx m, cpx q, cpx& x1, cpx& x2) {
   const cpx s = fma2(m, mk(1.f, -1.f), z);
@@ -259,19 +265,21 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) stft_fwd_kernel_4096v2(const
         const cpx zlo_p = Ep + v[pp], zhi_p = Ep - v[pp], zlo_r = Er + v[r], zhi_r = Er - v[r];
         const cpx far_r = mk(__shfl_sync(0xffffffffu, zhi_r.x, lp), __shfl_sync(0xffffffffu, zhi_r.y, lp));
         const cpx far_p = mk(__shfl_sync(0xffffffffu, zhi_p.x, lp), __shfl_sync(0xffffffffu, zhi_p.y, lp));
-        if (lane != 0) {
-          cpx x1, x2;
-          split_fwd(zlo_p, far_r, s_qs[pp * 32 + lane], x1, x2);
-          stg_stream(spec + lane + 32 * pp, x1);
-          stg_stream(spec + C - lane - 32 * pp, x2);
-          split_fwd(zlo_r, far_p, s_qs[r * 32 + lane], x1, x2);
-          stg_stream(spec + lane + 32 * r, x1);
-          stg_stream(spec + C - lane - 32 * r, x2);
-        } else {                                             // lane 0's bins 32*pp pair with its OWN registers:
-          ex[pp] = zlo_p; ex[r] = zlo_r;                     // shared out over the warp below
+        // branch-free: every lane runs the split (lane 0's results are garbage and stay unstored: its bins 32*pp pair
+        // with its OWN registers and are shared out over the warp below); the stores carry a predicate and no memory
+        // clobber, so the loads and shuffles of the next pair can be scheduled above them
+        cpx x1, x2, y1, y2;
+        split_fwd(zlo_p, far_r, s_qs[pp * 32 + lane], x1, x2);
+        split_fwd(zlo_r, far_p, s_qs[r * 32 + lane], y1, y2);
+        stg_stream_if(lane != 0, spec + lane + 32 * pp, x1);
+        stg_stream_if(lane != 0, spec + C - lane - 32 * pp, x2);
+        stg_stream_if(lane != 0, spec + lane + 32 * r, y1);
+        stg_stream_if(lane != 0, spec + C - lane - 32 * r, y2);
+        if (lane == 0) {
+          ex[pp] = zlo_p; ex[r] = zlo_r;
           ex[32 + pp] = zhi_p; ex[32 + r] = zhi_r;
-          if (pp == 0) zhi0 = zhi_p;
         }
+        if (pp == 0) zhi0 = zhi_p;
       }
       __syncwarp();
       if (lane != 0) {                                       // bins 32*l and 2048 - 32*l: Z[32 l] with Z[1024 + 32 (32 - l)]
