@@ -549,7 +549,11 @@ cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st) {
     case 256: return launch_k1<256>(p, st);
     case 512: return launch_k1<512>(p, st);
     case 1024: return launch_k1<1024>(p, st);
-    case 2048: return launch_k1<2048>(p, st);
+    case 2048:
+      // hop 512, Framer addressing: the 16-warp kernel that carries the raw samples in tensor memory (k1_2048tm.cu; same
+      // bits).  CRLOT_K1_NO_TM16=1 keeps the kernel below for the A/B (read per call).
+      if (stft_fwd_2048tm_supported(p) && getenv("CRLOT_K1_NO_TM16") == nullptr) return launch_stft_fwd_2048tm(p, st);
+      return launch_k1<2048>(p, st);
     case 4096: {
       // CRLOT_K1_4096_V1=1: the first version (one 64-register transform per frame, 8 warps) for A/B timing
       static const bool v1 = getenv("CRLOT_K1_4096_V1") != nullptr;

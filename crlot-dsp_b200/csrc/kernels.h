@@ -35,6 +35,8 @@ struct K1Params {
 cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st);
 cudaError_t launch_stft_fwd_generic(const K1Params& p, cudaStream_t st);   // k_generic.cu, called by launch_stft_fwd
 cudaError_t launch_stft_fwd_4096v2(const K1Params& p, cudaStream_t st);    // k1_4096v2.cu: nfft 4096 as two 1024-point sub-transforms
+bool stft_fwd_2048tm_supported(const K1Params& p);                         // k1_2048tm.cu: nfft 2048 / hop 512, raw samples in tensor memory, 16 warps
+cudaError_t launch_stft_fwd_2048tm(const K1Params& p, cudaStream_t st);
 bool generic_len_supported(int complex_len);
 
 // ---- kernel 2: inverse real FFT * (1/nfft) + clean-up (+ synthesis window) --------------------
