@@ -202,25 +202,218 @@ __global__ void __launch_bounds__(kTmWarps * 32, 1) stft_fwd_kernel_2048tm(const
   if (warp == 0) tmem_dealloc<512>(s_tmem_base);
 }
 
+
+// ---- N = 1024, hop = 256: two frames per warp-step (GeoX<1024>: lanes hold frames 2s and 2s+1, 16 points each) -----------
+// A hop is four register steps, so a sample stays in its lane here too.  In rows of 32 complex points from the start of
+// the chunk-run, frame f begins at row 4f and step s (frames 2s, 2s+1) spans rows [8s, 8s+20); the ring is cut into chunks of
+// eight rows OFFSET BY FOUR, chunk k = rows [8k-4, 8k+4), so that the two hops a step brings in (rows [8s+12, 8s+20)) are
+// exactly chunk s+2 -- one tcgen05.st -- and frame 2s+1 (rows [8s+4, 8s+20)) is exactly chunks s+1 and s+2; frame 2s takes
+// the upper half of chunk s, chunk s+1 and the lower half of chunk s+2 (register renaming, the three loads are shared).
+//   TMEM columns: [0,32) window, [32,64) twiddles, [64,320) four warps x 64 raw.
+using XK = GeoX<1024>;
+constexpr int kTmPerWarp1024 = XK::XCPX * 8 + kTmStage;
+constexpr int kTmSmem1024 = kTmWarps * kTmPerWarp1024;
+
+template <int SCRUB>
+__global__ void __launch_bounds__(kTmWarps * 32, 1) stft_fwd_kernel_1024tm(const K1Params p) {
+  constexpr int C = 512, A = 32, B = 16, H = 256;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint32_t s_tmem_base;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  cpx* ex = reinterpret_cast<cpx*>(smem_raw + warp * kTmPerWarp1024);
+  cpx* stage = ex + XK::XCPX;
+
+  if (warp == 0) tmem_alloc<512>(&s_tmem_base);
+  tmem_fence_before_sync();
+  __syncthreads();
+  tmem_fence_after_sync();
+  const uint32_t tmb = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+  const uint32_t twin = tmb, ttw = tmb + 32, tring = tmb + 64 + 64 * (warp >> 2);
+  if (warp < 4) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      cpx w8[8], t8[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int b = 8 * c + i;
+        w8[i] = *reinterpret_cast<const cpx*>(p.window + 2 * lane + 2 * A * b);
+        t8[i] = p.tw1[b * A + lane];
+      }
+      tmem_st8(twin + 16 * c, w8);
+      tmem_st8(ttw + 16 * c, t8);
+    }
+    tmem_wait_st();
+  }
+  tmem_fence_before_sync();
+  __syncthreads();
+  tmem_fence_after_sync();
+
+  const SplitLane<XK::M2> SL = make_split_fwd<XK>(lane);
+  const int lp = mirror_lane<B>(lane);
+  const long long frames_per_chunk = static_cast<long long>(p.chunk_steps) * 2;
+  const long long chunks_per_chan = (p.frames + frames_per_chunk - 1) / frames_per_chunk;
+  const long long total_chunks = chunks_per_chan * p.channels;
+
+  for (;;) {
+    unsigned long long qq = 0;
+    if (lane == 0) qq = atomicAdd(p.counter, 1u);
+    qq = __shfl_sync(0xffffffffu, qq, 0);
+    if (static_cast<long long>(qq) >= total_chunks) break;
+    const long long c = qq / chunks_per_chan;
+    const long long first = (qq % chunks_per_chan) * frames_per_chunk;
+    const long long nfr = min(frames_per_chunk, p.frames - first);
+    const int nsteps = static_cast<int>((nfr + 1) / 2);
+    const float* sig = p.sig + c * p.chan_stride;
+    cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (C + 1);
+    const long long p0 = first * H;                          // first sample of the run
+    int dirty = 0;
+
+    for (int s = 0; s < nsteps; ++s) {
+      unsigned int wmin = 0xffffffffu;
+      cpx nf = mk(0.f, 0.f);
+      auto screen = [&](const cpx (&x8)[8]) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const unsigned int u0 = __float_as_uint(x8[i].x), u1 = __float_as_uint(x8[i].y);
+          wmin = min(wmin, min(u0 + u0 - 2u, u1 + u1 - 2u));
+          nf = fma2(x8[i], mk(0.f, 0.f), nf);
+        }
+      };
+      // ---- new samples into the tensor-memory ring: chunk k = samples p0 + 512 k - 256 .. + 512 ---------------------------
+      if (s > 0) {                                           // chunk s+2, staged by cp.async a step ago
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncwarp();
+        cpx x8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x8[i] = stage[lane + 32 * i];
+        tmem_st8(tring + 16 * ((s + 2) & 3), x8);
+        if (SCRUB == 2) screen(x8);
+      } else {
+#pragma unroll 1
+        for (int k = 0; k < 3; ++k) {
+          cpx x8[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const long long idx = p0 + 512 * k - 256 + 2 * lane + 64 * i;
+            x8[i] = (k == 0 && i < 4) ? mk(0.f, 0.f) : ld_pair_guard_tm(sig, idx, p.len);   // rows before the run: unused
+          }
+          tmem_st8(tring + 16 * k, x8);
+          if (SCRUB == 2) screen(x8);
+        }
+      }
+      tmem_wait_st();
+      __syncwarp();                                          // every lane has read the stage
+      if (s + 1 < nsteps) {                                  // chunk s+3 for the next step
+        const long long g0 = p0 + 512ll * (s + 3) - 256;
+        const bool in = g0 + 512 <= p.len;
+        float4* st4 = reinterpret_cast<float4*>(stage);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const long long idx = g0 + 4 * (lane + 32 * i);
+          if (in)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(st4 + i * 32 + lane)), "l"(sig + idx) : "memory");
+          else
+            st4[i * 32 + lane] = ld4_guard_tm(sig, p.len, idx);
+        }
+      }
+      bool clean_all = SCRUB == 1;
+      if (SCRUB == 2) {
+        const bool suspect = (wmin < p.tiny2) || (nf.x != 0.0f) || (nf.y != 0.0f);
+        if (__any_sync(0xffffffffu, suspect)) dirty = 3;     // 3/G + 2 steps, as stft_fwd_kernel<1024>
+        clean_all = dirty > 0 || s == 0;
+        if (dirty > 0) --dirty;
+      }
+      // ---- the two frames out of the ring, times the window -------------------------------------------------------------
+      cpx v[32];
+      {
+        cpx xa[8], xb[8], xc[8], w0[8], w1[8];
+        tmem_ld8(tring + 16 * (s & 3), xa);
+        tmem_ld8(tring + 16 * ((s + 1) & 3), xb);
+        tmem_ld8(tring + 16 * ((s + 2) & 3), xc);
+        tmem_ld8(twin, w0);
+        tmem_ld8(twin + 16, w1);
+        tmem_wait_ld8(xa);
+        tmem_wait_ld8(xb);
+        tmem_wait_ld8(xc);
+        tmem_wait_ld8(w0);
+        tmem_wait_ld8(w1);
+#pragma unroll
+        for (int b = 0; b < 16; ++b) {
+          const cpx w = b < 8 ? w0[b & 7] : w1[b & 7];
+          const cpx f0 = b < 4 ? xa[4 + b] : b < 12 ? xb[b - 4] : xc[b - 12];   // frame 2s: rows 8s + b
+          const cpx f1 = b < 8 ? xb[b] : xc[b - 8];                             // frame 2s+1: rows 8s + 4 + b
+          v[b] = mul2(f0, w);                                // one rounding per sample, as frame[i]*window[i]
+          v[16 + b] = mul2(f1, w);
+        }
+      }
+      if (clean_all) {
+#pragma unroll
+        for (int r = 0; r < 32; ++r) v[r] = mk(scrub(v[r].x), scrub(v[r].y));
+      }
+      // ---- two 512-point complex transforms --------------------------------------------------------------------------------
+      {
+        cpx t0[8], t1[8];
+        tmem_ld8(ttw, t0);
+        tmem_ld8(ttw + 16, t1);
+        pass1<XK, false>(v);
+        tmem_wait_ld8(t0);
+        tmem_wait_ld8(t1);
+#pragma unroll
+        for (int ob = 1; ob < 16; ++ob) {
+          const cpx t = ob < 8 ? t0[ob & 7] : t1[ob & 7];
+          v[ob] = cmul(v[ob], t);
+          v[16 + ob] = cmul(v[16 + ob], t);
+        }
+      }
+      xchg_write<XK>(v, lane, ex);
+      __syncwarp();
+      xchg_read<XK>(v, lane, ex);
+      __syncwarp();
+      pass2<XK, false>(v);
+      cpx nyq[XK::M2], mid[XK::M2];
+      auto mirror = [&](int r) { return mk(__shfl_sync(0xffffffffu, v[r].x, lp), __shfl_sync(0xffffffffu, v[r].y, lp)); };
+      fwd_split_pairs<XK>(v, lane, SL, mirror, nyq, mid);
+      fwd_split_finish<XK>(v, lane, mirror, mid);
+      const long long left = nfr - 2ll * s;
+      const int g = lane / B, ob = lane % B;
+      if (g < left) {
+        cpx* row = spec + static_cast<long long>(g) * (C + 1);
+#pragma unroll
+        for (int oa = 0; oa < A; ++oa) stg_stream(row + ob + B * oa, v[oa]);
+        if (ob == 0) stg_stream(row + C, nyq[0]);
+      }
+      spec += 2 * (C + 1);
+    }
+  }
+  tmem_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(s_tmem_base);
+}
+
 }  // namespace
 
-bool stft_fwd_2048tm_supported(const K1Params& p) {
-  return p.nfft == 2048 && p.hop == 512 && p.pad == 0 && p.pad_mode == 0 && !p.generic;   // Framer addressing only (zeros beyond the end)
+bool stft_fwd_2048tm_supported(const K1Params& p) {   // Framer addressing only (zeros beyond the end)
+  return ((p.nfft == 2048 && p.hop == 512) || (p.nfft == 1024 && p.hop == 256)) && p.pad == 0 && p.pad_mode == 0 && !p.generic;
 }
 
 cudaError_t launch_stft_fwd_2048tm(const K1Params& p_in, cudaStream_t st) {
   K1Params p = p_in;
   p.chunk_steps = 64;
   const int mode = !p.scrub ? 0 : p.scrub == 2 ? 2 : 1;
-  auto kern = mode == 0 ? stft_fwd_kernel_2048tm<0> : mode == 1 ? stft_fwd_kernel_2048tm<1> : stft_fwd_kernel_2048tm<2>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmSmem);
+  const bool n1024 = p.nfft == 1024;
+  void (*kern)(const K1Params) = nullptr;
+  if (n1024) kern = mode == 0 ? stft_fwd_kernel_1024tm<0> : mode == 1 ? stft_fwd_kernel_1024tm<1> : stft_fwd_kernel_1024tm<2>;
+  else       kern = mode == 0 ? stft_fwd_kernel_2048tm<0> : mode == 1 ? stft_fwd_kernel_2048tm<1> : stft_fwd_kernel_2048tm<2>;
+  const int smem = n1024 ? kTmSmem1024 : kTmSmem;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
   if (e != cudaSuccess) return e;
-  const long long total_chunks = ((p.frames + p.chunk_steps - 1) / p.chunk_steps) * p.channels;
+  const long long frames_per_chunk = static_cast<long long>(p.chunk_steps) * (n1024 ? 2 : 1);
+  const long long total_chunks = ((p.frames + frames_per_chunk - 1) / frames_per_chunk) * p.channels;
   const long long want_blocks = (total_chunks + kTmWarps - 1) / kTmWarps;
   const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
-  kern<<<grid > 0 ? grid : 1, kTmWarps * 32, kTmSmem, st>>>(p);
+  kern<<<grid > 0 ? grid : 1, kTmWarps * 32, smem, st>>>(p);
   return cudaGetLastError();
 }
 

@@ -548,7 +548,9 @@ cudaError_t launch_stft_fwd(const K1Params& p, cudaStream_t st) {
   switch (p.nfft) {
     case 256: return launch_k1<256>(p, st);
     case 512: return launch_k1<512>(p, st);
-    case 1024: return launch_k1<1024>(p, st);
+    case 1024:
+      if (stft_fwd_2048tm_supported(p) && getenv("CRLOT_K1_NO_TM16") == nullptr) return launch_stft_fwd_2048tm(p, st);   // hop 256: as below
+      return launch_k1<1024>(p, st);
     case 2048:
       // hop 512, Framer addressing: the 16-warp kernel that carries the raw samples in tensor memory (k1_2048tm.cu; same
       // bits).  CRLOT_K1_NO_TM16=1 keeps the kernel below for the A/B (read per call).

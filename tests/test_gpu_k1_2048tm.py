@@ -1,4 +1,4 @@
-"""Kernel 1 for N = 2048 / hop 512, 16-warp version with the raw samples carried in tensor memory (csrc/k1_2048tm.cu)
+"""Kernel 1 for N = 2048 / hop 512 and N = 1024 / hop 256, 16-warp version with the raw samples carried in tensor memory (csrc/k1_2048tm.cu)
 against the ring kernel it replaces by default (stft_fwd_kernel<2048>, CRLOT_K1_NO_TM16=1): the same arithmetic in the
 same order, so BIT-IDENTICAL spectra; and against the oracle (kissfft_adapter.cc:83-122 -> kiss_fftr)."""
 import os
@@ -9,7 +9,6 @@ import pytest
 import pyoracle as po
 
 pytestmark = pytest.mark.gpu
-N, H = 2048, 512
 
 
 @pytest.fixture()
@@ -35,10 +34,13 @@ def ring_kernel(fn):
         del os.environ["CRLOT_K1_NO_TM16"]
 
 
+@pytest.mark.parametrize("N,H", [(2048, 512), (1024, 256)])
 @pytest.mark.parametrize("mode,L,ch", [(po.DROP, (1 << 22) + 12344, 2), (po.ZERO_PAD, 70 * 512 + 76, 3), (po.ZERO_PAD, 70 * 512 + 77, 1),
-                                       (po.DROP, 2048, 1), (po.ZERO_PAD, 5, 1), (po.DROP, 64 * 512 + 2048, 1), (po.DROP, 65 * 512 + 2048, 1)])
-def test_bit_identical_to_the_ring_kernel(cuda, dsp, oracle, mode, L, ch):
-    """Chunk boundaries (64 frames per chunk: 65 and 66 frames), ragged ZERO_PAD tails, several channels, and the clean-up
+                                       (po.DROP, 2048, 1), (po.ZERO_PAD, 5, 1), (po.DROP, 64 * 512 + 2048, 1), (po.DROP, 65 * 512 + 2048, 1),
+                                       (po.DROP, 127 * 256 + 1024, 1), (po.DROP, 128 * 256 + 1024, 1), (po.ZERO_PAD, 129 * 256 + 3, 1)])
+def test_bit_identical_to_the_ring_kernel(cuda, dsp, oracle, N, H, mode, L, ch):
+    """Chunk boundaries (64 steps per chunk: 65 and 66 frames at N = 2048, 128 to 130 at N = 1024, where a step is two
+    frames and an odd count leaves half a step), ragged ZERO_PAD tails, several channels, and the clean-up
     rule on raw samples that enter the ring once (NaN, a denormal-range value)."""
     w = oracle.window(po.HANN, N)
     plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=mode)
@@ -51,7 +53,8 @@ def test_bit_identical_to_the_ring_kernel(cuda, dsp, oracle, mode, L, ch):
     assert cuda.equal(cuda.view_as_real(a).contiguous().view(cuda.int32), cuda.view_as_real(b).contiguous().view(cuda.int32))
 
 
-def test_against_the_oracle(cuda, dsp, oracle):
+@pytest.mark.parametrize("N,H", [(2048, 512), (1024, 256)])
+def test_against_the_oracle(cuda, dsp, oracle, N, H):
     w = oracle.window(po.HANN, N)
     plan = dsp.Plan(N, H, analysis_window=w, ola_window=w, boundary_mode=po.DROP)
     L = 200 * H + N
