@@ -526,6 +526,9 @@ cudaError_t launch_k23(const K23Params& p, cudaStream_t st) {
   const int smem = NFFT * 4 + (tm ? 0 : X::C * 8) + kK23Warps * (acap * 4 + X::XCPX * 8);
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
   const int rdiv = (NFFT % p.hop == 0) ? NFFT / p.hop : 0;
+  // nfft 2048 / hop 512: the 16-warp kernel with the accumulator ring in tensor memory (k23_2048tm.cu; same bits).
+  // CRLOT_K23_NO_TM16=1 keeps the kernel below for the A/B (read per call).
+  if (NFFT == 2048 && istft_ola_2048tm_supported(p) && getenv("CRLOT_K23_NO_TM16") == nullptr) return launch_istft_ola_2048tm(p, st);
   void (*kern)(const K23Params, const int) = nullptr;
 #define CRLOT_K23_PICK(RD) kern = tm ? istft_ola_kernel<NFFT, RD, true> : istft_ola_kernel<NFFT, RD, false>
   switch (rdiv) {

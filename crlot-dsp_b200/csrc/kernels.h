@@ -140,6 +140,8 @@ bool istft_ola_supported(int nfft, int hop, long long ring_len, long long t_offs
                          long long out_chan_stride, const void* out, const void* norm);
 cudaError_t launch_istft_ola(K23Params p, cudaStream_t st);
 cudaError_t launch_istft_ola_4096(const K23Params& p, cudaStream_t st);   // k23_4096.cu, called by launch_istft_ola
+bool istft_ola_2048tm_supported(const K23Params& p);                      // k23_2048tm.cu: nfft 2048 / hop 512, accumulator ring in tensor memory, 16 warps
+cudaError_t launch_istft_ola_2048tm(const K23Params& p, cudaStream_t st);
 
 // in-place spectral hook as its own pass: spec[row][k] *= gain[row*row_stride + k]
 cudaError_t launch_spectral_gain(cpx* spec, long long rows, int bins, const float* gain, long long row_stride,
