@@ -77,9 +77,15 @@ __global__ void __launch_bounds__(kW * 32, 1) istft_ola_kernel_2048tm(const K23P
   const SplitLane<X::M1> SL = make_split_inv<X>(lane);
   const int lp = mirror_lane<A>(lane);
   const long long F = p.frames_per_chan;
+  // Chunks are handed out by an atomic counter; a warp that draws its last chunk late leaves the SM waiting at the end
+  // (6 % of the stall samples with uniform chunks).  So the first three quarters of every channel go in big chunks (few
+  // warm-up frames) and the rest, drawn after all the big ones, in chunks a quarter of the size.
   const long long nblocks = p.m_end - p.m_begin;
-  const long long chunks_per_chan = (nblocks + p.chunk_blocks - 1) / p.chunk_blocks;
-  const long long total_chunks = chunks_per_chan * p.channels;
+  const long long cb = p.chunk_blocks, cbs = cb >= 32 ? cb / 4 : cb;
+  const long long big_per_chan = (nblocks * 3 / 4) / cb;
+  const long long small_per_chan = (nblocks - big_per_chan * cb + cbs - 1) / cbs;
+  const long long total_big = big_per_chan * p.channels;
+  const long long total_chunks = total_big + small_per_chan * p.channels;
   const long long u_cov = F > 0 ? (F - 1) * H + NFFT : 0;          // u >= u_cov: no frame contributes
   const int ring_len = static_cast<int>(p.ring_len);
   const float gain = p.gain, eps = p.eps;
@@ -105,9 +111,17 @@ __global__ void __launch_bounds__(kW * 32, 1) istft_ola_kernel_2048tm(const K23P
     if (lane == 0) q = atomicAdd(p.counter, 1u);
     q = __shfl_sync(0xffffffffu, q, 0);
     if (static_cast<long long>(q) >= total_chunks) break;
-    const long long c = q / chunks_per_chan;
-    const long long m0 = p.m_begin + (q % chunks_per_chan) * p.chunk_blocks;
-    const long long m1 = min(m0 + p.chunk_blocks, p.m_end);
+    long long c, m0, m1;
+    if (static_cast<long long>(q) < total_big) {
+      c = q / big_per_chan;
+      m0 = p.m_begin + (q % big_per_chan) * cb;
+      m1 = m0 + cb;
+    } else {
+      const long long qs = q - total_big;
+      c = qs / small_per_chan;
+      m0 = p.m_begin + big_per_chan * cb + (qs % small_per_chan) * cbs;
+      m1 = min(m0 + cbs, p.m_end);
+    }
     const cpx* spec = p.spec + c * p.spec_chan_rows * (C + 1);
     float* out = p.out + c * p.out_chan_stride;
     const float* sgain = p.sgain ? p.sgain + c * p.spec_chan_rows * p.sgain_row_stride : nullptr;
@@ -178,6 +192,12 @@ __global__ void __launch_bounds__(kW * 32, 1) istft_ola_kernel_2048tm(const K23P
       fence_proxy_async_smem();                          // this lane's generic-proxy writes to the buffer before the copy's
       __syncwarp();
       if (k + 1 < k1) stage_row(spec + (k + 1) * (C + 1));
+      if (k + 2 < k1) {                                  // and the row after it into L2: the copy then takes an L2 round trip
+        const char* nx = reinterpret_cast<const char*>(spec + (k + 2) * (C + 1)) + lane * 128;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(nx));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 4096));
+        if (lane == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 8192));
+      }
       pass2<X, true>(v);                                 // v[oa] = samples 2*lane + 64*oa, +1 (raw, times N/2)
 
       // ---- clean-up screen on the raw registers (non-finite, or 0 < |v * 2/N| < 1e-30) ----------------------------------
@@ -327,7 +347,9 @@ cudaError_t launch_istft_ola_2048tm(const K23Params& p, cudaStream_t st) {
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
   if (e != cudaSuccess) return e;
   const long long nblocks = p.m_end - p.m_begin;
-  const long long total_chunks = ((nblocks + p.chunk_blocks - 1) / p.chunk_blocks) * p.channels;
+  const long long cb = p.chunk_blocks, cbs = cb >= 32 ? cb / 4 : cb;           // as in the kernel
+  const long long big_per_chan = (nblocks * 3 / 4) / cb;
+  const long long total_chunks = (big_per_chan + (nblocks - big_per_chan * cb + cbs - 1) / cbs) * p.channels;
   const long long want_blocks = (total_chunks + kW - 1) / kW;
   const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
   istft_ola_kernel_2048tm<<<grid > 0 ? grid : 1, kW * 32, kSmem, st>>>(p);
