@@ -130,9 +130,13 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) stft_fwd_kernel_4096v2(const
   }
   const int H = p.hop;
   const bool carry = H == 1024 && p.pad == 0;              // raw samples stay in tensor memory between frames
-  const long long frames_per_chunk = p.chunk_steps;
-  const long long chunks_per_chan = (p.frames + frames_per_chunk - 1) / frames_per_chunk;
-  const long long total_chunks = chunks_per_chan * p.channels;
+  // chunk_steps frames per chunk for the first three quarters of a channel, a quarter of that for the rest (drawn after
+  // all the big ones): few chunk starts -- each re-reads three hops -- and still a short tail at the end of the kernel
+  const long long cb = p.chunk_steps, cbs = cb >= 16 ? cb / 4 : cb;
+  const long long big_per_chan = (p.frames * 3 / 4) / cb;
+  const long long small_per_chan = (p.frames - big_per_chan * cb + cbs - 1) / cbs;
+  const long long total_big = big_per_chan * p.channels;
+  const long long total_chunks = total_big + small_per_chan * p.channels;
   const int lp = (32 - lane) & 31;
 
   for (;;) {
@@ -140,9 +144,18 @@ __global__ void __launch_bounds__(kV2Warps * 32, 1) stft_fwd_kernel_4096v2(const
     if (lane == 0) qq = atomicAdd(p.counter, 1u);
     qq = __shfl_sync(0xffffffffu, qq, 0);
     if (static_cast<long long>(qq) >= total_chunks) break;
-    const long long c = qq / chunks_per_chan;
-    const long long first = (qq % chunks_per_chan) * frames_per_chunk;
-    const int nsteps = static_cast<int>(min(frames_per_chunk, p.frames - first));
+    long long c, first;
+    int nsteps;
+    if (static_cast<long long>(qq) < total_big) {
+      c = qq / big_per_chan;
+      first = (qq % big_per_chan) * cb;
+      nsteps = static_cast<int>(cb);
+    } else {
+      const long long qs = qq - total_big;
+      c = qs / small_per_chan;
+      first = big_per_chan * cb + (qs % small_per_chan) * cbs;
+      nsteps = static_cast<int>(min(cbs, p.frames - first));
+    }
     const float* sig = p.sig + c * p.chan_stride;
     cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (C + 1);
     int dirty = 0;
@@ -308,14 +321,16 @@ cudaError_t launch_stft_fwd_4096v2(const K1Params& p_in, cudaStream_t st) {
   K1Params p = p_in;
   // Short chunks: a frame takes ~10 us of a warp, so a 64-frame chunk is a 0.7 ms tail on a 6 ms kernel (32: half); the price of a
   // chunk start is three extra hops read (from L2: the neighbouring chunk has just used them).
-  p.chunk_steps = 32;
+  p.chunk_steps = 64;                                      // big chunks; the last quarter of a channel goes in chunks of 16
   const int mode = !p.scrub ? 0 : p.scrub == 2 ? 2 : 1;
   auto kern = mode == 0 ? stft_fwd_kernel_4096v2<0> : mode == 1 ? stft_fwd_kernel_4096v2<1> : stft_fwd_kernel_4096v2<2>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kV2Smem);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
   if (e != cudaSuccess) return e;
-  const long long total_chunks = ((p.frames + p.chunk_steps - 1) / p.chunk_steps) * p.channels;
+  const long long cb = p.chunk_steps, cbs = cb >= 16 ? cb / 4 : cb;      // as in the kernel
+  const long long big_per_chan = (p.frames * 3 / 4) / cb;
+  const long long total_chunks = (big_per_chan + (p.frames - big_per_chan * cb + cbs - 1) / cbs) * p.channels;
   const long long want_blocks = (total_chunks + kV2Warps - 1) / kV2Warps;
   const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
   kern<<<grid > 0 ? grid : 1, kV2Warps * 32, kV2Smem, st>>>(p);
