@@ -19,7 +19,7 @@ LIB = os.path.join(HERE, "libcrlot_cuda.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
-SOURCES = ["k1_stft.cu", "k1_4096v2.cu", "k1_2048tm.cu", "k2_istft.cu", "k2_4096v2.cu", "k3_ola.cu", "k23_istft_ola.cu", "k23_4096.cu", "k23_2048tm.cu", "k_cfft.cu", "k_generic.cu", "aux_kernels.cu", "stream_kernels.cu", "framer.cu", "ring.cu", "shard.cu", "capi.cu"]
+SOURCES = ["k1_stft.cu", "k1_4096v2.cu", "k1_2048tm.cu", "k2_istft.cu", "k2_4096v2.cu", "k3_ola.cu", "k23_istft_ola.cu", "k23_4096.cu", "k23_2048tm.cu", "k_rt_2048tm.cu", "k_cfft.cu", "k_generic.cu", "aux_kernels.cu", "stream_kernels.cu", "framer.cu", "ring.cu", "shard.cu", "capi.cu"]
 
 
 def _newer(target, deps):

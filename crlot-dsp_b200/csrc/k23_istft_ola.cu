@@ -542,6 +542,9 @@ cudaError_t launch_k23(const K23Params& p, cudaStream_t st) {
   if (p.sig != nullptr) {                        // fully fused round trip
     if constexpr (NFFT == 2048) {
       if (rdiv != 4) return cudaErrorNotSupported;
+      // 16-byte aligned signal rows: the 16-warp kernel with both rings in tensor memory (k_rt_2048tm.cu; same bits).
+      // CRLOT_RT_NO_TM16=1 keeps the kernel below for the A/B (read per call).
+      if (roundtrip_2048tm_supported(p) && getenv("CRLOT_RT_NO_TM16") == nullptr) return launch_roundtrip_2048tm(p, st);
       kern = istft_ola_kernel<2048, 4, true, true>;
     } else {
       return cudaErrorNotSupported;

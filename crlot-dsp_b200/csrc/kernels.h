@@ -142,6 +142,8 @@ cudaError_t launch_istft_ola(K23Params p, cudaStream_t st);
 cudaError_t launch_istft_ola_4096(const K23Params& p, cudaStream_t st);   // k23_4096.cu, called by launch_istft_ola
 bool istft_ola_2048tm_supported(const K23Params& p);                      // k23_2048tm.cu: nfft 2048 / hop 512, accumulator ring in tensor memory, 16 warps
 cudaError_t launch_istft_ola_2048tm(const K23Params& p, cudaStream_t st);
+bool roundtrip_2048tm_supported(const K23Params& p);                      // k_rt_2048tm.cu: the one-kernel round trip, both rings in tensor memory, 16 warps
+cudaError_t launch_roundtrip_2048tm(const K23Params& p, cudaStream_t st);
 
 // in-place spectral hook as its own pass: spec[row][k] *= gain[row*row_stride + k]
 cudaError_t launch_spectral_gain(cpx* spec, long long rows, int bins, const float* gain, long long row_stride,
