@@ -71,18 +71,31 @@ __global__ void __launch_bounds__(kTmWarps * 32, 1) stft_fwd_kernel_2048tm(const
 
   const SplitLane<XT::M2> SL = make_split_fwd<XT>(lane);
   const int lp = mirror_lane<B>(lane);
-  const long long frames_per_chunk = p.chunk_steps;
-  const long long chunks_per_chan = (p.frames + frames_per_chunk - 1) / frames_per_chunk;
-  const long long total_chunks = chunks_per_chan * p.channels;
+  // Graded chunks, as in the fused kernel: whole chunks for the first three quarters of a channel, quarter chunks after
+  // them, so that the warps run dry within a quarter chunk of each other at the end of the launch.
+  const long long cb = p.chunk_steps, cbs = cb >= 16 ? cb / 4 : cb;
+  const long long big_per_chan = (p.frames * 3 / 4) / cb;
+  const long long small_per_chan = (p.frames - big_per_chan * cb + cbs - 1) / cbs;
+  const long long total_big = big_per_chan * p.channels;
+  const long long total_chunks = total_big + small_per_chan * p.channels;
 
   for (;;) {
     unsigned long long qq = 0;
     if (lane == 0) qq = atomicAdd(p.counter, 1u);
     qq = __shfl_sync(0xffffffffu, qq, 0);
     if (static_cast<long long>(qq) >= total_chunks) break;
-    const long long c = qq / chunks_per_chan;
-    const long long first = (qq % chunks_per_chan) * frames_per_chunk;
-    const int nsteps = static_cast<int>(min(frames_per_chunk, p.frames - first));
+    long long c, first;
+    int nsteps;
+    if (static_cast<long long>(qq) < total_big) {
+      c = qq / big_per_chan;
+      first = (qq % big_per_chan) * cb;
+      nsteps = static_cast<int>(cb);
+    } else {
+      const long long qs = qq - total_big;
+      c = qs / small_per_chan;
+      first = big_per_chan * cb + (qs % small_per_chan) * cbs;
+      nsteps = static_cast<int>(min(cbs, p.frames - first));
+    }
     const float* sig = p.sig + c * p.chan_stride;
     cpx* spec = p.spec + (c * p.spec_chan_rows + first) * (C + 1);
     int dirty = 0;
@@ -409,8 +422,15 @@ cudaError_t launch_stft_fwd_2048tm(const K1Params& p_in, cudaStream_t st) {
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st);
   if (e != cudaSuccess) return e;
-  const long long frames_per_chunk = static_cast<long long>(p.chunk_steps) * (n1024 ? 2 : 1);
-  const long long total_chunks = ((p.frames + frames_per_chunk - 1) / frames_per_chunk) * p.channels;
+  long long total_chunks;
+  if (n1024) {
+    const long long frames_per_chunk = static_cast<long long>(p.chunk_steps) * 2;
+    total_chunks = ((p.frames + frames_per_chunk - 1) / frames_per_chunk) * p.channels;
+  } else {                                                                     // graded, as in the kernel
+    const long long cb = p.chunk_steps, cbs = cb >= 16 ? cb / 4 : cb;
+    const long long big_per_chan = (p.frames * 3 / 4) / cb;
+    total_chunks = (big_per_chan + (p.frames - big_per_chan * cb + cbs - 1) / cbs) * p.channels;
+  }
   const long long want_blocks = (total_chunks + kTmWarps - 1) / kTmWarps;
   const int grid = static_cast<int>(want_blocks < device_sm_count() ? want_blocks : device_sm_count());
   kern<<<grid > 0 ? grid : 1, kTmWarps * 32, smem, st>>>(p);
