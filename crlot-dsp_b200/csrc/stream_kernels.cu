@@ -15,6 +15,8 @@
 //
 // The transforms reuse the warp-autonomous register FFT of kernels 1 and 2 (warpfft.cuh); a
 // warp-step takes its G frames from G *different streams* when a tick yields one frame per stream.
+#include <type_traits>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "warpfft.cuh"
@@ -249,20 +251,27 @@ __global__ void __launch_bounds__(kSWarps * 32) stream_tick1_kernel(const Stream
        step += static_cast<long long>(gridDim.x) * kSWarps) {
     const long long s_base = step * G;
     // 1. ingest the chunks of this step's streams
-    for (int q0 = lane; q0 < G * CL; q0 += 128) {        // four independent loads in flight per lane
-      float val[4];
-      long long dst[4];
+    constexpr int IB = 16;                                // sixteen independent loads in flight per lane: with one hop
+    const int dg = 32 / CL, di = 32 - dg * CL;            // of 64 samples per stream (G = 8) that is ONE round trip
+    for (int q0 = lane; q0 < G * CL; q0 += 32 * IB) {
+      float val[IB];
+      long long dst[IB];
+      int g = q0 / CL, i = q0 - g * CL;                   // (stream, sample) of q0 + 32 u, stepped instead of divided
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int q = q0 + 32 * u;
-        const int g = q / CL, i = q - g * CL;
+      for (int u = 0; u < IB; ++u) {
         const long long s = s_base + g;
-        const bool ok = q < G * CL && s < S;
+        const bool ok = g < G && s < S;
         dst[u] = ok ? s * p.rcap + ((w + i) & mask) : -1;
         val[u] = ok ? __ldg(chunk + s * p.chunk_stride + i) : 0.0f;
+        g += dg;
+        i += di;
+        if (i >= CL) {
+          i -= CL;
+          ++g;
+        }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+      for (int u = 0; u < IB; ++u)
         if (dst[u] >= 0) p.ring[dst[u]] = val[u];
     }
     __syncwarp();
@@ -336,56 +345,68 @@ __global__ void __launch_bounds__(kSWarps * 32) stream_tick1_kernel(const Stream
     pass2<X, true>(v);
     // 4. accumulate at k0*hop, produce the first hop (normalize_and_clear), keep the rest.
     //    All accumulator / envelope loads of a register group are issued before the first store, so a
-    //    group costs one L2 round trip instead of one per sample pair.
+    //    group costs one L2 round trip instead of one per sample pair.  With hop <= nfft/4 (the usual case, tested once
+    //    per warp) only the first quarter of a group's registers can fall below the hop: the others are compiled WITHOUT
+    //    the normalise-and-clear branch and its two IEEE divisions -- 24 of 32 taken branches and their code go away
+    //    (the tick is paced by one warp's instruction stream: `no_instruction` was half of the stall samples of this
+    //    step, profiles/r2g_ncu_tick.*).
+    auto step4 = [&](auto hop_small) {
+      constexpr bool HS = decltype(hop_small)::value;
+      constexpr int AQ = A >= 4 ? A / 4 : 1;
 #pragma unroll
-    for (int j = 0; j < X::M2; ++j) {
-      const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
-      const long long s = s_base + g;
-      if (s < S) {
-        float* accb = p.acc + s * p.ring_len;
-        float* outb = p.out + s * p.out_stride + (k0 - p.k_base) * H;
-        constexpr int AB = A < 16 ? A : 16;                 // loads batched 16 registers at a time
+      for (int j = 0; j < X::M2; ++j) {
+        const int i2 = lane + 32 * j, g = i2 / B, ob = i2 % B;
+        const long long s = s_base + g;
+        if (s < S) {
+          float* accb = p.acc + s * p.ring_len;
+          float* outb = p.out + s * p.out_stride + (k0 - p.k_base) * H;
+          constexpr int AB = A < 16 ? A : 16;                 // loads batched 16 registers at a time
 #pragma unroll
-        for (int o0 = 0; o0 < A; o0 += AB) {
-          float2 a2[AB], nm[AB];
-          int rps[AB];
+          for (int o0 = 0; o0 < A; o0 += AB) {
+            float2 a2[AB], nm[AB];
+            int rps[AB];
 #pragma unroll
-          for (int q = 0; q < AB; ++q) {
-            const int i = 2 * (ob + B * (o0 + q));
-            int rp = e0 + i;
-            if (rp >= p.ring_len) rp -= static_cast<int>(p.ring_len);
-            rps[q] = rp;
-            a2[q] = __ldcg(reinterpret_cast<const float2*>(accb + rp));
-            nm[q] = i < H ? __ldg(reinterpret_cast<const float2*>(p.norm + rp)) : make_float2(1.f, 1.f);
+            for (int q = 0; q < AB; ++q) {
+              const int i = 2 * (ob + B * (o0 + q));
+              const bool may = !HS || o0 + q < AQ;            // compile-time
+              int rp = e0 + i;
+              if (rp >= p.ring_len) rp -= static_cast<int>(p.ring_len);
+              rps[q] = rp;
+              a2[q] = __ldcg(reinterpret_cast<const float2*>(accb + rp));
+              nm[q] = (may && i < H) ? __ldg(reinterpret_cast<const float2*>(p.norm + rp)) : make_float2(1.f, 1.f);
+            }
+#pragma unroll
+            for (int q = 0; q < AB; ++q) {
+              const int oa = o0 + q, i = 2 * (ob + B * oa);
+              const bool may = !HS || oa < AQ;                // compile-time
+              float y0 = v[j * A + oa].x * scale, y1 = v[j * A + oa].y * scale;
+              if (SCRUB) {
+                y0 = scrub(y0);
+                y1 = scrub(y1);
+              }
+              if (WIN) {
+                const float2 ws = *reinterpret_cast<const float2*>(s_wsyn + i);
+                y0 = __fmul_rn(y0, ws.x);
+                y1 = __fmul_rn(y1, ws.y);
+              }
+              float2 acc2 = a2[q];
+              acc2.x = __fmaf_rn(y0, p.gain, acc2.x);
+              acc2.y = __fmaf_rn(y1, p.gain, acc2.y);
+              if (may && i < H) {
+                *reinterpret_cast<float2*>(outb + i) =
+                    make_float2(__fdiv_rn(acc2.x, fmaxf(nm[q].x, p.eps)), __fdiv_rn(acc2.y, fmaxf(nm[q].y, p.eps)));
+                acc2 = make_float2(0.f, 0.f);
+              }
+              a2[q] = acc2;
+            }
+#pragma unroll
+            for (int q = 0; q < AB; ++q) *reinterpret_cast<float2*>(accb + rps[q]) = a2[q];
           }
-#pragma unroll
-          for (int q = 0; q < AB; ++q) {
-            const int oa = o0 + q, i = 2 * (ob + B * oa);
-            float y0 = v[j * A + oa].x * scale, y1 = v[j * A + oa].y * scale;
-            if (SCRUB) {
-              y0 = scrub(y0);
-              y1 = scrub(y1);
-            }
-            if (WIN) {
-              const float2 ws = *reinterpret_cast<const float2*>(s_wsyn + i);
-              y0 = __fmul_rn(y0, ws.x);
-              y1 = __fmul_rn(y1, ws.y);
-            }
-            float2 acc2 = a2[q];
-            acc2.x = __fmaf_rn(y0, p.gain, acc2.x);
-            acc2.y = __fmaf_rn(y1, p.gain, acc2.y);
-            if (i < H) {
-              *reinterpret_cast<float2*>(outb + i) =
-                  make_float2(__fdiv_rn(acc2.x, fmaxf(nm[q].x, p.eps)), __fdiv_rn(acc2.y, fmaxf(nm[q].y, p.eps)));
-              acc2 = make_float2(0.f, 0.f);
-            }
-            a2[q] = acc2;
-          }
-#pragma unroll
-          for (int q = 0; q < AB; ++q) *reinterpret_cast<float2*>(accb + rps[q]) = a2[q];
         }
       }
-    }
+    };
+    if (4 * H <= NFFT) step4(std::true_type{});
+    else               step4(std::false_type{});
   }
   // 5. the last block to finish advances the counters
   __syncthreads();
